@@ -1,0 +1,133 @@
+"""ctypes binding of the CPU oracle (oracle/rnafold_oracle.c).  TEST INFRASTRUCTURE ONLY.
+
+Importable only from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs.  The product package (rnagent_b200) never imports this module.
+
+Restates RNA.fold of ViennaRNA 2.4.14 as bound by the reference at rlif/settings.py:63-64;
+parity pinned by tests/golden/vienna_logged_rows.jsonl (rows of rlif/logs/*/solutions*.csv).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "librnafold_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = [os.path.join(_HERE, f) for f in ("rnafold_oracle.c", "rnafold_oracle.h", "Makefile")]
+    if (not force and os.path.exists(_SO)
+            and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in src)):
+        return _SO
+    subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = ctypes.CDLL(_SO)
+        L.orc_params_new.restype = ctypes.c_void_p
+        L.orc_params_free.argtypes = [ctypes.c_void_p]
+        L.orc_params_load.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.orc_params_export.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_fold.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_char_p,
+                               ctypes.POINTER(ctypes.c_int)]
+        L.orc_last_fold_candidates.restype = ctypes.c_longlong
+        L.orc_eval_structure.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_char_p,
+                                         ctypes.POINTER(ctypes.c_int)]
+        L.orc_bruteforce_mfe.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int,
+                                         ctypes.POINTER(ctypes.c_int)]
+        L.orc_fold_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                     ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_int]
+        _lib = L
+    return _lib
+
+
+def mfe_float(dcal):
+    """ViennaRNA returns (float)(e/100.): float32 of the double quotient, widened by Python."""
+    return float(np.float32(np.float64(dcal) / 100.0))
+
+
+class Params:
+    """One loaded parameter set (RNA.read_parameter_file equivalent for the oracle)."""
+
+    def __init__(self, path):
+        self._L = lib()
+        self._p = self._L.orc_params_new()
+        rc = self._L.orc_params_load(self._p, os.fsencode(path))
+        if rc != 0:
+            raise RuntimeError(f"oracle: cannot load parameter file {path!r} (rc={rc})")
+        self.path = path
+
+    def __del__(self):
+        try:
+            self._L.orc_params_free(self._p)
+        except Exception:
+            pass
+
+    def export(self):
+        n = self._L.orc_params_export_size()
+        out = np.zeros(n, dtype=np.int32)
+        k = self._L.orc_params_export(self._p, out.ctypes.data)
+        assert k == n, (k, n)
+        return out
+
+    def fold_dcal(self, seq):
+        b = seq.encode()
+        db = ctypes.create_string_buffer(len(b) + 1)
+        e = ctypes.c_int(0)
+        rc = self._L.orc_fold(self._p, b, len(b), db, ctypes.byref(e))
+        if rc != 0:
+            raise RuntimeError(f"oracle: backtrack failed rc={rc} for {seq}")
+        return db.value.decode(), e.value
+
+    def fold(self, seq):
+        s, e = self.fold_dcal(seq)
+        return s, mfe_float(e)
+
+    def last_candidates(self):
+        return int(self._L.orc_last_fold_candidates())
+
+    def eval_structure(self, seq, db):
+        e = ctypes.c_int(0)
+        rc = self._L.orc_eval_structure(self._p, seq.encode(), len(seq), db.encode(), ctypes.byref(e))
+        if rc != 0:
+            raise ValueError(f"oracle: invalid structure rc={rc}")
+        return e.value
+
+    def bruteforce_mfe(self, seq):
+        e = ctypes.c_int(0)
+        rc = self._L.orc_bruteforce_mfe(self._p, seq.encode(), len(seq), ctypes.byref(e))
+        if rc != 0:
+            raise ValueError("oracle: bruteforce needs n <= 20")
+        return e.value
+
+    def fold_batch(self, seqs_u8, off, targets_u8=None, nthreads=0):
+        """seqs_u8: uint8 ASCII concatenation, off: int32[B+1].  Returns (db_u8, mfe_dcal, hd)."""
+        seqs_u8 = np.ascontiguousarray(seqs_u8, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int32)
+        B = len(off) - 1
+        db = np.zeros_like(seqs_u8)
+        mfe = np.zeros(B, dtype=np.int32)
+        hd = np.zeros(B, dtype=np.int32)
+        tp = None
+        if targets_u8 is not None:
+            targets_u8 = np.ascontiguousarray(targets_u8, dtype=np.uint8)
+            tp = targets_u8.ctypes.data
+        rc = self._L.orc_fold_batch(self._p, seqs_u8.ctypes.data, off.ctypes.data, B, tp,
+                                    db.ctypes.data, mfe.ctypes.data, hd.ctypes.data, int(nthreads))
+        if rc != 0:
+            raise RuntimeError(f"oracle: batch fold failed rc={rc}")
+        return db, mfe, hd
+
+
+def hamming_distance(a, b):
+    """rlif/rna/utils.py:67-75 restated: zip-truncating; returns (hd, mismatch indices)."""
+    m = [x != y for x, y in zip(a, b)]
+    return sum(m), np.where(m)[0]
