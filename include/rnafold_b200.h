@@ -1,0 +1,103 @@
+/*
+ * rnafold_b200.h -- C ABI of the B200-native replacement for the reference's reward hot path:
+ * batched Zuker MFE folding (Turner nearest-neighbour model, ViennaRNA defaults dangles=2,
+ * MAXLOOP=30, integer dcal/mol) + dot-bracket Hamming distance to a target structure.
+ *
+ * Plain pointers and sizes only; no torch/CUDA types.  Every entry point returns 0 on success or a
+ * negative RNAFOLD_E* code and records a message retrievable with rnafold_last_error().
+ *
+ * Reference interfaces each entry point replaces (paths relative to the reference checkout):
+ *   rnafold_fold_batch / rnafold_fold_hamming_batch
+ *        <- `fold_fn(string) -> (structure, mfe)` = RNA.fold, bound at rlif/settings.py:62-71 and called
+ *           at rlif/rna/solution.py:134,140,204; rlif/rna/utils.py:23; rlif/CLI.py:216;
+ *           fused with hamming_distance (rlif/rna/utils.py:67-75) and the reward of
+ *           Solution.evaluate (rlif/rna/solution.py:145-149).
+ *   rnafold_read_parameter_file
+ *        <- RNA.read_parameter_file(path): rlif/rna/vienna.py:18, rlif/CLI.py:21,
+ *           rlif/interface/widgets.py:31, rlif/interface/parameters.py:10.
+ *   rnafold_set_md
+ *        <- setattr(RNA.cvar, name, value): rlif/rna/vienna.py:21-26, rlif/interface/widgets.py:25-26;
+ *           names temperature, dangles, noGU, no_closingGU, uniq_ML (rlif/settings.py:35-39).
+ *
+ * Buffers: every input/output pointer may be a host pointer or a device pointer on the context's
+ * device (detected with cudaPointerGetAttributes).  Host buffers are staged through pinned memory
+ * inside the call; device buffers are used in place and the call is asynchronous on `stream`
+ * (a cudaStream_t passed as void*, NULL = the context's own stream) unless any buffer is a host one.
+ *
+ * Batches are CSR: `seq` holds the ASCII nucleotides of all B sequences back to back and `off[B+1]`
+ * their start offsets (off[0] = 0).  Structures are written with the same offsets.
+ */
+#ifndef RNAFOLD_B200_H
+#define RNAFOLD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RNAFOLD_OK 0
+#define RNAFOLD_EINVAL -1   /* bad argument */
+#define RNAFOLD_ECUDA -2    /* CUDA runtime error (sticky) */
+#define RNAFOLD_EIO -3      /* parameter file unreadable / malformed */
+#define RNAFOLD_ENOTSUP -4  /* model detail other than the reference's defaults */
+#define RNAFOLD_ENOINIT -5  /* rnafold_init not called */
+
+#define RNAFOLD_MAX_LEN 4000 /* longest sequence accepted */
+
+/* Create the per-process context on CUDA device `device`, load the built-in Turner 2004
+ * parameters (ViennaRNA's compiled-in default) and upload them.  Idempotent per device. */
+int rnafold_init(int device);
+void rnafold_shutdown(void);
+const char *rnafold_last_error(void);
+const char *rnafold_version(void);
+
+/* Parse an "RNAfold parameter file v2.0", rescale for 37 C / dangles=2 and upload.  Takes effect
+ * on the next fold, like the process-global state of RNA.read_parameter_file. */
+int rnafold_read_parameter_file(const char *path);
+/* Flat int32 dump of the live parameter tables in the oracle's export order (tests only);
+ * returns the number of ints written (<= cap) or a negative code. */
+int rnafold_export_params(int32_t *out, int cap);
+
+/* Host-only variant: parse `path` (NULL = built-in Turner 2004) without touching a device and dump
+ * the tables the same way.  Used by the CPU test-suite to check the loader. */
+int rnafold_parse_params(const char *path, int32_t *out, int cap);
+
+/* Model details (RNA.cvar).  Only the reference's defaults are implemented: temperature=37,
+ * dangles=2, noGU=0, no_closingGU=0, uniq_ML=0.  Any other value -> RNAFOLD_ENOTSUP. */
+int rnafold_set_md(const char *name, double value);
+int rnafold_get_md(const char *name, double *value);
+
+/* Bytes of device scratch a batch of B sequences with maximum length nmax will use. */
+int rnafold_workspace_bytes(int32_t B, int32_t nmax, size_t *bytes);
+
+/* Fold B sequences.  db_out: total-length bytes ('(', ')', '.'); mfe_dcal_out: int32[B] in
+ * dcal/mol (RNA.fold's float is (float)(e/100.)). */
+int rnafold_fold_batch(const uint8_t *seq, const int32_t *off, int32_t B, uint8_t *db_out,
+                       int32_t *mfe_dcal_out, void *stream);
+
+/* Fold + Hamming distance to `target` (same CSR offsets as seq) + reward
+ * r = (1 - hd/len)^reward_exp (+0.25 if hd == 0), as rlif/rna/solution.py:145-148.
+ * hd_out int32[B]; reward_out float64[B] (may be NULL); mismatch_out: one byte per position
+ * (1 where target != structure; may be NULL); db_out / mfe_dcal_out may be NULL. */
+int rnafold_fold_hamming_batch(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target,
+                               uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
+                               double *reward_out, uint8_t *mismatch_out, double reward_exp,
+                               void *stream);
+
+/* Counters of the last fold call: kernel launches issued, and sequences routed to each kernel
+ * family (0: shared-memory CTA kernel, 1: cluster/DSMEM kernel, 2: global-memory kernel). */
+int rnafold_last_launch_info(int32_t *launches, int32_t routed[3]);
+
+/* Enable (1) / disable (0) CUDA-event timing of the kernels of each fold call. */
+int rnafold_set_timing(int enabled);
+
+/* Time of the last fold call's kernels in milliseconds, measured with CUDA events on the stream
+ * the kernels were launched on (synchronises the stream). */
+int rnafold_last_kernel_ms(float *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -420,6 +420,7 @@ int orc_fold(const orc_params *P, const char *seq_in, int n, char *db, int *mfe_
   short *S = (short *)malloc(sizeof(short) * (size_t)(n + 2));
   for (int k = 0; k < n; k++) {
     seq[k] = (char)toupper((unsigned char)seq_in[k]);
+    if (seq[k] == 'T') seq[k] = 'U'; /* DNA letters fold as RNA (as RNAfold's input filter does); unpinned */
     S[k + 1] = (short)encode_base(seq_in[k]);
   }
   seq[n] = 0;
@@ -675,6 +676,7 @@ int orc_eval_structure(const orc_params *P, const char *seq_in, int n, const cha
   int sp = 0, err = 0;
   for (int k = 0; k < n; k++) {
     seq[k] = (char)toupper((unsigned char)seq_in[k]);
+    if (seq[k] == 'T') seq[k] = 'U'; /* DNA letters fold as RNA (as RNAfold's input filter does); unpinned */
     S[k + 1] = (short)encode_base(seq_in[k]);
   }
   seq[n] = 0;
@@ -733,6 +735,7 @@ int orc_bruteforce_mfe(const orc_params *P, const char *seq_in, int n, int *mfe_
   int pt[34] = {0}, open[34];
   for (int k = 0; k < n; k++) {
     seq[k] = (char)toupper((unsigned char)seq_in[k]);
+    if (seq[k] == 'T') seq[k] = 'U'; /* DNA letters fold as RNA (as RNAfold's input filter does); unpinned */
     S[k + 1] = (short)encode_base(seq_in[k]);
   }
   seq[n] = 0;

@@ -1,0 +1,12 @@
+"""rnagent_b200 -- B200-native reward hot path of RLIF (andriusbern/RNAgent).
+
+Batched Zuker MFE folding + dot-bracket Hamming distance behind the reference's own call
+signatures.  Import is cheap and GPU-free; the first fold binds the CUDA library
+(rnagent_b200/librnafold_b200.so) and raises if it, or a B200, is missing.
+"""
+from .utils import hamming_distance
+from .vienna import (PARAM_FILES, PARAMETERS, config_vienna, cvar, fold, fold_batch, fold_hamming_batch,
+                     read_parameter_file, set_vienna_params)
+
+__all__ = ["fold", "fold_batch", "fold_hamming_batch", "read_parameter_file", "set_vienna_params",
+           "config_vienna", "cvar", "hamming_distance", "PARAMETERS", "PARAM_FILES"]

@@ -1,0 +1,528 @@
+// capi.cu -- C ABI (include/rnafold_b200.h) over the CUDA kernels: context, parameter upload,
+// host/device buffer handling, length bucketing and kernel routing.
+//
+// Product code.  There is no CPU fold path in this library: every fold runs on the device, and
+// every entry point fails with RNAFOLD_ECUDA when no usable device is present.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "../../include/rnafold_b200.h"
+#include "fold_kernels.h"
+#include "fold_params.h"
+
+extern "C" const char rnafold_builtin_turner2004[];  // builtin_params.cpp (generated at build time)
+extern "C" const unsigned long rnafold_builtin_turner2004_len;
+
+namespace {
+
+using namespace rnafold;
+
+thread_local std::string g_err;
+int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  std::vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                              \
+  do {                                                                                              \
+    cudaError_t e_ = (expr);                                                                        \
+    if (e_ != cudaSuccess) return fail(RNAFOLD_ECUDA, "%s: %s", #expr, cudaGetErrorString(e_));     \
+  } while (0)
+
+// grow-only device / pinned buffers
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    want += want / 4;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+struct PinBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    want += want / 4;
+    cudaError_t e = cudaMallocHost(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct Context {
+  int device = -1;
+  int num_sms = 0;
+  int max_smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  HostParams hp;
+  FoldParams *d_params = nullptr;
+  // model details (RNA.cvar)
+  double md_temperature = 37.0, md_dangles = 2, md_noGU = 0, md_no_closingGU = 0, md_uniq_ML = 0;
+  // device staging for host-side callers
+  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws;
+  PinBuf h_in, h_out, h_off;
+  std::vector<int32_t> off_host, order_host;
+  int32_t last_launches = 0, last_routed[3] = {0, 0, 0};
+  bool timed = false;
+};
+
+Context *g_ctx = nullptr;
+std::mutex g_mu;
+
+bool is_device_ptr(const void *p) {
+  if (!p) return false;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+int upload_params(Context *c) {
+  CUDA_TRY(cudaMemcpyAsync(c->d_params, &c->hp.dev, sizeof(FoldParams), cudaMemcpyHostToDevice, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return RNAFOLD_OK;
+}
+
+void init_host_params(HostParams *hp) {
+  std::memset(hp, 0, sizeof(*hp));
+  hp->lxc = 107.856;
+  hp->dev.s.max_ninio = 300;
+}
+
+// Length classes of the shared-memory kernel: a launch is sized (shared memory, hence CTAs/SM)
+// by the longest sequence in it, so mixed batches are split into classes.
+const int kSmemClasses[] = {40, 64, 80, 100, 128, 160, 200, 232};
+
+struct Launch {
+  int begin, end;  // slice of the length-sorted order
+  int nmax;
+  bool smem;
+};
+
+int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target,
+              uint8_t *db_out, int32_t *mfe_out, int32_t *hd_out, double *reward_out,
+              uint8_t *mismatch_out, double reward_exp, void *stream_v) {
+  if (B < 0 || !off || (B > 0 && !seq)) return fail(RNAFOLD_EINVAL, "null seq/off or negative batch size");
+  c->last_launches = 0;
+  c->last_routed[0] = c->last_routed[1] = c->last_routed[2] = 0;
+  if (B == 0) return RNAFOLD_OK;
+  CUDA_TRY(cudaSetDevice(c->device));
+
+  const bool off_dev = is_device_ptr(off);
+  const bool seq_dev = is_device_ptr(seq);
+  const bool tgt_dev = is_device_ptr(target);
+  const bool any_host_out = (db_out && !is_device_ptr(db_out)) || (mfe_out && !is_device_ptr(mfe_out)) ||
+                            (hd_out && !is_device_ptr(hd_out)) || (reward_out && !is_device_ptr(reward_out)) ||
+                            (mismatch_out && !is_device_ptr(mismatch_out));
+  cudaStream_t st = stream_v ? (cudaStream_t)stream_v : c->stream;
+
+  // offsets on the host (needed for routing)
+  c->off_host.resize((size_t)B + 1);
+  if (off_dev) {
+    CUDA_TRY(cudaMemcpyAsync(c->off_host.data(), off, sizeof(int32_t) * ((size_t)B + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+  } else {
+    std::memcpy(c->off_host.data(), off, sizeof(int32_t) * ((size_t)B + 1));
+  }
+  const int32_t *oh = c->off_host.data();
+  if (oh[0] != 0) return fail(RNAFOLD_EINVAL, "off[0] must be 0");
+  int nmax_all = 0;
+  for (int b = 0; b < B; ++b) {
+    const int n = oh[b + 1] - oh[b];
+    if (n < 0 || n > RNAFOLD_MAX_LEN) return fail(RNAFOLD_EINVAL, "sequence %d has length %d (limit %d)", b, n, RNAFOLD_MAX_LEN);
+    nmax_all = std::max(nmax_all, n);
+  }
+  const size_t total = (size_t)oh[B];
+
+  // processing order: longest first (cubic cost), stable
+  c->order_host.resize((size_t)B);
+  std::iota(c->order_host.begin(), c->order_host.end(), 0);
+  std::stable_sort(c->order_host.begin(), c->order_host.end(),
+                   [&](int x, int y) { return oh[x + 1] - oh[x] > oh[y + 1] - oh[y]; });
+  auto len_at = [&](int k) { return oh[c->order_host[k] + 1] - oh[c->order_host[k]]; };
+
+  // split into launches
+  std::vector<Launch> launches;
+  {
+    int k = 0;
+    const int smem_limit = kSmemClasses[sizeof(kSmemClasses) / sizeof(int) - 1];
+    while (k < B && len_at(k) > smem_limit) ++k;
+    if (k > 0) launches.push_back(Launch{0, k, len_at(0), false});
+    const int ncls = (int)(sizeof(kSmemClasses) / sizeof(int));
+    for (int cls = ncls - 1; cls >= 0 && k < B; --cls) {
+      const int lo = cls > 0 ? kSmemClasses[cls - 1] : -1;
+      int e = k;
+      while (e < B && len_at(e) > lo) ++e;
+      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), true});
+      k = e;
+    }
+  }
+
+  // ---- device views of the inputs
+  const uint8_t *d_seq = seq;
+  const int32_t *d_off = off;
+  const uint8_t *d_target = target;
+  if (!seq_dev) {
+    CUDA_TRY(c->d_seq.reserve(total + 16));
+    CUDA_TRY(c->h_in.reserve(2 * total + 32));
+    std::memcpy(c->h_in.p, seq, total);
+    CUDA_TRY(cudaMemcpyAsync(c->d_seq.p, c->h_in.p, total, cudaMemcpyHostToDevice, st));
+    d_seq = (const uint8_t *)c->d_seq.p;
+  }
+  if (target && !tgt_dev) {
+    CUDA_TRY(c->d_target.reserve(total + 16));
+    CUDA_TRY(c->h_in.reserve(2 * total + 32));
+    uint8_t *stage = (uint8_t *)c->h_in.p + total + 16;
+    std::memcpy(stage, target, total);
+    CUDA_TRY(cudaMemcpyAsync(c->d_target.p, stage, total, cudaMemcpyHostToDevice, st));
+    d_target = (const uint8_t *)c->d_target.p;
+  }
+  {
+    // offsets + order travel together from one pinned block
+    CUDA_TRY(c->h_off.reserve(sizeof(int32_t) * (2 * (size_t)B + 2)));
+    int32_t *ho = (int32_t *)c->h_off.p;
+    std::memcpy(ho, oh, sizeof(int32_t) * ((size_t)B + 1));
+    std::memcpy(ho + B + 1, c->order_host.data(), sizeof(int32_t) * (size_t)B);
+    CUDA_TRY(c->d_order.reserve(sizeof(int32_t) * (2 * (size_t)B + 2)));
+    CUDA_TRY(cudaMemcpyAsync(c->d_order.p, ho, sizeof(int32_t) * (2 * (size_t)B + 1), cudaMemcpyHostToDevice, st));
+    if (!off_dev) d_off = (const int32_t *)c->d_order.p;
+  }
+  const int32_t *d_order = (const int32_t *)c->d_order.p + B + 1;
+
+  // ---- device views of the outputs
+  auto out_view = [&](void *user, DevBuf &buf, size_t bytes, void **dev) -> cudaError_t {
+    if (!user) {
+      *dev = nullptr;
+      return cudaSuccess;
+    }
+    if (is_device_ptr(user)) {
+      *dev = user;
+      return cudaSuccess;
+    }
+    cudaError_t e = buf.reserve(bytes);
+    *dev = buf.p;
+    return e;
+  };
+  void *v_db, *v_mfe, *v_hd, *v_rw, *v_mm;
+  CUDA_TRY(out_view(db_out, c->d_db, total + 16, &v_db));
+  CUDA_TRY(out_view(mfe_out, c->d_mfe, sizeof(int32_t) * (size_t)B, &v_mfe));
+  CUDA_TRY(out_view(target ? hd_out : nullptr, c->d_hd, sizeof(int32_t) * (size_t)B, &v_hd));
+  CUDA_TRY(out_view(target ? reward_out : nullptr, c->d_reward, sizeof(double) * (size_t)B, &v_rw));
+  CUDA_TRY(out_view(target ? mismatch_out : nullptr, c->d_mismatch, total + 16, &v_mm));
+
+  // ---- control words: one queue counter per launch + status
+  const int nl = (int)launches.size();
+  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(nl + 1)));
+  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)(nl + 1), st));
+  int32_t *d_ctl = (int32_t *)c->d_ctl.p;
+
+  if (c->timed) CUDA_TRY(cudaEventRecord(c->ev0, st));
+  for (int li = 0; li < nl; ++li) {
+    const Launch &L = launches[li];
+    const int count = L.end - L.begin;
+    BatchArgs a;
+    a.seq = d_seq;
+    a.off = d_off;
+    a.order = d_order + L.begin;
+    a.B = count;
+    a.target = d_target;
+    a.db = (uint8_t *)v_db;
+    a.mfe = (int32_t *)v_mfe;
+    a.hd = (int32_t *)v_hd;
+    a.reward = (double *)v_rw;
+    a.mismatch = (uint8_t *)v_mm;
+    a.reward_exp = reward_exp;
+    a.status = d_ctl + nl;
+    const int occ = std::max(1, cta_kernel_occupancy(L.nmax, L.smem));
+    const int grid = std::min(count, c->num_sms * occ);
+    int *ws = nullptr;
+    long long stride = 0;
+    if (!L.smem) {
+      stride = 2LL * table_cells(L.nmax);
+      CUDA_TRY(c->d_ws.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
+      ws = (int *)c->d_ws.p;
+    }
+    CUDA_TRY(launch_fold_cta(c->d_params, a, L.nmax, L.smem, grid, ws, stride, d_ctl + li, st));
+    c->last_launches++;
+    c->last_routed[L.smem ? 0 : 2] += count;
+  }
+  if (c->timed) CUDA_TRY(cudaEventRecord(c->ev1, st));
+
+  // ---- copy back for host-side callers
+  if (any_host_out) {
+    size_t need = 0;
+    auto slot = [&](void *user, size_t bytes) -> size_t {
+      if (!user || is_device_ptr(user)) return 0;
+      size_t o = need;
+      need += (bytes + 15) / 16 * 16;
+      return o;
+    };
+    const size_t o_db = slot(db_out, total), o_mfe = slot(mfe_out, 4 * (size_t)B),
+                 o_hd = slot(target ? hd_out : nullptr, 4 * (size_t)B),
+                 o_rw = slot(target ? reward_out : nullptr, 8 * (size_t)B),
+                 o_mm = slot(target ? mismatch_out : nullptr, total);
+    CUDA_TRY(c->h_out.reserve(need + 16));
+    uint8_t *ho = (uint8_t *)c->h_out.p;
+    auto back = [&](void *user, void *dev, size_t off_b, size_t bytes) -> cudaError_t {
+      if (!user || is_device_ptr(user) || bytes == 0) return cudaSuccess;
+      return cudaMemcpyAsync(ho + off_b, dev, bytes, cudaMemcpyDeviceToHost, st);
+    };
+    CUDA_TRY(back(db_out, v_db, o_db, total));
+    CUDA_TRY(back(mfe_out, v_mfe, o_mfe, 4 * (size_t)B));
+    CUDA_TRY(back(target ? hd_out : nullptr, v_hd, o_hd, 4 * (size_t)B));
+    CUDA_TRY(back(target ? reward_out : nullptr, v_rw, o_rw, 8 * (size_t)B));
+    CUDA_TRY(back(target ? mismatch_out : nullptr, v_mm, o_mm, total));
+    int32_t status = 0;
+    CUDA_TRY(cudaMemcpyAsync(&status, d_ctl + nl, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    auto fin = [&](void *user, size_t off_b, size_t bytes) {
+      if (user && !is_device_ptr(user) && bytes) std::memcpy(user, ho + off_b, bytes);
+    };
+    fin(db_out, o_db, total);
+    fin(mfe_out, o_mfe, 4 * (size_t)B);
+    fin(target ? hd_out : nullptr, o_hd, 4 * (size_t)B);
+    fin(target ? reward_out : nullptr, o_rw, 8 * (size_t)B);
+    fin(target ? mismatch_out : nullptr, o_mm, total);
+    if (status) return fail(RNAFOLD_ECUDA, "backtrack found no decomposition (code %d)", status);
+  } else if (!seq_dev || (target && !tgt_dev) || !off_dev) {
+    // pinned staging buffers are reused by the next call
+    CUDA_TRY(cudaStreamSynchronize(st));
+  }
+  return RNAFOLD_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *rnafold_last_error(void) { return g_err.c_str(); }
+const char *rnafold_version(void) { return "rnafold_b200 0.1 (sm_100a)"; }
+
+int rnafold_init(int device) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (g_ctx && g_ctx->device == device) return RNAFOLD_OK;
+  if (g_ctx) return fail(RNAFOLD_EINVAL, "context already bound to device %d", g_ctx->device);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(RNAFOLD_ECUDA, "no CUDA device available (%s); this library has no CPU path",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(RNAFOLD_EINVAL, "device %d out of range (0..%d)", device, ndev - 1);
+  CUDA_TRY(cudaSetDevice(device));
+  Context *c = new Context();
+  c->device = device;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    delete c;
+    return fail(RNAFOLD_ECUDA, "device %d is sm_%d%d; this build targets sm_100a (B200)", device, prop.major, prop.minor);
+  }
+  c->num_sms = prop.multiProcessorCount;
+  c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+  CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreate(&c->ev0));
+  CUDA_TRY(cudaEventCreate(&c->ev1));
+  CUDA_TRY(cudaMalloc((void **)&c->d_params, sizeof(FoldParams)));
+  init_host_params(&c->hp);
+  char err[256] = "";
+  if (parse_parameter_text(rnafold_builtin_turner2004, (size_t)rnafold_builtin_turner2004_len, &c->hp, err, sizeof(err))) {
+    delete c;
+    return fail(RNAFOLD_EIO, "built-in Turner 2004 parameters: %s", err);
+  }
+  int rc = upload_params(c);
+  if (rc) {
+    delete c;
+    return rc;
+  }
+  g_ctx = c;
+  return RNAFOLD_OK;
+}
+
+void rnafold_shutdown(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  Context *c = g_ctx;
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (DevBuf *b : {&c->d_seq, &c->d_off, &c->d_order, &c->d_target, &c->d_db, &c->d_mfe, &c->d_hd,
+                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws})
+    b->release();
+  for (PinBuf *b : {&c->h_in, &c->h_out, &c->h_off}) b->release();
+  cudaFree(c->d_params);
+  cudaEventDestroy(c->ev0);
+  cudaEventDestroy(c->ev1);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  g_ctx = nullptr;
+}
+
+int rnafold_read_parameter_file(const char *path) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (!path) return fail(RNAFOLD_EINVAL, "null path");
+  HostParams *hp = new HostParams(g_ctx->hp);  // absent sections keep the live values
+  char err[256] = "";
+  if (load_parameter_file(path, hp, err, sizeof(err))) {
+    delete hp;
+    return fail(RNAFOLD_EIO, "%s", err);
+  }
+  g_ctx->hp = *hp;
+  delete hp;
+  CUDA_TRY(cudaSetDevice(g_ctx->device));
+  return upload_params(g_ctx);
+}
+
+int rnafold_export_params(int32_t *out, int cap) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  int n = export_params(&g_ctx->hp, out, cap);
+  if (n < 0) return fail(RNAFOLD_EINVAL, "export buffer too small");
+  return n;
+}
+
+int rnafold_parse_params(const char *path, int32_t *out, int cap) {
+  // host-only: parse `path` (NULL = the built-in Turner 2004 text) and dump the tables; no device needed
+  HostParams *hp = new HostParams();
+  init_host_params(hp);
+  char err[256] = "";
+  int rc = parse_parameter_text(rnafold_builtin_turner2004, (size_t)rnafold_builtin_turner2004_len, hp, err, sizeof(err));
+  if (!rc && path) rc = load_parameter_file(path, hp, err, sizeof(err));
+  if (rc) {
+    delete hp;
+    return fail(RNAFOLD_EIO, "%s", err);
+  }
+  int n = export_params(hp, out, cap);
+  delete hp;
+  if (n < 0) return fail(RNAFOLD_EINVAL, "export buffer too small");
+  return n;
+}
+
+static double *md_slot(Context *c, const char *name, double *dflt) {
+  struct {
+    const char *n;
+    double *p;
+    double d;
+  } tab[] = {{"temperature", &c->md_temperature, 37.0}, {"dangles", &c->md_dangles, 2.0},
+             {"noGU", &c->md_noGU, 0.0},                {"no_closingGU", &c->md_no_closingGU, 0.0},
+             {"uniq_ML", &c->md_uniq_ML, 0.0}};
+  for (auto &t : tab)
+    if (!std::strcmp(t.n, name)) {
+      *dflt = t.d;
+      return t.p;
+    }
+  return nullptr;
+}
+
+int rnafold_set_md(const char *name, double value) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  double dflt = 0;
+  double *p = name ? md_slot(g_ctx, name, &dflt) : nullptr;
+  if (!p) return fail(RNAFOLD_EINVAL, "unknown model detail '%s'", name ? name : "(null)");
+  if (value != dflt)
+    return fail(RNAFOLD_ENOTSUP, "model detail %s=%g is not implemented (only the reference default %g)", name, value, dflt);
+  *p = value;
+  return RNAFOLD_OK;
+}
+
+int rnafold_get_md(const char *name, double *value) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  double dflt = 0;
+  double *p = name ? md_slot(g_ctx, name, &dflt) : nullptr;
+  if (!p || !value) return fail(RNAFOLD_EINVAL, "unknown model detail");
+  *value = *p;
+  return RNAFOLD_OK;
+}
+
+int rnafold_workspace_bytes(int32_t B, int32_t nmax, size_t *bytes) {
+  if (!bytes || B < 0 || nmax < 0 || nmax > RNAFOLD_MAX_LEN) return fail(RNAFOLD_EINVAL, "bad arguments");
+  const int smem_limit = kSmemClasses[sizeof(kSmemClasses) / sizeof(int) - 1];
+  size_t ws = 0;
+  if (nmax > smem_limit) {
+    const int sms = g_ctx ? g_ctx->num_sms : 148;
+    ws = sizeof(int32_t) * 2 * (size_t)table_cells(nmax) * (size_t)std::min<long long>(B, 8LL * sms);
+  }
+  *bytes = ws + (size_t)B * (size_t)nmax * 3 + (size_t)B * 32;
+  return RNAFOLD_OK;
+}
+
+int rnafold_fold_hamming_batch(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target,
+                               uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out, double *reward_out,
+                               uint8_t *mismatch_out, double reward_exp, void *stream) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  return run_batch(g_ctx, seq, off, B, target, db_out, mfe_dcal_out, hd_out, reward_out, mismatch_out,
+                   reward_exp, stream);
+}
+
+int rnafold_fold_batch(const uint8_t *seq, const int32_t *off, int32_t B, uint8_t *db_out,
+                       int32_t *mfe_dcal_out, void *stream) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  return run_batch(g_ctx, seq, off, B, nullptr, db_out, mfe_dcal_out, nullptr, nullptr, nullptr, 1.0, stream);
+}
+
+int rnafold_last_launch_info(int32_t *launches, int32_t routed[3]) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (launches) *launches = g_ctx->last_launches;
+  if (routed) std::memcpy(routed, g_ctx->last_routed, sizeof(g_ctx->last_routed));
+  return RNAFOLD_OK;
+}
+
+int rnafold_set_timing(int enabled) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  g_ctx->timed = enabled != 0;
+  return RNAFOLD_OK;
+}
+
+int rnafold_last_kernel_ms(float *ms) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (!ms || !g_ctx->timed) return fail(RNAFOLD_EINVAL, "timing not enabled (rnafold_set_timing)");
+  CUDA_TRY(cudaEventSynchronize(g_ctx->ev1));
+  CUDA_TRY(cudaEventElapsedTime(ms, g_ctx->ev0, g_ctx->ev1));
+  return RNAFOLD_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,36 @@
+// fold_kernels.h -- launch interface between the C ABI (capi.cu) and the CUDA kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "fold_params.h"
+
+namespace rnafold {
+
+constexpr int kCtaThreads = 128;
+
+// Cells of the diagonal-major triangle (diagonals 4..n-1) of one DP table.
+__host__ __device__ inline int table_cells(int n) { return n > 4 ? ((n - 4) * (n - 3)) / 2 : 0; }
+
+// Device pointers of one batch (CSR layout, see include/rnafold_b200.h).
+struct BatchArgs {
+  const uint8_t *seq;
+  const int32_t *off;
+  const int32_t *order;  // processing order (longest first) or nullptr
+  int32_t B;
+  const uint8_t *target;  // nullptr: fold only
+  uint8_t *db;
+  int32_t *mfe;
+  int32_t *hd;
+  double *reward;
+  uint8_t *mismatch;
+  double reward_exp;
+  int32_t *status;  // set non-zero by a CTA whose backtrack found no decomposition
+};
+
+size_t cta_kernel_smem_bytes(int nmax, bool tables_in_smem);
+int cta_kernel_occupancy(int nmax, bool tables_in_smem);
+cudaError_t launch_fold_cta(const FoldParams *gp, const BatchArgs &a, int nmax, bool tables_in_smem,
+                            int grid, int *gws, long long ws_stride, int *queue, cudaStream_t st);
+
+}  // namespace rnafold

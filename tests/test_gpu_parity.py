@@ -1,0 +1,128 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle (bit-exact)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_batch(rng, B, nlo, nhi, alphabet="ACGU"):
+    lens = rng.integers(nlo, nhi + 1, B)
+    return ["".join(rng.choice(list(alphabet), int(n))) for n in lens]
+
+
+def _oracle_batch(P, seqs, targets=None):
+    buf = np.frombuffer("".join(seqs).encode(), dtype=np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int32)
+    t = np.frombuffer("".join(targets).encode(), dtype=np.uint8) if targets else None
+    db, mfe, hd = P.fold_batch(buf, off, targets_u8=t, nthreads=0)
+    raw = db.tobytes().decode()
+    return [raw[off[k]:off[k + 1]] for k in range(len(seqs))], mfe, hd
+
+
+@pytest.fixture(scope="module")
+def engine():
+    import rnagent_b200
+    from rnagent_b200 import _lib
+    _lib.lib()
+    yield rnagent_b200
+    rnagent_b200.set_vienna_params(1)
+
+
+def _check(engine, P, seqs):
+    from rnagent_b200 import _lib
+    from rnagent_b200.vienna import pack, unpack
+    buf, off = pack(seqs)
+    db = np.zeros_like(buf)
+    mfe = np.zeros(len(seqs), dtype=np.int32)
+    _lib.fold_hamming_raw(buf, off, len(seqs), db=db, mfe=mfe)
+    got = unpack(db, off)
+    want, wmfe, _ = _oracle_batch(P, seqs)
+    bad = [k for k in range(len(seqs)) if got[k] != want[k] or mfe[k] != wmfe[k]]
+    assert not bad, (len(bad), seqs[bad[0]], got[bad[0]], want[bad[0]], int(mfe[bad[0]]), int(wmfe[bad[0]]))
+
+
+def test_golden_rows_both_parameter_sets(engine, golden_rows, golden_folds):
+    from rnagent_b200 import _lib
+    from rnagent_b200.vienna import pack, unpack
+    for setno, name in ((1, "turner2004"), (2, "turner1999")):
+        engine.set_vienna_params(setno)
+        idx = [k for k, r in enumerate(golden_rows) if r["params"] == name]
+        seqs = [golden_rows[k]["seq"] for k in idx]
+        tgts = [golden_rows[k]["target"] for k in idx]
+        structs, mfe, hd, mism, reward = engine.fold_hamming_batch(seqs, tgts, reward_exp=9)
+        for n, k in enumerate(idx):
+            s, e = golden_folds[k]
+            assert structs[n] == s and int(round(float(mfe[n]) * 100)) == e, golden_rows[k]["line"]
+            want_hd = sum(a != b for a, b in zip(s, tgts[n]))
+            assert hd[n] == want_hd and len(mism[n]) == want_hd
+            r = (1 - want_hd / len(s)) ** 9 + (0.25 if want_hd == 0 else 0)
+            assert abs(reward[n] - r) < 1e-12
+        launches, routed = _lib.last_launch_info()
+        assert launches >= 2 and routed[0] > 0 and routed[2] > 0   # both kernel families exercised
+    engine.set_vienna_params(1)
+
+
+@pytest.mark.parametrize("setno,name", [(1, "turner2004"), (2, "turner1999"), (3, "andronescu2007")])
+def test_random_short(engine, oracle_params, setno, name):
+    engine.set_vienna_params(setno)
+    rng = np.random.default_rng(100 + setno)
+    _check(engine, oracle_params(name), _rand_batch(rng, 3000, 0, 120))
+
+
+def test_random_n100_block(engine, oracle_params):
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(100)
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 4096, 100, 100))
+
+
+def test_random_long_global_kernel(engine, oracle_params):
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(400)
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 96, 233, 460))
+
+
+def test_biased_composition_and_unknown_letters(engine, oracle_params):
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(5)
+    P = oracle_params("turner2004")
+    _check(engine, P, _rand_batch(rng, 1500, 20, 140, alphabet="GC"))      # deep stems, many ties
+    _check(engine, P, _rand_batch(rng, 1500, 20, 140, alphabet="GGCCAU"))
+    _check(engine, P, _rand_batch(rng, 1500, 20, 140, alphabet="ACGUN"))   # unpairable letters
+    _check(engine, P, _rand_batch(rng, 500, 20, 140, alphabet="acgut"))
+
+
+def test_fold_signature_and_edge_cases(engine):
+    engine.set_vienna_params(1)
+    s, e = engine.fold("GCAAAAAAAAAUUUGC")
+    assert s == "(((((......)))))" and e == float(np.float32(-2.2))
+    assert engine.fold("") == ("", 0.0)
+    assert engine.fold("ACGU") == ("....", 0.0)
+    structs, mfe = engine.fold_batch([])
+    assert structs == [] and len(mfe) == 0
+    with pytest.raises(NotImplementedError):
+        engine.cvar.dangles = 0
+    engine.cvar.dangles = 2
+    assert engine.cvar.dangles == 2
+    with pytest.raises(ValueError):
+        engine.fold("A" * 5000)
+
+
+def test_device_buffers_async(engine, oracle_params):
+    import torch
+    from rnagent_b200 import _lib
+    from rnagent_b200.vienna import pack, unpack
+    rng = np.random.default_rng(11)
+    seqs = _rand_batch(rng, 2048, 60, 100)
+    buf, off = pack(seqs)
+    dev = torch.device("cuda", _lib.device_index())
+    d_seq = torch.from_numpy(buf).to(dev)
+    d_off = torch.from_numpy(off).to(dev)
+    d_db = torch.zeros_like(d_seq)
+    d_mfe = torch.zeros(len(seqs), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    st = torch.cuda.Stream(device=dev)
+    _lib.fold_hamming_raw(d_seq, d_off, len(seqs), db=d_db, mfe=d_mfe, stream=st.cuda_stream)
+    st.synchronize()
+    want, wmfe, _ = _oracle_batch(oracle_params("turner2004"), seqs)
+    assert unpack(d_db.cpu().numpy(), off) == want
+    assert np.array_equal(d_mfe.cpu().numpy(), wmfe)

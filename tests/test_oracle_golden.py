@@ -1,0 +1,96 @@
+"""Pins the CPU oracle against every known answer the reference ships for RNA.fold.
+
+The reference has no assertions of its own; its committed logs
+rlif/logs/*/solutions*.csv hold (sequence, HD-to-target, MFE) rows written by
+rlif/utils/comparison.py:225-233 from `RNA.fold`.  tools/make_golden.py extracted them.
+"""
+import collections
+
+import numpy as np
+import pytest
+
+import oracle
+
+
+def _fe_matches(e_dcal, fe_text):
+    # logged with '{:.3f}' then possibly shortened by a spreadsheet ("-22" for "-22.000")
+    return abs(round(oracle.mfe_float(e_dcal), 3) - float(fe_text)) < 5e-4
+
+
+def test_worked_examples(oracle_params):
+    # hand-computed from the .par text, valid under both Turner sets
+    for name in ("turner2004", "turner1999"):
+        P = oracle_params(name)
+        assert P.fold_dcal("GCAAAAAAAAAUUUGC") == ("(((((......)))))", -220)
+        assert P.fold_dcal("GCAGAAAAAAAUCUGC") == ("(((((......)))))", -490)
+    assert oracle_params("turner2004").fold("GCAAAAAAAAAUUUGC")[1] == float(np.float32(-2.2))
+
+
+def test_every_logged_energy(golden_rows, golden_folds):
+    bad = [(r["file"], r["line"]) for r, (_, e) in zip(golden_rows, golden_folds) if not _fe_matches(e, r["fe"])]
+    assert len(golden_rows) == 1726
+    assert not bad, bad[:10]
+
+
+def test_logged_structures_and_hd(golden_rows, golden_folds):
+    """HD of our fold to the target equals the logged HD; for HD=0 rows the whole structure is pinned
+    (this is what pins the backtrack's tie-breaking order)."""
+    stats = collections.Counter()
+    bad = []
+    for r, (s, _) in zip(golden_rows, golden_folds):
+        hd = sum(a != b for a, b in zip(s, r["target"]))
+        ok = hd == r["hd"]
+        stats[(r["params"], ok)] += 1
+        if not ok:
+            bad.append(r)
+    # every Turner 1999 row (700, all sources, lengths 34..451) matches
+    assert stats[("turner1999", False)] == 0 and stats[("turner1999", True)] == 700
+    # Turner 2004: the only misses are 29 rows from sources whose HD is not reproducible under any
+    # parameter set (see conftest.HD_UNPINNED_SOURCES); every RNAinverse/MODENA/NUPACK/antaRNA/rnaMCTS
+    # row matches.
+    assert all(r["source"] in ("rlfold", "mrlfold", "LEARNA") for r in bad), [r["source"] for r in bad]
+    assert len(bad) == 29
+    full = sum(1 for r in golden_rows if r["hd"] == 0 and r not in bad)
+    assert full >= 1090
+
+
+def test_eval_of_own_structure_equals_mfe(golden_rows, golden_folds, oracle_params):
+    for r, (s, e) in zip(golden_rows, golden_folds):
+        P = oracle_params(r["params"])
+        assert P.eval_structure(r["seq"], s) == e
+
+
+def test_bruteforce_small(oracle_params):
+    rng = np.random.default_rng(7)
+    for name in ("turner2004", "turner1999"):
+        P = oracle_params(name)
+        for _ in range(60):
+            n = int(rng.integers(5, 15))
+            seq = "".join(rng.choice(list("ACGU"), n))
+            s, e = P.fold_dcal(seq)
+            assert P.bruteforce_mfe(seq) == e, seq
+            assert P.eval_structure(seq, s) == e
+
+
+def test_edge_cases(oracle_params):
+    P = oracle_params("turner2004")
+    assert P.fold_dcal("") == ("", 0)
+    assert P.fold_dcal("ACGU") == ("....", 0)
+    assert P.fold_dcal("NNNNNNNNNNNN") == ("." * 12, 0)
+    s, e = P.fold_dcal("GGGGAAAACCCC")
+    assert s == "((((....))))" and e < 0
+    assert P.fold_dcal("ggggaaaacccc") == (s, e)       # case-insensitive encoding
+    assert P.fold_dcal("GGGGAAAACCCC".replace("U", "T"))[1] == e
+
+
+def test_batch_matches_single(oracle_params):
+    P = oracle_params("turner2004")
+    rng = np.random.default_rng(3)
+    seqs = ["".join(rng.choice(list("ACGU"), int(n))) for n in rng.integers(0, 90, 40)]
+    buf = np.frombuffer("".join(seqs).encode(), dtype=np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int32)
+    db, mfe, hd = P.fold_batch(buf, off, targets_u8=np.full_like(buf, ord(".")), nthreads=2)
+    for k, s in enumerate(seqs):
+        st, e = P.fold_dcal(s)
+        assert db[off[k]:off[k + 1]].tobytes().decode() == st and mfe[k] == e
+        assert hd[k] == len(s) - st.count(".")
