@@ -97,6 +97,14 @@ int rnafold_set_timing(int enabled);
  * the kernels were launched on (synchronises the stream). */
 int rnafold_last_kernel_ms(float *ms);
 
+/* Measurement helper (bench.py): on-box peaks of the two on-chip resources that bound the fold DP,
+ * whole device: conflict-free 4-byte shared-memory loads per second and integer add+min
+ * (min-plus candidate) updates per second. */
+int rnafold_measure_onchip_peaks(double *lds_per_s, double *minplus_per_s);
+
+/* SM count and opt-in shared memory per CTA of the bound device. */
+int rnafold_device_info(int32_t *num_sms, int32_t *smem_optin_bytes);
+
 #ifdef __cplusplus
 }
 #endif

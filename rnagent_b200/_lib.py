@@ -17,6 +17,7 @@ EXPORTS = [
     "rnafold_read_parameter_file", "rnafold_export_params", "rnafold_parse_params", "rnafold_set_md", "rnafold_get_md",
     "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch",
     "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
+    "rnafold_measure_onchip_peaks", "rnafold_device_info",
 ]
 
 _lock = threading.Lock()
@@ -54,6 +55,8 @@ def load_library():
         L.rnafold_last_launch_info.argtypes = [ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
         L.rnafold_set_timing.argtypes = [ci]
         L.rnafold_last_kernel_ms.argtypes = [ctypes.POINTER(ctypes.c_float)]
+        L.rnafold_measure_onchip_peaks.argtypes = [ctypes.POINTER(cd), ctypes.POINTER(cd)]
+        L.rnafold_device_info.argtypes = [ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
         _cdll = L
         return L
 
@@ -126,6 +129,19 @@ def last_kernel_ms():
     ms = ctypes.c_float(0)
     check(lib().rnafold_last_kernel_ms(ctypes.byref(ms)))
     return ms.value
+
+
+def measure_onchip_peaks():
+    """(4-byte shared loads per second, min-plus updates per second) measured on the bound device."""
+    a, b = ctypes.c_double(0), ctypes.c_double(0)
+    check(lib().rnafold_measure_onchip_peaks(ctypes.byref(a), ctypes.byref(b)))
+    return a.value, b.value
+
+
+def device_info():
+    a, b = ctypes.c_int32(0), ctypes.c_int32(0)
+    check(lib().rnafold_device_info(ctypes.byref(a), ctypes.byref(b)))
+    return a.value, b.value
 
 
 def export_params():

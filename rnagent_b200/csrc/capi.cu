@@ -525,4 +525,21 @@ int rnafold_last_kernel_ms(float *ms) {
   return RNAFOLD_OK;
 }
 
+int rnafold_measure_onchip_peaks(double *lds_per_s, double *minplus_per_s) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (!lds_per_s || !minplus_per_s) return fail(RNAFOLD_EINVAL, "null output");
+  CUDA_TRY(cudaSetDevice(g_ctx->device));
+  CUDA_TRY(measure_onchip_peaks(g_ctx->num_sms, g_ctx->stream, lds_per_s, minplus_per_s));
+  return RNAFOLD_OK;
+}
+
+int rnafold_device_info(int32_t *num_sms, int32_t *smem_optin_bytes) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (num_sms) *num_sms = g_ctx->num_sms;
+  if (smem_optin_bytes) *smem_optin_bytes = g_ctx->max_smem_optin;
+  return RNAFOLD_OK;
+}
+
 }  // extern "C"

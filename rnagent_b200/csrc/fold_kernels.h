@@ -33,4 +33,7 @@ int cta_kernel_occupancy(int nmax, bool tables_in_smem);
 cudaError_t launch_fold_cta(const FoldParams *gp, const BatchArgs &a, int nmax, bool tables_in_smem,
                             int grid, int *gws, long long ws_stride, int *queue, cudaStream_t st);
 
+// peaks.cu: on-box shared-memory-load and min-plus (ALU) peak rates, whole device, per second
+cudaError_t measure_onchip_peaks(int num_sms, cudaStream_t st, double *lds_per_s, double *minplus_per_s);
+
 }  // namespace rnafold
