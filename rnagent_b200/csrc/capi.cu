@@ -95,7 +95,7 @@ struct Context {
   // model details (RNA.cvar)
   double md_temperature = 37.0, md_dangles = 2, md_noGU = 0, md_no_closingGU = 0, md_uniq_ML = 0;
   // device staging for host-side callers
-  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws;
+  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws, d_redo;
   PinBuf h_in, h_out, h_off;
   std::vector<int32_t> off_host, order_host;
   int32_t last_launches = 0, last_routed[3] = {0, 0, 0};
@@ -117,6 +117,7 @@ bool is_device_ptr(const void *p) {
 
 int upload_params(Context *c) {
   CUDA_TRY(cudaMemcpyAsync(c->d_params, &c->hp.dev, sizeof(FoldParams), cudaMemcpyHostToDevice, c->stream));
+  CUDA_TRY(wave_upload_constants(c->hp, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   return RNAFOLD_OK;
 }
@@ -127,14 +128,17 @@ void init_host_params(HostParams *hp) {
   hp->dev.s.max_ninio = 300;
 }
 
-// Length classes of the shared-memory kernel: a launch is sized (shared memory, hence CTAs/SM)
-// by the longest sequence in it, so mixed batches are split into classes.
-const int kSmemClasses[] = {40, 64, 80, 100, 128, 160, 200, 232};
+// Length classes: a launch is sized (shared memory, hence CTAs/SM) by the longest sequence in it,
+// so mixed batches are split into classes.  Sequences that fit the fast wavefront kernel (int16
+// tables in shared memory) go there; longer ones use the int32 CTA kernel with global tables.
+const int kWaveClasses[] = {32, 48, 64, 80, 100, 128, 160, 200, 256};
+const int kLegacySmemLimit = 232;
 
+enum { kKindWave16 = 0, kKindLegacySmem = 1, kKindLegacyGlobal = 2 };
 struct Launch {
   int begin, end;  // slice of the length-sorted order
   int nmax;
-  bool smem;
+  int kind;
 };
 
 int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target,
@@ -182,16 +186,19 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   // split into launches
   std::vector<Launch> launches;
   {
+    const int ncls = (int)(sizeof(kWaveClasses) / sizeof(int));
+    int wave_limit = 0;
+    for (int k = 0; k < ncls; ++k)
+      if (wave_smem_bytes(kWaveClasses[k], 2) + 1024 <= (size_t)c->max_smem_optin) wave_limit = kWaveClasses[k];
     int k = 0;
-    const int smem_limit = kSmemClasses[sizeof(kSmemClasses) / sizeof(int) - 1];
-    while (k < B && len_at(k) > smem_limit) ++k;
-    if (k > 0) launches.push_back(Launch{0, k, len_at(0), false});
-    const int ncls = (int)(sizeof(kSmemClasses) / sizeof(int));
+    while (k < B && len_at(k) > wave_limit) ++k;
+    if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal});
     for (int cls = ncls - 1; cls >= 0 && k < B; --cls) {
-      const int lo = cls > 0 ? kSmemClasses[cls - 1] : -1;
+      if (kWaveClasses[cls] > wave_limit) continue;
+      const int lo = cls > 0 ? kWaveClasses[cls - 1] : -1;
       int e = k;
       while (e < B && len_at(e) > lo) ++e;
-      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), true});
+      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), kKindWave16});
       k = e;
     }
   }
@@ -248,11 +255,30 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   CUDA_TRY(out_view(target ? reward_out : nullptr, c->d_reward, sizeof(double) * (size_t)B, &v_rw));
   CUDA_TRY(out_view(target ? mismatch_out : nullptr, c->d_mismatch, total + 16, &v_mm));
 
-  // ---- control words: one queue counter per launch + status
+  // ---- control words: two queue counters per launch (+ range-check re-run) + status; redo flags
   const int nl = (int)launches.size();
-  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(nl + 1)));
-  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)(nl + 1), st));
+  const int nctl = 2 * nl + 1;
+  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)nctl));
+  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)nctl, st));
   int32_t *d_ctl = (int32_t *)c->d_ctl.p;
+  CUDA_TRY(c->d_redo.reserve(sizeof(int32_t) * (size_t)B));
+  CUDA_TRY(cudaMemsetAsync(c->d_redo.p, 0, sizeof(int32_t) * (size_t)B, st));
+
+  auto legacy = [&](const Launch &L, BatchArgs a, bool smem_tables, int32_t *queue) -> int {
+    const int count = L.end - L.begin;
+    const int occ = std::max(1, cta_kernel_occupancy(L.nmax, smem_tables));
+    const int grid = std::min(count, c->num_sms * occ);
+    int *ws = nullptr;
+    long long stride = 0;
+    if (!smem_tables) {
+      stride = 2LL * table_cells(L.nmax);
+      CUDA_TRY(c->d_ws.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
+      ws = (int *)c->d_ws.p;
+    }
+    CUDA_TRY(launch_fold_cta(c->d_params, a, L.nmax, smem_tables, grid, ws, stride, queue, st));
+    c->last_launches++;
+    return RNAFOLD_OK;
+  };
 
   if (c->timed) CUDA_TRY(cudaEventRecord(c->ev0, st));
   for (int li = 0; li < nl; ++li) {
@@ -270,19 +296,25 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     a.reward = (double *)v_rw;
     a.mismatch = (uint8_t *)v_mm;
     a.reward_exp = reward_exp;
-    a.status = d_ctl + nl;
-    const int occ = std::max(1, cta_kernel_occupancy(L.nmax, L.smem));
-    const int grid = std::min(count, c->num_sms * occ);
-    int *ws = nullptr;
-    long long stride = 0;
-    if (!L.smem) {
-      stride = 2LL * table_cells(L.nmax);
-      CUDA_TRY(c->d_ws.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
-      ws = (int *)c->d_ws.p;
+    a.status = d_ctl + 2 * nl;
+    a.redo = (int32_t *)c->d_redo.p;
+    a.redo_filter = 0;
+    if (L.kind == kKindWave16) {
+      const int threads = wave_threads(L.nmax);
+      const int occ = std::max(1, wave_occupancy(L.nmax, 2, threads));
+      const int grid = std::min(count, c->num_sms * occ);
+      CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, 2, grid, threads, d_ctl + 2 * li, st));
+      c->last_launches++;
+      c->last_routed[0] += count;
+      // sequences whose values left the int16 range (flagged on the device) are re-run in int32
+      a.redo_filter = 1;
+      int rc = legacy(L, a, L.nmax <= kLegacySmemLimit, d_ctl + 2 * li + 1);
+      if (rc) return rc;
+    } else {
+      int rc = legacy(L, a, L.kind == kKindLegacySmem, d_ctl + 2 * li);
+      if (rc) return rc;
+      c->last_routed[L.kind == kKindLegacySmem ? 0 : 2] += count;
     }
-    CUDA_TRY(launch_fold_cta(c->d_params, a, L.nmax, L.smem, grid, ws, stride, d_ctl + li, st));
-    c->last_launches++;
-    c->last_routed[L.smem ? 0 : 2] += count;
   }
   if (c->timed) CUDA_TRY(cudaEventRecord(c->ev1, st));
 
@@ -311,7 +343,7 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     CUDA_TRY(back(target ? reward_out : nullptr, v_rw, o_rw, 8 * (size_t)B));
     CUDA_TRY(back(target ? mismatch_out : nullptr, v_mm, o_mm, total));
     int32_t status = 0;
-    CUDA_TRY(cudaMemcpyAsync(&status, d_ctl + nl, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&status, d_ctl + 2 * nl, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     auto fin = [&](void *user, size_t off_b, size_t bytes) {
       if (user && !is_device_ptr(user) && bytes) std::memcpy(user, ho + off_b, bytes);
@@ -383,7 +415,7 @@ void rnafold_shutdown(void) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   for (DevBuf *b : {&c->d_seq, &c->d_off, &c->d_order, &c->d_target, &c->d_db, &c->d_mfe, &c->d_hd,
-                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws})
+                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws, &c->d_redo})
     b->release();
   for (PinBuf *b : {&c->h_in, &c->h_out, &c->h_off}) b->release();
   cudaFree(c->d_params);
@@ -475,7 +507,7 @@ int rnafold_get_md(const char *name, double *value) {
 
 int rnafold_workspace_bytes(int32_t B, int32_t nmax, size_t *bytes) {
   if (!bytes || B < 0 || nmax < 0 || nmax > RNAFOLD_MAX_LEN) return fail(RNAFOLD_EINVAL, "bad arguments");
-  const int smem_limit = kSmemClasses[sizeof(kSmemClasses) / sizeof(int) - 1];
+  const int smem_limit = kLegacySmemLimit;
   size_t ws = 0;
   if (nmax > smem_limit) {
     const int sms = g_ctx ? g_ctx->num_sms : 148;

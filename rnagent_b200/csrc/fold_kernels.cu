@@ -103,6 +103,7 @@ fold_cta_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *_
     const int slot = misc[0];
     if (slot >= a.B) break;
     const int b = a.order ? a.order[slot] : slot;
+    if (a.redo_filter && !a.redo[b]) continue;
     const int beg = a.off[b];
     const int n = a.off[b + 1] - beg;
 

@@ -26,12 +26,22 @@ struct BatchArgs {
   uint8_t *mismatch;
   double reward_exp;
   int32_t *status;  // set non-zero by a CTA whose backtrack found no decomposition
+  int32_t *redo;    // per sequence: set by the int16 kernel when a value left its checked range
+  int32_t redo_filter;  // non-zero: fold only sequences whose redo flag is set (int32 re-run)
 };
 
 size_t cta_kernel_smem_bytes(int nmax, bool tables_in_smem);
 int cta_kernel_occupancy(int nmax, bool tables_in_smem);
 cudaError_t launch_fold_cta(const FoldParams *gp, const BatchArgs &a, int nmax, bool tables_in_smem,
                             int grid, int *gws, long long ws_stride, int *queue, cudaStream_t st);
+
+// fold_wave.cu: the fast wavefront kernel (tables in shared memory, int16 or int32 storage)
+size_t wave_smem_bytes(int nmax, int esz);
+int wave_threads(int nmax);
+int wave_occupancy(int nmax, int esz, int threads);
+cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st);
+cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax, int esz, int grid, int threads,
+                             int *queue, cudaStream_t st);
 
 // peaks.cu: on-box shared-memory-load and min-plus (ALU) peak rates, whole device, per second
 cudaError_t measure_onchip_peaks(int num_sms, cudaStream_t st, double *lds_per_s, double *minplus_per_s);

@@ -1,0 +1,619 @@
+// fold_wave.cu -- the fast fold kernel: anti-diagonal wavefront with warp-level work items.
+//
+// One CTA folds one sequence at a time (persistent CTAs, length-sorted queue).  Per anti-diagonal
+// d ("phase") the CTA's warps share a list of independent work items, one __syncthreads per phase:
+//
+//   I(b,r)  interior-loop partial minima of diagonal d for cell block b (32 consecutive cells) and
+//           loop-size range r.  Lanes run across cells, so for a fixed loop shape (n1,n2) every lane
+//           reads consecutive words (no bank conflicts) and the shape's energy term is warp-uniform:
+//           one LDS + one DPX VIADDMNMX (constant-bank operand) per candidate, fully unrolled.
+//   M(b,m)  multibranch split partial minima  min_t fML(i,i+t) + fML(i+t+1,j)  of diagonal d.
+//   F(b)    finalisation of diagonal d-1: hairpin, the 9 tabulated small loops, multiloop closing,
+//           combination of the partials, fML, and the pre-added table variants read by I().
+//   X       one step of the exterior recursion f5[d-1].
+//
+// Storage: full triangles of c and fML (diagonal-major) plus 32-diagonal rolling windows of
+//   cI = c + mismatchI(inner side), c1 = c + mismatch1nI(inner side), cB = c + TerminalAU(inner)
+// so that a generic / 1xn / bulge candidate is a single add.  Tables are int16 (fast path, range
+// checked on every store; a violation flags the sequence for the int32 kernels) or int32.
+//
+// Replaces ViennaRNA 2.4.14 fill_arrays + backtrack behind `RNA.fold` (rlif/settings.py:63-64;
+// recursions SURVEY.md 8a' F3-F7), fused with hamming_distance (rlif/rna/utils.py:67-75) and the
+// reward of Solution.evaluate (rlif/rna/solution.py:145-148).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "energy.cuh"
+#include "fold_kernels.h"
+
+namespace rnafold {
+
+// warp-uniform constants of the live parameter set (constant bank -> usable as instruction operands)
+struct WaveConst {
+  int G[31][32];  // G[L][n1]: size/asymmetry term of loop shape (n1, L-n1): bulge[L] or interior[L]+ninio
+  int MLbase, MLclosing, MLintern, TerminalAU;
+};
+__constant__ WaveConst cW;
+
+namespace {
+
+constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are read by phase d)
+constexpr int kParts = 4;   // loop-size ranges of the interior work items
+__device__ __constant__ int kPartBeg[kParts + 1] = {2, 15, 22, 27, 31};
+constexpr int kMlChunk = 128;  // split points per multiloop work item
+
+template <typename ST> struct Store;
+template <> struct Store<int16_t> {
+  static constexpr int kInfS = 30000;   // stored "infinity"
+  static constexpr int kThr = 15000;    // anything >= kThr is infinity
+  static constexpr int kLo = -25000;    // real values must stay inside (kLo, kHi) or the sequence is
+  static constexpr int kHi = 3000;      // re-run by the int32 kernel
+  static constexpr bool kChecked = true;
+};
+template <> struct Store<int32_t> {
+  static constexpr int kInfS = kInf;
+  static constexpr int kThr = 5000000;
+  static constexpr int kLo = -2000000000;
+  static constexpr int kHi = 5000000;
+  static constexpr bool kChecked = false;
+};
+
+__device__ __forceinline__ int tri(int n, int d) {
+  const int k = d - 4;
+  return k * (n - 4) - (k * (k - 1)) / 2;
+}
+
+__device__ __forceinline__ int enc_base(unsigned char ch) {
+  switch (ch) {
+    case 'A': case 'a': return 1;
+    case 'C': case 'c': return 2;
+    case 'G': case 'g': return 3;
+    case 'U': case 'u': case 'T': case 't': return 4;
+    default: return 0;
+  }
+}
+
+// loop-shape classes of the unrolled interior scan
+enum { kSkip = 0, kGen = 1, k1n = 2, kBul = 3 };
+__host__ __device__ constexpr int shape_class(int n1, int n2) {
+  const int nl = n1 > n2 ? n1 : n2, ns = n1 > n2 ? n2 : n1;
+  if (ns == 0) return nl >= 2 ? kBul : kSkip;          // stack, 1-bulge are tabulated specials
+  if (ns == 1) return nl >= 3 ? k1n : kSkip;           // 1x1, 1x2 specials
+  if (ns == 2) return nl >= 4 ? kGen : kSkip;          // 2x2, 2x3 specials
+  return kGen;
+}
+
+struct WaveSmem {
+  int f5_off, dml_off, bt_off, misc_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, wB_off, total;
+  int rs;        // window row stride (elements)
+  int mlparts;   // max multiloop parts per cell
+  __host__ __device__ static WaveSmem make(int nmax, int esz) {
+    WaveSmem L;
+    int o = 0;
+    auto take = [&](int bytes) { int r = o; o += (bytes + 15) / 16 * 16; return r; };
+    const int np = nmax + 8;
+    L.rs = (nmax + 7) / 8 * 8;
+    L.mlparts = (nmax + kMlChunk - 1) / kMlChunk;
+    L.f5_off = take(np * 4);
+    L.dml_off = take(3 * np * 4);
+    L.bt_off = take(np * 4);
+    L.misc_off = take(64);
+    L.S_off = take(np);
+    L.db_off = take(np);
+    L.part_off = take(2 * kParts * 3 * np * esz);   // [parity][part][class][cell]
+    L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
+    const int cells = table_cells(nmax) + 64;
+    L.C_off = take(cells * esz);
+    L.F_off = take(cells * esz);
+    L.wI_off = take((kWin * L.rs + 64) * esz);
+    L.w1_off = take((kWin * L.rs + 64) * esz);
+    L.wB_off = take((kWin * L.rs + 64) * esz);
+    L.total = o;
+    return L;
+  }
+};
+
+
+// ---------------------------------------------------------------------------------------------
+// I(b,r): all non-tabulated loop shapes of total size L for 32 consecutive cells.
+// rowX point at window row (d-2-L) + x; shape (n1, L-n1) reads element n1 of the row.
+// ---------------------------------------------------------------------------------------------
+template <typename ST, int L>
+__device__ __forceinline__ void interior_row(const ST *__restrict__ rowI, const ST *__restrict__ row1,
+                                             const ST *__restrict__ rowB, int &aI0, int &aI1, int &a1, int &aB) {
+#pragma unroll
+  for (int n1 = 0; n1 <= L; ++n1) {
+    const int cls = shape_class(n1, L - n1);
+    if (cls == kBul) aB = __viaddmin_s32((int)rowB[n1], cW.G[L][n1], aB);
+    else if (cls == k1n) a1 = __viaddmin_s32((int)row1[n1], cW.G[L][n1], a1);
+    else if (cls == kGen) {
+      if (n1 & 1) aI1 = __viaddmin_s32((int)rowI[n1], cW.G[L][n1], aI1);
+      else aI0 = __viaddmin_s32((int)rowI[n1], cW.G[L][n1], aI0);
+    }
+  }
+}
+
+template <typename ST>
+__device__ __forceinline__ void interior_rows(int L, const ST *rowI, const ST *row1, const ST *rowB, int &aI0,
+                                              int &aI1, int &a1, int &aB) {
+  switch (L) {
+#define ROW_CASE(K) case K: interior_row<ST, K>(rowI, row1, rowB, aI0, aI1, a1, aB); break;
+    ROW_CASE(2) ROW_CASE(3) ROW_CASE(4) ROW_CASE(5) ROW_CASE(6) ROW_CASE(7) ROW_CASE(8) ROW_CASE(9)
+    ROW_CASE(10) ROW_CASE(11) ROW_CASE(12) ROW_CASE(13) ROW_CASE(14) ROW_CASE(15) ROW_CASE(16) ROW_CASE(17)
+    ROW_CASE(18) ROW_CASE(19) ROW_CASE(20) ROW_CASE(21) ROW_CASE(22) ROW_CASE(23) ROW_CASE(24) ROW_CASE(25)
+    ROW_CASE(26) ROW_CASE(27) ROW_CASE(28) ROW_CASE(29) ROW_CASE(30)
+#undef ROW_CASE
+    default: break;
+  }
+}
+
+template <typename ST>
+__device__ __forceinline__ ST put(int v, int &flag) {
+  if (v >= Store<ST>::kThr) return (ST)Store<ST>::kInfS;
+  if (Store<ST>::kChecked && (v <= Store<ST>::kLo || v >= Store<ST>::kHi)) flag = 1;
+  return (ST)v;
+}
+
+__device__ __forceinline__ int nparts_of(int d, int n) {
+  if (d >= n) return 0;
+  const int lmax = min(kMaxLoop, d - 6);
+  int np = 0;
+#pragma unroll
+  for (int r = 0; r < kParts; ++r) np += (kPartBeg[r] <= lmax) ? 1 : 0;
+  return np;
+}
+__device__ __forceinline__ int mlparts_of(int d, int n) {
+  const int nsplit = d - 2 * kTurn - 2;  // t = 4 .. d-5
+  return (d < n && nsplit > 0) ? (nsplit + kMlChunk - 1) / kMlChunk : 0;
+}
+
+// the 9 tabulated loop shapes handled in the finalisation
+__device__ __constant__ int kSpecialN1[9] = {0, 0, 1, 1, 1, 2, 2, 2, 3};
+__device__ __constant__ int kSpecialN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
+
+// ---------------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------------
+template <typename ST, int MAXT>
+__global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
+                                                        int *__restrict__ queue) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const WaveSmem Ls = WaveSmem::make(nmax, (int)sizeof(ST));
+  int *f5 = reinterpret_cast<int *>(smem + Ls.f5_off);
+  int *dml = reinterpret_cast<int *>(smem + Ls.dml_off);
+  int *bt = reinterpret_cast<int *>(smem + Ls.bt_off);
+  int *misc = reinterpret_cast<int *>(smem + Ls.misc_off);
+  unsigned char *S = smem + Ls.S_off;
+  unsigned char *db = smem + Ls.db_off;
+  ST *part = reinterpret_cast<ST *>(smem + Ls.part_off);
+  int *mlp = reinterpret_cast<int *>(smem + Ls.mlp_off);
+  ST *C = reinterpret_cast<ST *>(smem + Ls.C_off);
+  ST *F = reinterpret_cast<ST *>(smem + Ls.F_off);
+  ST *wI = reinterpret_cast<ST *>(smem + Ls.wI_off);
+  ST *w1 = reinterpret_cast<ST *>(smem + Ls.w1_off);
+  ST *wB = reinterpret_cast<ST *>(smem + Ls.wB_off);
+  const int np = nmax + 8, rs = Ls.rs, mlparts = Ls.mlparts;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = blockDim.x >> 5, NT = blockDim.x;
+  const SmallParams &sp = gp->s;
+  constexpr int kInfS = Store<ST>::kInfS;
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) {
+      misc[0] = atomicAdd(queue, 1);
+      misc[1] = 0;  // backtrack failure code
+      misc[2] = 0;  // Hamming accumulator
+      misc[3] = 0;  // range-check flag
+    }
+    __syncthreads();
+    const int slot = misc[0];
+    if (slot >= a.B) break;
+    const int b = a.order ? a.order[slot] : slot;
+    const int beg = a.off[b];
+    const int n = a.off[b + 1] - beg;
+    int flag = 0;
+
+    for (int k = tid; k < n; k += NT) {
+      S[k + 1] = (unsigned char)enc_base(a.seq[beg + k]);
+      db[k] = '.';
+    }
+    for (int k = tid; k <= n; k += NT) f5[k] = 0;
+    __syncthreads();
+    if (tid == 0 && n > 0) {
+      S[0] = S[n];
+      S[n + 1] = S[1];
+    }
+    __syncthreads();
+
+    for (int d = kTurn + 1; d <= n + 1; ++d) {
+      const int par = d & 1, par1 = par ^ 1;
+      const int cells_d = (d < n) ? n - d : 0;
+      const int nb_d = (cells_d + 31) >> 5;
+      const int lmax = min(kMaxLoop, d - 6);
+      const int npd = nparts_of(d, n), mpd = mlparts_of(d, n);
+      const int d1 = d - 1;
+      const int cells_1 = (d1 >= kTurn + 1 && d1 < n) ? n - d1 : 0;
+      const int nb_1 = (cells_1 + 31) >> 5;
+      const int has_x = (d1 >= kTurn + 2 && d1 <= n) ? 1 : 0;
+      const int nI = nb_d * npd, nM = nb_d * mpd, nF = nb_1;
+      const int total = nI + nM + nF + has_x;
+      for (int k = warp; k < total; k += NW) {
+        if (k < nI) {
+          // ---------------- I(b,r)
+          const int blk = k / npd, r = k - blk * npd;
+          const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
+          int aI0 = kInfS, aI1 = kInfS, a1 = kInfS, aB = kInfS;
+          const int l0 = kPartBeg[r], l1 = min(kPartBeg[r + 1] - 1, lmax);
+          for (int L = l0; L <= l1; ++L) {
+            const int row = ((d - 2 - L) & (kWin - 1)) * rs + xc + 1;  // inner pair p = i+1+n1 -> cell p-1
+            interior_rows<ST>(L, wI + row, w1 + row, wB + row, aI0, aI1, a1, aB);
+          }
+          if (x < cells_d) {
+            ST *dst = part + ((par * kParts + r) * 3) * np + x;
+            dst[0] = (ST)min(aI0, aI1);
+            dst[np] = (ST)a1;
+            dst[2 * np] = (ST)aB;
+          }
+        } else if (k < nI + nM) {
+          // ---------------- M(b,m)
+          const int kk = k - nI;
+          const int blk = kk / mpd, m = kk - blk * mpd;
+          const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
+          const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
+          int ia = tri(n, t0) + xc, ib = tri(n, d - 1 - t0) + xc + t0 + 1;
+          int acc0 = kInf, acc1 = kInf;
+          int t = t0;
+          for (; t + 1 < t1; t += 2) {
+            const int va = (int)F[ia], vb = (int)F[ib];
+            const int ia2 = ia + (n - t), ib2 = ib - (n - (d - 1 - t));
+            const int vc = (int)F[ia2], vd = (int)F[ib2];
+            acc0 = __viaddmin_s32(va, vb, acc0);
+            acc1 = __viaddmin_s32(vc, vd, acc1);
+            ia = ia2 + (n - t - 1);
+            ib = ib2 - (n - (d - 2 - t));
+          }
+          if (t < t1) acc0 = __viaddmin_s32((int)F[ia], (int)F[ib], acc0);
+          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = min(acc0, acc1);
+        } else if (k < nI + nM + nF) {
+          // ---------------- F(b): finalise diagonal d1
+          const int blk = k - nI - nM;
+          const int x = blk * 32 + lane;
+          if (x < cells_1) {
+            const int i = x + 1, j = i + d1;
+            const int type = pair_type(S[i], S[j]);
+            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+            int cij = kInf;
+            if (type) {
+              cij = e_hairpin(sp, gp, S, i, j, type);
+              const int np1 = nparts_of(d1, n);
+              int pI = kInfS, p1 = kInfS, pB = kInfS;
+              for (int r = 0; r < np1; ++r) {
+                const ST *src = part + ((par1 * kParts + r) * 3) * np + x;
+                pI = min(pI, (int)src[0]);
+                p1 = min(p1, (int)src[np]);
+                pB = min(pB, (int)src[2 * np]);
+              }
+              cij = min(cij, pI + __ldg(&sp.mmI[type][si1][sj1]));
+              cij = min(cij, p1 + __ldg(&sp.mm1nI[type][si1][sj1]));
+              cij = min(cij, pB + (type > 2 ? cW.TerminalAU : 0));
+#pragma unroll
+              for (int s = 0; s < 9; ++s) {
+                const int n1 = kSpecialN1[s], n2 = kSpecialN2[s];
+                if (n1 + n2 <= d1 - 6) {
+                  const int p = i + 1 + n1, q = j - 1 - n2;
+                  const int t2 = pair_type(S[p], S[q]);
+                  if (t2) {
+                    const int cpq = (int)C[tri(n, q - p) + p - 1];
+                    cij = min(cij, cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si1, sj1, S[p - 1], S[q + 1]));
+                  }
+                }
+              }
+              if (d1 >= 2 * kTurn + 4)
+                cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
+            }
+            const int wrow = (d1 & (kWin - 1)) * rs + x;
+            C[tri(n, d1) + x] = put<ST>(cij, flag);
+            if (type) {
+              const int rt = rtype_of(type);
+              wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
+              w1[wrow] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
+              wB[wrow] = put<ST>(cij + (rt > 2 ? cW.TerminalAU : 0), flag);
+            } else {
+              wI[wrow] = (ST)kInfS;
+              w1[wrow] = (ST)kInfS;
+              wB[wrow] = (ST)kInfS;
+            }
+            int e = kInf;
+            if (d1 > kTurn + 1) {
+              const int pb = tri(n, d1 - 1) + x;
+              e = min((int)F[pb + 1], (int)F[pb]) + cW.MLbase;
+            }
+            if (type) e = min(e, cij + e_mlstem(sp, type, sim1, sjp1));
+            int dm = kInf;
+            const int mp1 = mlparts_of(d1, n);
+            for (int m = 0; m < mp1; ++m) dm = min(dm, mlp[(par1 * mlparts + m) * np + x]);
+            dml[(d1 % 3) * np + x] = dm;
+            F[tri(n, d1) + x] = put<ST>(min(e, dm), flag);
+          }
+        } else {
+          // ---------------- X: f5[d1]
+          const int j = d1;
+          const int s3 = (j < n) ? (int)S[j + 1] : -1;
+          int best = kInf;
+          for (int i = j - kTurn - 1 - lane; i >= 1; i -= 32) {
+            const int type = pair_type(S[i], S[j]);
+            if (!type) continue;
+            best = min(best, f5[i - 1] + (int)C[tri(n, j - i) + i - 1] + e_extloop(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
+          }
+          for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+          if (lane == 0) f5[j] = min(f5[j - 1], best);
+        }
+      }
+      __syncthreads();
+    }
+
+    if (flag) misc[3] = 1;
+    __syncthreads();
+
+    // ---- backtrack (ViennaRNA's deterministic order); warp 0, lanes scan candidates in that order
+    if (warp == 0 && !misc[3]) {
+      const unsigned full = 0xffffffffu;
+      int top = 0, failc = 0;
+      if (n > 0) {
+        if (lane == 0) bt[0] = (1 << 14) | (n << 2) | 0;
+        top = 1;
+      }
+      __syncwarp();
+      while (top > 0 && !failc) {
+        const int w = bt[--top];
+        __syncwarp();
+        int i = w >> 14, j = (w >> 2) & 0xfff;
+        const int ml = w & 3;
+        if (ml == 0) {
+          // largest jj <= j with f5[jj] != f5[jj-1]
+          int jj = 0;
+          for (int base = j; base >= 1 && !jj; base -= 32) {
+            const int k = base - lane;
+            const unsigned m = __ballot_sync(full, k >= 1 && f5[k] != f5[k - 1]);
+            if (m) jj = base - (__ffs(m) - 1);
+          }
+          if (jj < kTurn + 2) continue;
+          const int fij = f5[jj];
+          const int s3 = (jj < n) ? (int)S[jj + 1] : -1;
+          int u = 0;
+          for (int base = jj - kTurn - 1; base >= 1 && !u; base -= 32) {
+            const int k = base - lane;
+            bool hit = false;
+            if (k >= 1) {
+              const int type = pair_type(S[k], S[jj]);
+              if (type) {
+                const int e = (int)C[tri(n, jj - k) + k - 1] + e_extloop(sp, type, k > 1 ? (int)S[k - 1] : -1, s3);
+                hit = (fij == e + f5[k - 1]);
+              }
+            }
+            const unsigned m = __ballot_sync(full, hit);
+            if (m) u = base - (__ffs(m) - 1);
+          }
+          if (!u) { failc = 1; break; }
+          if (u - 1 > 0) {
+            if (lane == 0) bt[top] = (1 << 14) | ((u - 1) << 2) | 0;
+            top++;
+          }
+          i = u;
+          j = jj;
+        } else {
+          // fML sector: strip 3' bases, then 5' bases, then stem or split
+          int ii = i, jj = 0;
+          for (int base = j; base >= ii + kTurn + 1 && !jj; base -= 32) {
+            const int k = base - lane;
+            bool stop = false;
+            if (k >= ii + kTurn + 1) {
+              const int fij = (int)F[tri(n, k - ii) + ii - 1];
+              const int fi = (k - 1 - ii > kTurn) ? (int)F[tri(n, k - 1 - ii) + ii - 1] + cW.MLbase : kInf;
+              stop = (fij != fi);
+            }
+            const unsigned m = __ballot_sync(full, stop);
+            if (m) jj = base - (__ffs(m) - 1);
+          }
+          if (!jj) { failc = 2; break; }
+          int i2 = 0;
+          for (int base = ii; base <= jj - kTurn - 1 && !i2; base += 32) {
+            const int k = base + lane;
+            bool stop = false;
+            if (k <= jj - kTurn - 1) {
+              const int fij = (int)F[tri(n, jj - k) + k - 1];
+              const int fi = (jj - k - 1 > kTurn) ? (int)F[tri(n, jj - k - 1) + k] + cW.MLbase : kInf;
+              stop = (fij != fi);
+            }
+            const unsigned m = __ballot_sync(full, stop);
+            if (m) i2 = base + (__ffs(m) - 1);
+          }
+          if (!i2) { failc = 2; break; }
+          ii = i2;
+          const int fij = (int)F[tri(n, jj - ii) + ii - 1];
+          const int type = pair_type(S[ii], S[jj]);
+          if (type && fij == (int)C[tri(n, jj - ii) + ii - 1] + e_mlstem(sp, type, S[ii - 1], S[jj + 1])) {
+            i = ii;
+            j = jj;
+          } else {
+            int u = 0;
+            for (int base = ii + 1 + kTurn; base <= jj - 2 - kTurn && !u; base += 32) {
+              const int k = base + lane;
+              bool hit = false;
+              if (k <= jj - 2 - kTurn)
+                hit = (fij == (int)F[tri(n, k - ii) + ii - 1] + (int)F[tri(n, jj - k - 1) + k]);
+              const unsigned m = __ballot_sync(full, hit);
+              if (m) u = base + (__ffs(m) - 1);
+            }
+            if (!u) { failc = 3; break; }
+            if (lane == 0) {
+              bt[top] = (ii << 14) | (u << 2) | 1;
+              bt[top + 1] = ((u + 1) << 14) | (jj << 2) | 1;
+            }
+            top += 2;
+            __syncwarp();
+            continue;
+          }
+        }
+        // (i,j) pairs: walk down the helix / interior loops until a hairpin or a multiloop
+        for (;;) {
+          if (lane == 0) {
+            db[i - 1] = '(';
+            db[j - 1] = ')';
+          }
+          const int d = j - i;
+          const int type = pair_type(S[i], S[j]);
+          const int cij = (int)C[tri(n, d) + i - 1];
+          if (cij == e_hairpin(sp, gp, S, i, j, type)) break;
+          const int si1 = S[i + 1], sj1 = S[j - 1];
+          bool found = false;
+          const int amax = min(kMaxLoop, d - 6);
+          for (int n1 = 0; n1 <= amax && !found; ++n1) {
+            const int p = i + 1 + n1;
+            const int bmax = min(kMaxLoop - n1, d - 6 - n1);
+            const int n2 = lane, q = j - 1 - n2;
+            bool hit = false;
+            if (n2 <= bmax) {
+              const int t2 = pair_type(S[p], S[q]);
+              if (t2) {
+                const int e = (int)C[tri(n, q - p) + p - 1] +
+                              e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si1, sj1, S[p - 1], S[q + 1]);
+                hit = (e == cij);
+              }
+            }
+            const unsigned m = __ballot_sync(full, hit);
+            if (m) {
+              i = p;
+              j = j - 1 - (__ffs(m) - 1);
+              found = true;
+            }
+          }
+          if (found) continue;
+          const int e = cij - e_mlstem(sp, rtype_of(type), sj1, si1) - cW.MLclosing;
+          const int p = i + 1, q = j - 1;
+          int u = 0;
+          for (int base = p + kTurn + 1; base < q - kTurn - 1 && !u; base += 32) {
+            const int k = base + lane;
+            bool hit = false;
+            if (k < q - kTurn - 1) hit = (e == (int)F[tri(n, k - p) + p - 1] + (int)F[tri(n, q - k - 1) + k]);
+            const unsigned m = __ballot_sync(full, hit);
+            if (m) u = base + (__ffs(m) - 1);
+          }
+          if (!u) { failc = 4; break; }
+          if (lane == 0) {
+            bt[top] = (p << 14) | (u << 2) | 1;
+            bt[top + 1] = ((u + 1) << 14) | (q << 2) | 1;
+          }
+          top += 2;
+          break;
+        }
+        __syncwarp();
+      }
+      if (lane == 0 && failc) misc[1] = failc;
+    }
+    __syncthreads();
+
+    // ---- emit structure, energy, Hamming distance, reward
+    int local_hd = 0;
+    for (int k = tid; k < n; k += NT) {
+      const unsigned char ch = db[k];
+      if (a.db) a.db[beg + k] = ch;
+      if (a.target) {
+        const int mm = a.target[beg + k] != ch;
+        local_hd += mm;
+        if (a.mismatch) a.mismatch[beg + k] = (unsigned char)mm;
+      }
+    }
+    if (a.target) {
+      for (int o = 16; o; o >>= 1) local_hd += __shfl_xor_sync(0xffffffffu, local_hd, o);
+      if (lane == 0 && local_hd) atomicAdd(&misc[2], local_hd);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (a.mfe) a.mfe[b] = (n > 0) ? f5[n] : 0;
+      if (a.target) {
+        const int hd = misc[2];
+        if (a.hd) a.hd[b] = hd;
+        if (a.reward) {
+          double r = (n > 0) ? pow(1.0 - (double)hd / (double)n, a.reward_exp) : 0.0;
+          if (hd == 0) r += 0.25;
+          a.reward[b] = r;
+        }
+      }
+      if (Store<ST>::kChecked && a.redo) a.redo[b] = misc[3];
+      if (misc[1] && !misc[3]) atomicExch(a.status, misc[1]);
+    }
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+size_t wave_smem_bytes(int nmax, int esz) { return (size_t)WaveSmem::make(nmax, esz).total; }
+
+int wave_threads(int nmax) { return nmax <= 128 ? 128 : (nmax <= 224 ? 256 : 512); }
+
+cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
+  static WaveConst w;  // staging must outlive the async copy
+  const SmallParams &s = hp.dev.s;
+  for (int L = 0; L <= 30; ++L)
+    for (int n1 = 0; n1 < 32; ++n1) {
+      int v = 0;
+      if (n1 <= L) {
+        const int cls = shape_class(n1, L - n1);
+        const int asym = (L - 2 * n1 < 0 ? 2 * n1 - L : L - 2 * n1) * s.ninio;
+        v = (cls == kBul) ? s.bulge[L] : s.interior[L] + (asym < s.max_ninio ? asym : s.max_ninio);
+      }
+      w.G[L][n1] = v;
+    }
+  w.MLbase = s.MLbase;
+  w.MLclosing = s.MLclosing;
+  w.MLintern = s.MLintern;
+  w.TerminalAU = s.TerminalAU;
+  cudaError_t e = cudaMemcpyToSymbolAsync(cW, &w, sizeof(w), 0, cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return e;
+  return cudaStreamSynchronize(st);
+}
+
+template <typename ST, int MAXT>
+static cudaError_t launch_wave_t(const FoldParams *gp, const BatchArgs &a, int nmax, int grid, int *queue,
+                                 cudaStream_t st) {
+  const size_t smem = wave_smem_bytes(nmax, (int)sizeof(ST));
+  cudaError_t err =
+      cudaFuncSetAttribute(fold_wave_kernel<ST, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (err != cudaSuccess) return err;
+  fold_wave_kernel<ST, MAXT><<<grid, MAXT, smem, st>>>(gp, a, nmax, queue);
+  return cudaGetLastError();
+}
+
+template <typename ST, int MAXT>
+static int occupancy_t(int nmax) {
+  int nb = 0;
+  const size_t smem = wave_smem_bytes(nmax, (int)sizeof(ST));
+  if (cudaFuncSetAttribute(fold_wave_kernel<ST, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+      cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fold_wave_kernel<ST, MAXT>, MAXT, smem);
+  return nb;
+}
+
+#define WAVE_DISPATCH(FN, ...)                                                        \
+  (esz == 2 ? (threads == 128   ? FN<int16_t, 128>(__VA_ARGS__)                        \
+               : threads == 256 ? FN<int16_t, 256>(__VA_ARGS__)                        \
+                                : FN<int16_t, 512>(__VA_ARGS__))                       \
+            : (threads == 128   ? FN<int32_t, 128>(__VA_ARGS__)                        \
+               : threads == 256 ? FN<int32_t, 256>(__VA_ARGS__)                        \
+                                : FN<int32_t, 512>(__VA_ARGS__)))
+
+cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax, int esz, int grid, int threads,
+                             int *queue, cudaStream_t st) {
+  return WAVE_DISPATCH(launch_wave_t, gp, a, nmax, grid, queue, st);
+}
+
+int wave_occupancy(int nmax, int esz, int threads) { return WAVE_DISPATCH(occupancy_t, nmax); }
+
+}  // namespace rnafold

@@ -91,6 +91,26 @@ def test_biased_composition_and_unknown_letters(engine, oracle_params):
     _check(engine, P, _rand_batch(rng, 500, 20, 140, alphabet="acgut"))
 
 
+def test_int16_range_overflow_reruns_in_int32(engine, oracle_params):
+    """GC-only sequences of 200-256 nt reach energies below the int16 tables' checked range: the fast
+    kernel flags them on the device and the int32 kernel re-folds them; results stay bit-exact."""
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(16)
+    P = oracle_params("turner2004")
+    seqs = _rand_batch(rng, 64, 200, 256, alphabet="GC") + ["GC" * 128, "G" * 120 + "AAAA" + "C" * 120]
+    seqs += _rand_batch(rng, 64, 129, 256)
+    _check(engine, P, seqs)
+    want, wmfe, _ = _oracle_batch(P, seqs[:66])
+    assert wmfe.min() < -25000   # the case is really exercised
+
+
+def test_every_length_up_to_70(engine, oracle_params):
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(70)
+    seqs = ["".join(rng.choice(list("ACGU"), n)) for n in range(0, 71) for _ in range(12)]
+    _check(engine, oracle_params("turner2004"), seqs)
+
+
 def test_fold_signature_and_edge_cases(engine):
     engine.set_vienna_params(1)
     s, e = engine.fold("GCAAAAAAAAAUUUGC")
