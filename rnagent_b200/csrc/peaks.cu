@@ -31,8 +31,9 @@ __global__ void __launch_bounds__(kPeakThreads) lds_stream_kernel(int *out, int 
     for (int u = 0; u < kPeakUnroll; ++u) {
       int v;
       // consecutive lanes -> consecutive words (conflict free); rows rotate so loads stay distinct
-      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + 4u * kPeakThreads * (unsigned)(u & 3)));
-      acc[u] ^= v;
+      // the address changes every iteration so no load can be hoisted or merged
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + 4u * kPeakThreads * (unsigned)((u + it) & 3)));
+      acc[u] += v;
     }
   }
   int r = 0;
@@ -48,7 +49,7 @@ __global__ void __launch_bounds__(kPeakThreads) minplus_stream_kernel(int *out, 
   for (int u = 0; u < kPeakUnroll; ++u) acc[u] = 1000000 + u;
   for (int it = 0; it < iters; ++it) {
 #pragma unroll
-    for (int u = 0; u < kPeakUnroll; ++u) acc[u] = __viaddmin_s32(acc[u], x, acc[(u + 1) % kPeakUnroll] ^ it);
+    for (int u = 0; u < kPeakUnroll; ++u) acc[u] = __viaddmin_s32(acc[u], x, acc[(u + 1) % kPeakUnroll]);
   }
   int r = 0;
 #pragma unroll
