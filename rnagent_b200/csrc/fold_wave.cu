@@ -8,13 +8,14 @@
 //           reads consecutive words (no bank conflicts) and the shape's energy term is warp-uniform:
 //           one LDS + one DPX VIADDMNMX (constant-bank operand) per candidate, fully unrolled.
 //   M(b,m)  multibranch split partial minima  min_t fML(i,i+t) + fML(i+t+1,j)  of diagonal d.
-//   F(b)    finalisation of diagonal d-1: hairpin, the 9 tabulated small loops, multiloop closing,
-//           combination of the partials, fML, and the pre-added table variants read by I().
+//   T(b)    the 9 tabulated small loop shapes (stack, 1-bulge, 1x1, 1x2, 2x1, 2x2, 2x3, 3x2) of diagonal d.
+//   F(b)    finalisation of diagonal d-1: hairpin, multiloop closing, combination of the partials,
+//           fML, and the pre-added table variants read by I().
 //   X       one step of the exterior recursion f5[d-1].
 //
-// Storage: full triangles of c and fML (diagonal-major) plus 32-diagonal rolling windows of
-//   cI = c + mismatchI(inner side), c1 = c + mismatch1nI(inner side), cB = c + TerminalAU(inner)
-// so that a generic / 1xn / bulge candidate is a single add.  Tables are int16 (fast path, range
+// Storage (diagonal-major): full triangles of cB = c + TerminalAU(pair) and fML, plus 32-diagonal
+// rolling windows of cI = c + mismatchI(inner side) and c1 = c + mismatch1nI(inner side), so that a
+// generic / 1xn / bulge candidate is a single add.  Tables are int16 (fast path, range
 // checked on every store; a violation flags the sequence for the int32 kernels) or int32.
 //
 // Replaces ViennaRNA 2.4.14 fill_arrays + backtrack behind `RNA.fold` (rlif/settings.py:63-64;
@@ -39,7 +40,9 @@ namespace {
 
 constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are read by phase d)
 constexpr int kParts = 4;   // loop-size ranges of the interior work items
-__device__ __constant__ int kPartBeg[kParts + 1] = {2, 15, 22, 27, 31};
+constexpr int kSlots = kParts * 3 + 1;
+__host__ __device__ constexpr int part_beg(int r) { return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31; }
+constexpr int kMaxMlParts = 4;
 constexpr int kMlChunk = 128;  // split points per multiloop work item
 
 template <typename ST> struct Store;
@@ -84,7 +87,7 @@ __host__ __device__ constexpr int shape_class(int n1, int n2) {
 }
 
 struct WaveSmem {
-  int f5_off, dml_off, bt_off, misc_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, wB_off, total;
+  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, total;
   int rs;        // window row stride (elements)
   int mlparts;   // max multiloop parts per cell
   __host__ __device__ static WaveSmem make(int nmax, int esz) {
@@ -98,16 +101,16 @@ struct WaveSmem {
     L.dml_off = take(3 * np * 4);
     L.bt_off = take(np * 4);
     L.misc_off = take(64);
+    L.ptab_off = take(64);
     L.S_off = take(np);
     L.db_off = take(np);
-    L.part_off = take(2 * kParts * 3 * np * esz);   // [parity][part][class][cell]
+    L.part_off = take(2 * kSlots * np * esz);       // [parity][slot][cell]; slot = part*3+class, 12 = tabulated
     L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
     const int cells = table_cells(nmax) + 64;
     L.C_off = take(cells * esz);
     L.F_off = take(cells * esz);
     L.wI_off = take((kWin * L.rs + 64) * esz);
     L.w1_off = take((kWin * L.rs + 64) * esz);
-    L.wB_off = take((kWin * L.rs + 64) * esz);
     L.total = o;
     return L;
   }
@@ -133,18 +136,28 @@ __device__ __forceinline__ void interior_row(const ST *__restrict__ rowI, const 
   }
 }
 
-template <typename ST>
-__device__ __forceinline__ void interior_rows(int L, const ST *rowI, const ST *row1, const ST *rowB, int &aI0,
-                                              int &aI1, int &a1, int &aB) {
-  switch (L) {
-#define ROW_CASE(K) case K: interior_row<ST, K>(rowI, row1, rowB, aI0, aI1, a1, aB); break;
-    ROW_CASE(2) ROW_CASE(3) ROW_CASE(4) ROW_CASE(5) ROW_CASE(6) ROW_CASE(7) ROW_CASE(8) ROW_CASE(9)
-    ROW_CASE(10) ROW_CASE(11) ROW_CASE(12) ROW_CASE(13) ROW_CASE(14) ROW_CASE(15) ROW_CASE(16) ROW_CASE(17)
-    ROW_CASE(18) ROW_CASE(19) ROW_CASE(20) ROW_CASE(21) ROW_CASE(22) ROW_CASE(23) ROW_CASE(24) ROW_CASE(25)
-    ROW_CASE(26) ROW_CASE(27) ROW_CASE(28) ROW_CASE(29) ROW_CASE(30)
-#undef ROW_CASE
-    default: break;
+// One work item: loop sizes part_beg(R) .. part_beg(R+1)-1, all compile-time; rows beyond lmax
+// (short diagonals) are skipped by a warp-uniform branch.  xo = cell index of the inner pair's
+// first candidate (x + 1).
+template <typename ST, int L, int LEND>
+__device__ __forceinline__ void interior_span(const ST *__restrict__ wI, const ST *__restrict__ w1,
+                                              const ST *__restrict__ CB, int d, int n, int rs, int xo, int lmax,
+                                              int &aI0, int &aI1, int &a1, int &aB) {
+  if constexpr (L < LEND) {
+    if (L <= lmax) {
+      const int wrow = ((d - 2 - L) & (kWin - 1)) * rs + xo;
+      const int trow = tri(n, d - 2 - L) + xo;
+      interior_row<ST, L>(wI + wrow, w1 + wrow, CB + trow, aI0, aI1, a1, aB);
+    }
+    interior_span<ST, L + 1, LEND>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB);
   }
+}
+
+template <typename ST, int R>
+__device__ __forceinline__ void interior_part(const ST *__restrict__ wI, const ST *__restrict__ w1,
+                                              const ST *__restrict__ CB, int d, int n, int rs, int xo, int lmax,
+                                              int &aI0, int &aI1, int &a1, int &aB) {
+  interior_span<ST, part_beg(R), part_beg(R + 1)>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB);
 }
 
 template <typename ST>
@@ -159,7 +172,7 @@ __device__ __forceinline__ int nparts_of(int d, int n) {
   const int lmax = min(kMaxLoop, d - 6);
   int np = 0;
 #pragma unroll
-  for (int r = 0; r < kParts; ++r) np += (kPartBeg[r] <= lmax) ? 1 : 0;
+  for (int r = 0; r < kParts; ++r) np += (part_beg(r) <= lmax) ? 1 : 0;
   return np;
 }
 __device__ __forceinline__ int mlparts_of(int d, int n) {
@@ -167,9 +180,12 @@ __device__ __forceinline__ int mlparts_of(int d, int n) {
   return (d < n && nsplit > 0) ? (nsplit + kMlChunk - 1) / kMlChunk : 0;
 }
 
-// the 9 tabulated loop shapes handled in the finalisation
-__device__ __constant__ int kSpecialN1[9] = {0, 0, 1, 1, 1, 2, 2, 2, 3};
-__device__ __constant__ int kSpecialN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
+// k / nb for small quotients (warp-uniform, no integer division)
+__device__ __forceinline__ int div_small(int k, int nb, int qmax) {
+  int q = 0;
+  for (int t = 1; t < qmax; ++t) q += (k >= t * nb) ? 1 : 0;
+  return q;
+}
 
 // ---------------------------------------------------------------------------------------------
 // the kernel
@@ -187,15 +203,21 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
   unsigned char *db = smem + Ls.db_off;
   ST *part = reinterpret_cast<ST *>(smem + Ls.part_off);
   int *mlp = reinterpret_cast<int *>(smem + Ls.mlp_off);
-  ST *C = reinterpret_cast<ST *>(smem + Ls.C_off);
+  ST *CB = reinterpret_cast<ST *>(smem + Ls.C_off);
   ST *F = reinterpret_cast<ST *>(smem + Ls.F_off);
   ST *wI = reinterpret_cast<ST *>(smem + Ls.wI_off);
   ST *w1 = reinterpret_cast<ST *>(smem + Ls.w1_off);
-  ST *wB = reinterpret_cast<ST *>(smem + Ls.wB_off);
+  unsigned char *ptab = smem + Ls.ptab_off;
   const int np = nmax + 8, rs = Ls.rs, mlparts = Ls.mlparts;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = blockDim.x >> 5, NT = blockDim.x;
+  const int tid = threadIdx.x, lane = tid & 31, NW = blockDim.x >> 5, NT = blockDim.x;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
   const SmallParams &sp = gp->s;
   constexpr int kInfS = Store<ST>::kInfS;
+  const int tau = cW.TerminalAU;
+
+  if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
+  auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
+  auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
 
   for (;;) {
     __syncthreads();
@@ -235,93 +257,114 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
       const int cells_1 = (d1 >= kTurn + 1 && d1 < n) ? n - d1 : 0;
       const int nb_1 = (cells_1 + 31) >> 5;
       const int has_x = (d1 >= kTurn + 2 && d1 <= n) ? 1 : 0;
-      const int nI = nb_d * npd, nM = nb_d * mpd, nF = nb_1;
-      const int total = nI + nM + nF + has_x;
+      const int nI = nb_d * npd, nT = (lmax >= 0) ? nb_d : 0, nM = nb_d * mpd, nF = nb_1;
+      const int total = nI + nT + nM + nF + has_x;
       for (int k = warp; k < total; k += NW) {
         if (k < nI) {
-          // ---------------- I(b,r)
-          const int blk = k / npd, r = k - blk * npd;
-          const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
+          // ---------------- I(b,r): generic / 1xn / bulge shapes of loop sizes in part r
+          const int r = div_small(k, nb_d, kParts), blk = k - r * nb_d;
+          const int x = blk * 32 + lane, xo = min(x, cells_d - 1) + 1;
           int aI0 = kInfS, aI1 = kInfS, a1 = kInfS, aB = kInfS;
-          const int l0 = kPartBeg[r], l1 = min(kPartBeg[r + 1] - 1, lmax);
-          for (int L = l0; L <= l1; ++L) {
-            const int row = ((d - 2 - L) & (kWin - 1)) * rs + xc + 1;  // inner pair p = i+1+n1 -> cell p-1
-            interior_rows<ST>(L, wI + row, w1 + row, wB + row, aI0, aI1, a1, aB);
+          switch (r) {
+            case 0: interior_part<ST, 0>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
+            case 1: interior_part<ST, 1>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
+            case 2: interior_part<ST, 2>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
+            default: interior_part<ST, 3>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
           }
           if (x < cells_d) {
-            ST *dst = part + ((par * kParts + r) * 3) * np + x;
+            ST *dst = part + ((par * kSlots + r * 3)) * np + x;
             dst[0] = (ST)min(aI0, aI1);
             dst[np] = (ST)a1;
             dst[2 * np] = (ST)aB;
           }
-        } else if (k < nI + nM) {
-          // ---------------- M(b,m)
-          const int kk = k - nI;
-          const int blk = kk / mpd, m = kk - blk * mpd;
-          const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
-          const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
-          int ia = tri(n, t0) + xc, ib = tri(n, d - 1 - t0) + xc + t0 + 1;
-          int acc0 = kInf, acc1 = kInf;
-          int t = t0;
-          for (; t + 1 < t1; t += 2) {
-            const int va = (int)F[ia], vb = (int)F[ib];
-            const int ia2 = ia + (n - t), ib2 = ib - (n - (d - 1 - t));
-            const int vc = (int)F[ia2], vd = (int)F[ib2];
-            acc0 = __viaddmin_s32(va, vb, acc0);
-            acc1 = __viaddmin_s32(vc, vd, acc1);
-            ia = ia2 + (n - t - 1);
-            ib = ib2 - (n - (d - 2 - t));
-          }
-          if (t < t1) acc0 = __viaddmin_s32((int)F[ia], (int)F[ib], acc0);
-          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = min(acc0, acc1);
-        } else if (k < nI + nM + nF) {
-          // ---------------- F(b): finalise diagonal d1
-          const int blk = k - nI - nM;
+        } else if (k < nI + nT) {
+          // ---------------- T(b): the 9 tabulated shapes of diagonal d
+          const int blk = k - nI;
           const int x = blk * 32 + lane;
-          if (x < cells_1) {
-            const int i = x + 1, j = i + d1;
-            const int type = pair_type(S[i], S[j]);
-            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
-            int cij = kInf;
+          if (x < cells_d) {
+            const int i = x + 1, j = i + d;
+            const int type = PT(S[i], S[j]);
+            int best = kInfS;
             if (type) {
-              cij = e_hairpin(sp, gp, S, i, j, type);
-              const int np1 = nparts_of(d1, n);
-              int pI = kInfS, p1 = kInfS, pB = kInfS;
-              for (int r = 0; r < np1; ++r) {
-                const ST *src = part + ((par1 * kParts + r) * 3) * np + x;
-                pI = min(pI, (int)src[0]);
-                p1 = min(p1, (int)src[np]);
-                pB = min(pB, (int)src[2 * np]);
+              int si[5], sj[5];
+#pragma unroll
+              for (int u = 0; u < 5; ++u) {
+                si[u] = S[i + u];
+                sj[u] = S[j - u];
               }
-              cij = min(cij, pI + __ldg(&sp.mmI[type][si1][sj1]));
-              cij = min(cij, p1 + __ldg(&sp.mm1nI[type][si1][sj1]));
-              cij = min(cij, pB + (type > 2 ? cW.TerminalAU : 0));
 #pragma unroll
               for (int s = 0; s < 9; ++s) {
-                const int n1 = kSpecialN1[s], n2 = kSpecialN2[s];
-                if (n1 + n2 <= d1 - 6) {
-                  const int p = i + 1 + n1, q = j - 1 - n2;
-                  const int t2 = pair_type(S[p], S[q]);
+                constexpr int kN1[9] = {0, 0, 1, 1, 1, 2, 2, 2, 3};
+                constexpr int kN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
+                const int n1 = kN1[s], n2 = kN2[s];
+                if (n1 + n2 <= d - 6) {
+                  const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
                   if (t2) {
-                    const int cpq = (int)C[tri(n, q - p) + p - 1];
-                    cij = min(cij, cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si1, sj1, S[p - 1], S[q + 1]));
+                    const int cpq = craw((int)CB[tri(n, d - 2 - n1 - n2) + x + 1 + n1], t2);
+                    best = min(best, cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]));
                   }
                 }
               }
+            }
+            part[(par * kSlots + kParts * 3) * np + x] = (ST)min(best, kInfS);
+          }
+        } else if (k < nI + nT + nM) {
+          // ---------------- M(b,m): multibranch split points t0..t1-1 of diagonal d
+          const int kk = k - nI - nT;
+          const int m = (mpd == 1) ? 0 : div_small(kk, nb_d, kMaxMlParts), blk = kk - m * nb_d;
+          const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
+          const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
+          int oa = tri(n, t0), ob = tri(n, d - 1 - t0) + t0 + 1;  // warp-uniform offsets
+          int sa = n - t0, sb = n - (d - 1 - t0);
+          const ST *Fx = F + xc;
+          int acc0 = kInf, acc1 = kInf;
+          int t = t0;
+#pragma unroll 2
+          for (; t + 1 < t1; t += 2) {
+            const int oa2 = oa + sa, ob2 = ob - sb;
+            acc0 = __viaddmin_s32((int)Fx[oa], (int)Fx[ob], acc0);
+            acc1 = __viaddmin_s32((int)Fx[oa2], (int)Fx[ob2], acc1);
+            oa = oa2 + sa - 1;
+            ob = ob2 - sb - 1;
+            sa -= 2;
+            sb += 2;
+          }
+          if (t < t1) acc0 = __viaddmin_s32((int)Fx[oa], (int)Fx[ob], acc0);
+          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = min(acc0, acc1);
+        } else if (k < nI + nT + nM + nF) {
+          // ---------------- F(b): finalise diagonal d1
+          const int blk = k - nI - nT - nM;
+          const int x = blk * 32 + lane;
+          if (x < cells_1) {
+            const int i = x + 1, j = i + d1;
+            const int type = PT(S[i], S[j]);
+            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+            int cij = kInf;
+            const int wrow = (d1 & (kWin - 1)) * rs + x;
+            if (type) {
+              cij = e_hairpin(sp, gp, S, i, j, type);
+              const int np1 = nparts_of(d1, n);
+              const ST *src = part + (par1 * kSlots) * np + x;
+              int pI = kInfS, p1 = kInfS, pB = kInfS;
+              for (int r = 0; r < np1; ++r) {
+                pI = min(pI, (int)src[(r * 3) * np]);
+                p1 = min(p1, (int)src[(r * 3 + 1) * np]);
+                pB = min(pB, (int)src[(r * 3 + 2) * np]);
+              }
+              cij = min(cij, pI + __ldg(&sp.mmI[type][si1][sj1]));
+              cij = min(cij, p1 + __ldg(&sp.mm1nI[type][si1][sj1]));
+              cij = min(cij, pB + (type > 2 ? tau : 0));
+              if (d1 >= 6) cij = min(cij, (int)src[(kParts * 3) * np]);
               if (d1 >= 2 * kTurn + 4)
                 cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
-            }
-            const int wrow = (d1 & (kWin - 1)) * rs + x;
-            C[tri(n, d1) + x] = put<ST>(cij, flag);
-            if (type) {
               const int rt = rtype_of(type);
+              CB[tri(n, d1) + x] = put<ST>(cij + (type > 2 ? tau : 0), flag);
               wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
               w1[wrow] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
-              wB[wrow] = put<ST>(cij + (rt > 2 ? cW.TerminalAU : 0), flag);
             } else {
+              CB[tri(n, d1) + x] = (ST)kInfS;
               wI[wrow] = (ST)kInfS;
               w1[wrow] = (ST)kInfS;
-              wB[wrow] = (ST)kInfS;
             }
             int e = kInf;
             if (d1 > kTurn + 1) {
@@ -341,9 +384,10 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           const int s3 = (j < n) ? (int)S[j + 1] : -1;
           int best = kInf;
           for (int i = j - kTurn - 1 - lane; i >= 1; i -= 32) {
-            const int type = pair_type(S[i], S[j]);
+            const int type = PT(S[i], S[j]);
             if (!type) continue;
-            best = min(best, f5[i - 1] + (int)C[tri(n, j - i) + i - 1] + e_extloop(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
+            best = min(best, f5[i - 1] + craw((int)CB[tri(n, j - i) + i - 1], type) +
+                                 e_extloop(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
           }
           for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
           if (lane == 0) f5[j] = min(f5[j - 1], best);
@@ -387,7 +431,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             if (k >= 1) {
               const int type = pair_type(S[k], S[jj]);
               if (type) {
-                const int e = (int)C[tri(n, jj - k) + k - 1] + e_extloop(sp, type, k > 1 ? (int)S[k - 1] : -1, s3);
+                const int e = craw((int)CB[tri(n, jj - k) + k - 1], type) + e_extloop(sp, type, k > 1 ? (int)S[k - 1] : -1, s3);
                 hit = (fij == e + f5[k - 1]);
               }
             }
@@ -432,7 +476,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           ii = i2;
           const int fij = (int)F[tri(n, jj - ii) + ii - 1];
           const int type = pair_type(S[ii], S[jj]);
-          if (type && fij == (int)C[tri(n, jj - ii) + ii - 1] + e_mlstem(sp, type, S[ii - 1], S[jj + 1])) {
+          if (type && fij == craw((int)CB[tri(n, jj - ii) + ii - 1], type) + e_mlstem(sp, type, S[ii - 1], S[jj + 1])) {
             i = ii;
             j = jj;
           } else {
@@ -463,7 +507,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           }
           const int d = j - i;
           const int type = pair_type(S[i], S[j]);
-          const int cij = (int)C[tri(n, d) + i - 1];
+          const int cij = craw((int)CB[tri(n, d) + i - 1], type);
           if (cij == e_hairpin(sp, gp, S, i, j, type)) break;
           const int si1 = S[i + 1], sj1 = S[j - 1];
           bool found = false;
@@ -476,7 +520,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             if (n2 <= bmax) {
               const int t2 = pair_type(S[p], S[q]);
               if (t2) {
-                const int e = (int)C[tri(n, q - p) + p - 1] +
+                const int e = craw((int)CB[tri(n, q - p) + p - 1], t2) +
                               e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si1, sj1, S[p - 1], S[q + 1]);
                 hit = (e == cij);
               }
