@@ -31,7 +31,9 @@ namespace rnafold {
 
 // warp-uniform constants of the live parameter set (constant bank -> usable as instruction operands)
 struct WaveConst {
-  int G[31][32];  // G[L][n1]: size/asymmetry term of loop shape (n1, L-n1): bulge[L] or interior[L]+ninio
+  int GI[31][32];  // generic shapes (n1, L-n1): interior[L] + asymmetry penalty; kBig where the shape is not generic
+  int GB[32];      // bulges (0,L) and (L,0): bulge[L]
+  int G1[32];      // 1xn loops (1,L-1) and (L-1,1): interior[L] + asymmetry penalty
   int MLbase, MLclosing, MLintern, TerminalAU;
 };
 __constant__ WaveConst cW;
@@ -42,7 +44,10 @@ constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are r
 constexpr int kParts = 4;   // loop-size ranges of the interior work items
 constexpr int kSlots = kParts * 3 + 1;
 __host__ __device__ constexpr int part_beg(int r) { return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31; }
+__device__ __forceinline__ int part_beg_rt(int r) { return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31; }
 constexpr int kMaxMlParts = 4;
+constexpr int kBig = 10000000;  // additive term that can never win a minimum
+constexpr int kFullWinMax = 128;  // up to this length the cI / c1 tables are full triangles (cheaper row offsets)
 constexpr int kMlChunk = 128;  // split points per multiloop work item
 
 template <typename ST> struct Store;
@@ -109,8 +114,9 @@ struct WaveSmem {
     const int cells = table_cells(nmax) + 64;
     L.C_off = take(cells * esz);
     L.F_off = take(cells * esz);
-    L.wI_off = take((kWin * L.rs + 64) * esz);
-    L.w1_off = take((kWin * L.rs + 64) * esz);
+    const int wcells = nmax <= kFullWinMax ? cells : kWin * L.rs + 64;
+    L.wI_off = take(wcells * esz);
+    L.w1_off = take(wcells * esz);
     L.total = o;
     return L;
   }
@@ -118,46 +124,45 @@ struct WaveSmem {
 
 
 // ---------------------------------------------------------------------------------------------
-// I(b,r): all non-tabulated loop shapes of total size L for 32 consecutive cells.
-// rowX point at window row (d-2-L) + x; shape (n1, L-n1) reads element n1 of the row.
+// I(b,r): all non-tabulated loop shapes with loop size L in part r, for 32 consecutive cells.
+// Element n1 of table row (d-2-L), counted from the lane's cell + 1, is the inner pair of shape
+// (n1, L-n1).  The two bulges and the two 1xn loops of a row are taken at its ends; the generic
+// shapes n1 = 2..L-2 run through one of four fixed-width unrolled bodies (shapes beyond L-2 carry
+// kBig in cW.GI and never win), so the whole scan is a few KB of code that stays in the I-cache.
 // ---------------------------------------------------------------------------------------------
-template <typename ST, int L>
-__device__ __forceinline__ void interior_row(const ST *__restrict__ rowI, const ST *__restrict__ row1,
-                                             const ST *__restrict__ rowB, int &aI0, int &aI1, int &a1, int &aB) {
+template <typename ST, int W>
+__device__ __forceinline__ void generic_body(const ST *__restrict__ row, const int *__restrict__ g, int &a0, int &a1) {
 #pragma unroll
-  for (int n1 = 0; n1 <= L; ++n1) {
-    const int cls = shape_class(n1, L - n1);
-    if (cls == kBul) aB = __viaddmin_s32((int)rowB[n1], cW.G[L][n1], aB);
-    else if (cls == k1n) a1 = __viaddmin_s32((int)row1[n1], cW.G[L][n1], a1);
-    else if (cls == kGen) {
-      if (n1 & 1) aI1 = __viaddmin_s32((int)rowI[n1], cW.G[L][n1], aI1);
-      else aI0 = __viaddmin_s32((int)rowI[n1], cW.G[L][n1], aI0);
-    }
+  for (int k = 0; k < W; ++k) {
+    if (k & 1) a1 = __viaddmin_s32((int)row[k], g[k], a1);
+    else a0 = __viaddmin_s32((int)row[k], g[k], a0);
   }
 }
 
-// One work item: loop sizes part_beg(R) .. part_beg(R+1)-1, all compile-time; rows beyond lmax
-// (short diagonals) are skipped by a warp-uniform branch.  xo = cell index of the inner pair's
-// first candidate (x + 1).
-template <typename ST, int L, int LEND>
-__device__ __forceinline__ void interior_span(const ST *__restrict__ wI, const ST *__restrict__ w1,
-                                              const ST *__restrict__ CB, int d, int n, int rs, int xo, int lmax,
+template <typename ST, bool FULLW>
+__device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const ST *__restrict__ p1,
+                                              const ST *__restrict__ pB, int d, int n, int rs, int l0, int l1,
                                               int &aI0, int &aI1, int &a1, int &aB) {
-  if constexpr (L < LEND) {
-    if (L <= lmax) {
-      const int wrow = ((d - 2 - L) & (kWin - 1)) * rs + xo;
-      const int trow = tri(n, d - 2 - L) + xo;
-      interior_row<ST, L>(wI + wrow, w1 + wrow, CB + trow, aI0, aI1, a1, aB);
+  int off = tri(n, d - 2 - l0);      // warp-uniform: first cell of diagonal d-2-L
+  int step = n - d + 3 + l0;         // off(L+1) = off(L) - step(L)
+  for (int L = l0; L <= l1; ++L) {
+    const int offw = FULLW ? off : ((d - 2 - L) & (kWin - 1)) * rs;
+    const int gb = cW.GB[L], g1 = cW.G1[L];
+    aB = __viaddmin_s32((int)pB[off], gb, aB);
+    aB = __viaddmin_s32((int)pB[off + L], gb, aB);
+    a1 = __viaddmin_s32((int)p1[offw + 1], g1, a1);
+    a1 = __viaddmin_s32((int)p1[offw + L - 1], g1, a1);
+    if (L >= 6) {
+      const ST *row = pI + offw + 2;
+      const int *g = &cW.GI[L][2];
+      if (L <= 9) generic_body<ST, 6>(row, g, aI0, aI1);
+      else if (L <= 17) generic_body<ST, 14>(row, g, aI0, aI1);
+      else if (L <= 25) generic_body<ST, 22>(row, g, aI0, aI1);
+      else generic_body<ST, 27>(row, g, aI0, aI1);
     }
-    interior_span<ST, L + 1, LEND>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB);
+    off -= step;
+    ++step;
   }
-}
-
-template <typename ST, int R>
-__device__ __forceinline__ void interior_part(const ST *__restrict__ wI, const ST *__restrict__ w1,
-                                              const ST *__restrict__ CB, int d, int n, int rs, int xo, int lmax,
-                                              int &aI0, int &aI1, int &a1, int &aB) {
-  interior_span<ST, part_beg(R), part_beg(R + 1)>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB);
 }
 
 template <typename ST>
@@ -213,6 +218,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
   const SmallParams &sp = gp->s;
   constexpr int kInfS = Store<ST>::kInfS;
+  constexpr bool kFullW = (MAXT == 128);  // wave_threads(): 128 threads <=> nmax <= kFullWinMax
   const int tau = cW.TerminalAU;
 
   if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
@@ -265,12 +271,8 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           const int r = div_small(k, nb_d, kParts), blk = k - r * nb_d;
           const int x = blk * 32 + lane, xo = min(x, cells_d - 1) + 1;
           int aI0 = kInfS, aI1 = kInfS, a1 = kInfS, aB = kInfS;
-          switch (r) {
-            case 0: interior_part<ST, 0>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
-            case 1: interior_part<ST, 1>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
-            case 2: interior_part<ST, 2>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
-            default: interior_part<ST, 3>(wI, w1, CB, d, n, rs, xo, lmax, aI0, aI1, a1, aB); break;
-          }
+          const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
+          interior_item<ST, kFullW>(wI + xo, w1 + xo, CB + xo, d, n, rs, l0, l1, aI0, aI1, a1, aB);
           if (x < cells_d) {
             ST *dst = part + ((par * kSlots + r * 3)) * np + x;
             dst[0] = (ST)min(aI0, aI1);
@@ -340,7 +342,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             const int type = PT(S[i], S[j]);
             const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
             int cij = kInf;
-            const int wrow = (d1 & (kWin - 1)) * rs + x;
+            const int wrow = kFullW ? tri(n, d1) + x : (d1 & (kWin - 1)) * rs + x;
             if (type) {
               cij = e_hairpin(sp, gp, S, i, j, type);
               const int np1 = nparts_of(d1, n);
@@ -602,16 +604,15 @@ int wave_threads(int nmax) { return nmax <= 128 ? 128 : (nmax <= 224 ? 256 : 512
 cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
   static WaveConst w;  // staging must outlive the async copy
   const SmallParams &s = hp.dev.s;
-  for (int L = 0; L <= 30; ++L)
-    for (int n1 = 0; n1 < 32; ++n1) {
-      int v = 0;
-      if (n1 <= L) {
-        const int cls = shape_class(n1, L - n1);
-        const int asym = (L - 2 * n1 < 0 ? 2 * n1 - L : L - 2 * n1) * s.ninio;
-        v = (cls == kBul) ? s.bulge[L] : s.interior[L] + (asym < s.max_ninio ? asym : s.max_ninio);
-      }
-      w.G[L][n1] = v;
-    }
+  for (int L = 0; L < 32; ++L) {
+    const int lc = L <= 30 ? L : 30;
+    auto asym = [&](int k) { const int v = (k < 0 ? -k : k) * s.ninio; return v < s.max_ninio ? v : s.max_ninio; };
+    w.GB[L] = (L >= 2 && L <= 30) ? s.bulge[lc] : kBig;
+    w.G1[L] = (L >= 4 && L <= 30) ? s.interior[lc] + asym(L - 2) : kBig;
+    if (L <= 30)
+      for (int n1 = 0; n1 < 32; ++n1)
+        w.GI[L][n1] = (n1 <= L && shape_class(n1, L - n1) == kGen) ? s.interior[L] + asym(L - 2 * n1) : kBig;
+  }
   w.MLbase = s.MLbase;
   w.MLclosing = s.MLclosing;
   w.MLintern = s.MLintern;
