@@ -102,6 +102,10 @@ int rnafold_last_kernel_ms(float *ms);
  * (min-plus candidate) updates per second. */
 int rnafold_measure_onchip_peaks(double *lds_per_s, double *minplus_per_s);
 
+/* Host-only planning helper: dynamic shared memory (bytes) the wavefront kernel needs for sequences
+ * up to nmax with int16 (elem_bytes 2) or int32 (4) tables. */
+int rnafold_wave_smem_bytes(int32_t nmax, int32_t elem_bytes);
+
 /* SM count and opt-in shared memory per CTA of the bound device. */
 int rnafold_device_info(int32_t *num_sms, int32_t *smem_optin_bytes);
 

@@ -17,7 +17,7 @@ EXPORTS = [
     "rnafold_read_parameter_file", "rnafold_export_params", "rnafold_parse_params", "rnafold_set_md", "rnafold_get_md",
     "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch",
     "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
-    "rnafold_measure_onchip_peaks", "rnafold_device_info",
+    "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes",
 ]
 
 _lock = threading.Lock()
@@ -56,6 +56,7 @@ def load_library():
         L.rnafold_set_timing.argtypes = [ci]
         L.rnafold_last_kernel_ms.argtypes = [ctypes.POINTER(ctypes.c_float)]
         L.rnafold_measure_onchip_peaks.argtypes = [ctypes.POINTER(cd), ctypes.POINTER(cd)]
+        L.rnafold_wave_smem_bytes.argtypes = [ci, ci]
         L.rnafold_device_info.argtypes = [ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
         _cdll = L
         return L

@@ -134,7 +134,7 @@ void init_host_params(HostParams *hp) {
 const int kWaveClasses[] = {32, 48, 64, 80, 100, 128, 160, 200, 256};
 const int kLegacySmemLimit = 232;
 
-enum { kKindWave16 = 0, kKindLegacySmem = 1, kKindLegacyGlobal = 2 };
+enum { kKindWave = 0, kKindLegacySmem = 1, kKindLegacyGlobal = 2 };
 struct Launch {
   int begin, end;  // slice of the length-sorted order
   int nmax;
@@ -184,12 +184,13 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   auto len_at = [&](int k) { return oh[c->order_host[k] + 1] - oh[c->order_host[k]]; };
 
   // split into launches
+  const int wave_esz = wave_int16_ok(c->hp) ? 2 : 4;  // int16 tables unless the parameter set's terms are too large
   std::vector<Launch> launches;
   {
     const int ncls = (int)(sizeof(kWaveClasses) / sizeof(int));
     int wave_limit = 0;
     for (int k = 0; k < ncls; ++k)
-      if (wave_smem_bytes(kWaveClasses[k], 2) + 1024 <= (size_t)c->max_smem_optin) wave_limit = kWaveClasses[k];
+      if (wave_smem_bytes(kWaveClasses[k], wave_esz) + 1024 <= (size_t)c->max_smem_optin) wave_limit = kWaveClasses[k];
     int k = 0;
     while (k < B && len_at(k) > wave_limit) ++k;
     if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal});
@@ -198,7 +199,7 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
       const int lo = cls > 0 ? kWaveClasses[cls - 1] : -1;
       int e = k;
       while (e < B && len_at(e) > lo) ++e;
-      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), kKindWave16});
+      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), kKindWave});
       k = e;
     }
   }
@@ -299,17 +300,19 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     a.status = d_ctl + 2 * nl;
     a.redo = (int32_t *)c->d_redo.p;
     a.redo_filter = 0;
-    if (L.kind == kKindWave16) {
+    if (L.kind == kKindWave) {
       const int threads = wave_threads(L.nmax);
-      const int occ = std::max(1, wave_occupancy(L.nmax, 2, threads));
+      const int occ = std::max(1, wave_occupancy(L.nmax, wave_esz, threads));
       const int grid = std::min(count, c->num_sms * occ);
-      CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, 2, grid, threads, d_ctl + 2 * li, st));
+      CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, wave_esz, grid, threads, d_ctl + 2 * li, st));
       c->last_launches++;
       c->last_routed[0] += count;
-      // sequences whose values left the int16 range (flagged on the device) are re-run in int32
-      a.redo_filter = 1;
-      int rc = legacy(L, a, L.nmax <= kLegacySmemLimit, d_ctl + 2 * li + 1);
-      if (rc) return rc;
+      if (wave_esz == 2) {
+        // sequences whose values left the int16 range (flagged on the device) are re-run in int32
+        a.redo_filter = 1;
+        int rc = legacy(L, a, L.nmax <= kLegacySmemLimit, d_ctl + 2 * li + 1);
+        if (rc) return rc;
+      }
     } else {
       int rc = legacy(L, a, L.kind == kKindLegacySmem, d_ctl + 2 * li);
       if (rc) return rc;
@@ -564,6 +567,12 @@ int rnafold_measure_onchip_peaks(double *lds_per_s, double *minplus_per_s) {
   CUDA_TRY(cudaSetDevice(g_ctx->device));
   CUDA_TRY(measure_onchip_peaks(g_ctx->num_sms, g_ctx->stream, lds_per_s, minplus_per_s));
   return RNAFOLD_OK;
+}
+
+int rnafold_wave_smem_bytes(int32_t nmax, int32_t elem_bytes) {
+  // host-only planning helper: dynamic shared memory of the wavefront kernel for a length class
+  if (nmax < 0 || nmax > RNAFOLD_MAX_LEN || (elem_bytes != 2 && elem_bytes != 4)) return fail(RNAFOLD_EINVAL, "bad arguments");
+  return (int)wave_smem_bytes(nmax, elem_bytes);
 }
 
 int rnafold_device_info(int32_t *num_sms, int32_t *smem_optin_bytes) {

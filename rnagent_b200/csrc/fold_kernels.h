@@ -38,6 +38,7 @@ cudaError_t launch_fold_cta(const FoldParams *gp, const BatchArgs &a, int nmax, 
 // fold_wave.cu: the fast wavefront kernel (tables in shared memory, int16 or int32 storage)
 size_t wave_smem_bytes(int nmax, int esz);
 int wave_threads(int nmax);
+bool wave_int16_ok(const HostParams &hp);
 int wave_occupancy(int nmax, int esz, int threads);
 cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st);
 cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax, int esz, int grid, int threads,

@@ -24,6 +24,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <algorithm>
+
 #include "energy.cuh"
 #include "fold_kernels.h"
 
@@ -41,10 +43,10 @@ __constant__ WaveConst cW;
 namespace {
 
 constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are read by phase d)
-constexpr int kParts = 4;   // loop-size ranges of the interior work items
+constexpr int kParts = 3;   // loop-size ranges of the interior work items
 constexpr int kSlots = kParts * 3 + 1;
-__host__ __device__ constexpr int part_beg(int r) { return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31; }
-__device__ __forceinline__ int part_beg_rt(int r) { return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31; }
+__host__ __device__ constexpr int part_beg(int r) { return r == 0 ? 2 : r == 1 ? 18 : r == 2 ? 26 : 31; }
+__device__ __forceinline__ int part_beg_rt(int r) { return r == 0 ? 2 : r == 1 ? 18 : r == 2 ? 26 : 31; }
 constexpr int kMaxMlParts = 4;
 constexpr int kBig = 10000000;  // additive term that can never win a minimum
 constexpr int kFullWinMax = 128;  // up to this length the cI / c1 tables are full triangles (cheaper row offsets)
@@ -91,32 +93,36 @@ __host__ __device__ constexpr int shape_class(int n1, int n2) {
   return kGen;
 }
 
+__host__ __device__ constexpr int wave_np(int nmax) { return (nmax + 9) & ~1; }  // even row pitch of the scratch rows
+
 struct WaveSmem {
-  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, total;
+  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, pl_off, plo_off, total;
   int rs;        // window row stride (elements)
   int mlparts;   // max multiloop parts per cell
   __host__ __device__ static WaveSmem make(int nmax, int esz) {
     WaveSmem L;
     int o = 0;
     auto take = [&](int bytes) { int r = o; o += (bytes + 15) / 16 * 16; return r; };
-    const int np = nmax + 8;
+    const int np = wave_np(nmax);
     L.rs = (nmax + 7) / 8 * 8;
     L.mlparts = (nmax + kMlChunk - 1) / kMlChunk;
     L.f5_off = take(np * 4);
     L.dml_off = take(3 * np * 4);
-    L.bt_off = take(np * 4);
     L.misc_off = take(64);
     L.ptab_off = take(64);
     L.S_off = take(np);
     L.db_off = take(np);
-    L.part_off = take(2 * kSlots * np * esz);       // [parity][slot][cell]; slot = part*3+class, 12 = tabulated
+    L.part_off = take(2 * kSlots * np * esz);       // [parity][slot][cell]; slot = part*3+class, last = tabulated
+    L.bt_off = L.part_off;                          // the backtrack stack reuses the scratch rows after the fill
     L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
     const int cells = table_cells(nmax) + 64;
     L.C_off = take(cells * esz);
     L.F_off = take(cells * esz);
     const int wcells = nmax <= kFullWinMax ? cells : kWin * L.rs + 64;
     L.wI_off = take(wcells * esz);
-    L.w1_off = take(wcells * esz);
+    L.w1_off = take((kWin * L.rs + 64) * esz);  // c1 is only read at the two ends of a row: always a window
+    L.pl_off = take(nmax * nmax / 4 + 64);          // cells whose ends can pair, diagonal by diagonal (uint8 index)
+    L.plo_off = take(np * 2);                       // first list entry of each diagonal (+ total at [n])
     L.total = o;
     return L;
   }
@@ -146,14 +152,15 @@ __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const S
   int off = tri(n, d - 2 - l0);      // warp-uniform: first cell of diagonal d-2-L
   int step = n - d + 3 + l0;         // off(L+1) = off(L) - step(L)
   for (int L = l0; L <= l1; ++L) {
-    const int offw = FULLW ? off : ((d - 2 - L) & (kWin - 1)) * rs;
+    const int offw = ((d - 2 - L) & (kWin - 1)) * rs;
+    const int offi = FULLW ? off : offw;
     const int gb = cW.GB[L], g1 = cW.G1[L];
     aB = __viaddmin_s32((int)pB[off], gb, aB);
     aB = __viaddmin_s32((int)pB[off + L], gb, aB);
     a1 = __viaddmin_s32((int)p1[offw + 1], g1, a1);
     a1 = __viaddmin_s32((int)p1[offw + L - 1], g1, a1);
     if (L >= 6) {
-      const ST *row = pI + offw + 2;
+      const ST *row = pI + offi + 2;
       const int *g = &cW.GI[L][2];
       if (L <= 9) generic_body<ST, 6>(row, g, aI0, aI1);
       else if (L <= 17) generic_body<ST, 14>(row, g, aI0, aI1);
@@ -213,7 +220,9 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
   ST *wI = reinterpret_cast<ST *>(smem + Ls.wI_off);
   ST *w1 = reinterpret_cast<ST *>(smem + Ls.w1_off);
   unsigned char *ptab = smem + Ls.ptab_off;
-  const int np = nmax + 8, rs = Ls.rs, mlparts = Ls.mlparts;
+  unsigned char *pl = smem + Ls.pl_off;
+  unsigned short *plo = reinterpret_cast<unsigned short *>(smem + Ls.plo_off);
+  const int np = wave_np(nmax), rs = Ls.rs, mlparts = Ls.mlparts;
   const int tid = threadIdx.x, lane = tid & 31, NW = blockDim.x >> 5, NT = blockDim.x;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
   const SmallParams &sp = gp->s;
@@ -253,6 +262,45 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
     }
     __syncthreads();
 
+    // ---- lists of the cells whose ends can pair, one list per diagonal (at most n*n/4 entries in all):
+    // the interior-loop and tabulated-shape work items run over these lists, not over all cells.
+    for (int d = kTurn + 1 + warp; d < n; d += NW) {
+      int cnt = 0;
+      for (int base = 0; base < n - d; base += 32) {
+        const int x = base + lane;
+        cnt += __popc(__ballot_sync(0xffffffffu, x < n - d && PT(S[x + 1], S[x + 1 + d]) != 0));
+      }
+      if (lane == 0) plo[d] = (unsigned short)cnt;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      int carry = 0;
+      for (int base = kTurn + 1; base < n; base += 32) {
+        const int d = base + lane;
+        const int v = d < n ? (int)plo[d] : 0;
+        int inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += t;
+        }
+        if (d < n) plo[d] = (unsigned short)(carry + inc - v);
+        carry += __shfl_sync(0xffffffffu, inc, 31);
+      }
+      if (lane == 0 && n > kTurn + 1) plo[n] = (unsigned short)carry;
+    }
+    __syncthreads();
+    for (int d = kTurn + 1 + warp; d < n; d += NW) {
+      int pos = plo[d];
+      for (int base = 0; base < n - d; base += 32) {
+        const int x = base + lane;
+        const bool pr = x < n - d && PT(S[x + 1], S[x + 1 + d]) != 0;
+        const unsigned m = __ballot_sync(0xffffffffu, pr);
+        if (pr) pl[pos + __popc(m & ((1u << lane) - 1u))] = (unsigned char)x;
+        pos += __popc(m);
+      }
+    }
+    __syncthreads();
+
     for (int d = kTurn + 1; d <= n + 1; ++d) {
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
@@ -263,17 +311,21 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
       const int cells_1 = (d1 >= kTurn + 1 && d1 < n) ? n - d1 : 0;
       const int nb_1 = (cells_1 + 31) >> 5;
       const int has_x = (d1 >= kTurn + 2 && d1 <= n) ? 1 : 0;
-      const int nI = nb_d * npd, nT = (lmax >= 0) ? nb_d : 0, nM = nb_d * mpd, nF = nb_1;
+      const int pl0 = (d < n) ? (int)plo[d] : 0;
+      const int npair = (d < n) ? (int)plo[d + 1] - pl0 : 0;
+      const int nbI = (npair + 31) >> 5;
+      const int nI = nbI * npd, nT = (lmax >= 0) ? nbI : 0, nM = nb_d * mpd, nF = nb_1;
       const int total = nI + nT + nM + nF + has_x;
       for (int k = warp; k < total; k += NW) {
         if (k < nI) {
           // ---------------- I(b,r): generic / 1xn / bulge shapes of loop sizes in part r
-          const int r = div_small(k, nb_d, kParts), blk = k - r * nb_d;
-          const int x = blk * 32 + lane, xo = min(x, cells_d - 1) + 1;
-          int aI0 = kInfS, aI1 = kInfS, a1 = kInfS, aB = kInfS;
+          const int r = div_small(k, nbI, kParts), blk = k - r * nbI;
           const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
-          interior_item<ST, kFullW>(wI + xo, w1 + xo, CB + xo, d, n, rs, l0, l1, aI0, aI1, a1, aB);
-          if (x < cells_d) {
+          const int idx = blk * 32 + lane;
+          const int x = pl[pl0 + min(idx, npair - 1)];  // only cells whose ends can pair are scanned
+          int aI0 = kInfS, aI1 = kInfS, a1 = kInfS, aB = kInfS;
+          interior_item<ST, kFullW>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI0, aI1, a1, aB);
+          if (idx < npair) {
             ST *dst = part + ((par * kSlots + r * 3)) * np + x;
             dst[0] = (ST)min(aI0, aI1);
             dst[np] = (ST)a1;
@@ -281,13 +333,13 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           }
         } else if (k < nI + nT) {
           // ---------------- T(b): the 9 tabulated shapes of diagonal d
-          const int blk = k - nI;
-          const int x = blk * 32 + lane;
-          if (x < cells_d) {
+          const int idx = (k - nI) * 32 + lane;
+          if (idx < npair) {
+            const int x = pl[pl0 + idx];
             const int i = x + 1, j = i + d;
             const int type = PT(S[i], S[j]);
             int best = kInfS;
-            if (type) {
+            {
               int si[5], sj[5];
 #pragma unroll
               for (int u = 0; u < 5; ++u) {
@@ -342,7 +394,8 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             const int type = PT(S[i], S[j]);
             const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
             int cij = kInf;
-            const int wrow = kFullW ? tri(n, d1) + x : (d1 & (kWin - 1)) * rs + x;
+            const int wrow1 = (d1 & (kWin - 1)) * rs + x;
+            const int wrow = kFullW ? tri(n, d1) + x : wrow1;
             if (type) {
               cij = e_hairpin(sp, gp, S, i, j, type);
               const int np1 = nparts_of(d1, n);
@@ -362,11 +415,11 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
               const int rt = rtype_of(type);
               CB[tri(n, d1) + x] = put<ST>(cij + (type > 2 ? tau : 0), flag);
               wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
-              w1[wrow] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
+              w1[wrow1] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
             } else {
               CB[tri(n, d1) + x] = (ST)kInfS;
               wI[wrow] = (ST)kInfS;
-              w1[wrow] = (ST)kInfS;
+              w1[wrow1] = (ST)kInfS;
             }
             int e = kInf;
             if (d1 > kTurn + 1) {
@@ -598,6 +651,18 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
 // host side
 // ---------------------------------------------------------------------------------------------
 size_t wave_smem_bytes(int nmax, int esz) { return (size_t)WaveSmem::make(nmax, esz).total; }
+
+// The two-cells-per-lane int16 scan adds the loop-size terms in 16-bit lanes: every term must keep
+// table value + term inside int16 (tables are checked to lie in (-25000, 30000]).
+bool wave_int16_ok(const HostParams &hp) {
+  const SmallParams &s = hp.dev.s;
+  int lo = 0, hi = 0;
+  for (int L = 2; L <= 30; ++L) {
+    lo = std::min(lo, std::min(s.bulge[L], s.interior[L]));
+    hi = std::max(hi, std::max(s.bulge[L], s.interior[L] + std::max(0, s.max_ninio)));
+  }
+  return hi < 2700 && lo > -7000 && s.ninio >= 0;
+}
 
 int wave_threads(int nmax) { return nmax <= 128 ? 128 : (nmax <= 224 ? 256 : 512); }
 
