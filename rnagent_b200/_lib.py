@@ -10,7 +10,7 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librnafold_b200.so")
+LIB_PATH = os.environ.get("RNAFOLD_LIB") or os.path.join(_HERE, "librnafold_b200.so")
 
 EXPORTS = [
     "rnafold_init", "rnafold_shutdown", "rnafold_last_error", "rnafold_version",

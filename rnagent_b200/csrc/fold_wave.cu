@@ -43,10 +43,24 @@ __constant__ WaveConst cW;
 namespace {
 
 constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are read by phase d)
-constexpr int kParts = 3;   // loop-size ranges of the interior work items
-constexpr int kSlots = kParts * 3 + 1;
-__host__ __device__ constexpr int part_beg(int r) { return r == 0 ? 2 : r == 1 ? 18 : r == 2 ? 26 : 31; }
-__device__ __forceinline__ int part_beg_rt(int r) { return r == 0 ? 2 : r == 1 ? 18 : r == 2 ? 26 : 31; }
+#ifndef WAVE_PARTS
+#define WAVE_PARTS 3
+#endif
+#ifndef WAVE_FINE
+#define WAVE_FINE 0
+#endif
+constexpr int kParts = WAVE_PARTS;   // loop-size ranges of the interior work items
+constexpr int kSlots = kParts + 1;  // one candidate minimum per part + the tabulated shapes
+__host__ __device__ constexpr int part_beg(int r) {
+#if WAVE_PARTS == 5
+  return r == 0 ? 2 : r == 1 ? 13 : r == 2 ? 19 : r == 3 ? 23 : r == 4 ? 27 : 31;
+#elif WAVE_PARTS == 4
+  return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31;
+#else
+  return r == 0 ? 2 : r == 1 ? 18 : r == 2 ? 26 : 31;
+#endif
+}
+__device__ __forceinline__ int part_beg_rt(int r) { return part_beg(r); }
 constexpr int kMaxMlParts = 4;
 constexpr int kBig = 10000000;  // additive term that can never win a minimum
 constexpr int kFullWinMax = 128;  // up to this length the cI / c1 tables are full triangles (cheaper row offsets)
@@ -112,7 +126,7 @@ struct WaveSmem {
     L.ptab_off = take(64);
     L.S_off = take(np);
     L.db_off = take(np);
-    L.part_off = take(2 * kSlots * np * esz);       // [parity][slot][cell]; slot = part*3+class, last = tabulated
+    L.part_off = take(2 * kSlots * np * esz);       // [parity][slot][cell]; slot = part, last = tabulated shapes
     L.bt_off = L.part_off;                          // the backtrack stack reuses the scratch rows after the fill
     L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
     const int cells = table_cells(nmax) + 64;
@@ -137,18 +151,15 @@ struct WaveSmem {
 // kBig in cW.GI and never win), so the whole scan is a few KB of code that stays in the I-cache.
 // ---------------------------------------------------------------------------------------------
 template <typename ST, int W>
-__device__ __forceinline__ void generic_body(const ST *__restrict__ row, const int *__restrict__ g, int &a0, int &a1) {
+__device__ __forceinline__ void generic_body(const ST *__restrict__ row, const int *__restrict__ g, int (&a)[4]) {
 #pragma unroll
-  for (int k = 0; k < W; ++k) {
-    if (k & 1) a1 = __viaddmin_s32((int)row[k], g[k], a1);
-    else a0 = __viaddmin_s32((int)row[k], g[k], a0);
-  }
+  for (int k = 0; k < W; ++k) a[k & 3] = __viaddmin_s32((int)row[k], g[k], a[k & 3]);
 }
 
 template <typename ST, bool FULLW>
 __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const ST *__restrict__ p1,
                                               const ST *__restrict__ pB, int d, int n, int rs, int l0, int l1,
-                                              int &aI0, int &aI1, int &a1, int &aB) {
+                                              int (&aI)[4], int &a1, int &aB) {
   int off = tri(n, d - 2 - l0);      // warp-uniform: first cell of diagonal d-2-L
   int step = n - d + 3 + l0;         // off(L+1) = off(L) - step(L)
   for (int L = l0; L <= l1; ++L) {
@@ -159,13 +170,25 @@ __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const S
     aB = __viaddmin_s32((int)pB[off + L], gb, aB);
     a1 = __viaddmin_s32((int)p1[offw + 1], g1, a1);
     a1 = __viaddmin_s32((int)p1[offw + L - 1], g1, a1);
-    if (L >= 6) {
+    if (L >= 6) {  // generic shapes n1 = 2 .. L-2: smallest unrolled body that covers them
       const ST *row = pI + offi + 2;
       const int *g = &cW.GI[L][2];
-      if (L <= 9) generic_body<ST, 6>(row, g, aI0, aI1);
-      else if (L <= 17) generic_body<ST, 14>(row, g, aI0, aI1);
-      else if (L <= 25) generic_body<ST, 22>(row, g, aI0, aI1);
-      else generic_body<ST, 27>(row, g, aI0, aI1);
+#if !WAVE_FINE
+      if (L <= 9) generic_body<ST, 6>(row, g, aI);
+      else if (L <= 17) generic_body<ST, 14>(row, g, aI);
+      else if (L <= 25) generic_body<ST, 22>(row, g, aI);
+      else generic_body<ST, 27>(row, g, aI);
+#else
+      switch ((L - 3 + 3) >> 2) {
+        case 1: generic_body<ST, 4>(row, g, aI); break;
+        case 2: generic_body<ST, 8>(row, g, aI); break;
+        case 3: generic_body<ST, 12>(row, g, aI); break;
+        case 4: generic_body<ST, 16>(row, g, aI); break;
+        case 5: generic_body<ST, 20>(row, g, aI); break;
+        case 6: generic_body<ST, 24>(row, g, aI); break;
+        default: generic_body<ST, 27>(row, g, aI); break;
+      }
+#endif
     }
     off -= step;
     ++step;
@@ -323,13 +346,17 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
           const int idx = blk * 32 + lane;
           const int x = pl[pl0 + min(idx, npair - 1)];  // only cells whose ends can pair are scanned
-          int aI0 = kInfS, aI1 = kInfS, a1 = kInfS, aB = kInfS;
-          interior_item<ST, kFullW>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI0, aI1, a1, aB);
+          int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
+          interior_item<ST, kFullW>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
           if (idx < npair) {
-            ST *dst = part + ((par * kSlots + r * 3)) * np + x;
-            dst[0] = (ST)min(aI0, aI1);
-            dst[np] = (ST)a1;
-            dst[2 * np] = (ST)aB;
+            // close the three shape classes with the outer pair's terms: one candidate minimum per part
+            const int i = x + 1, j = i + d;
+            const int type = PT(S[i], S[j]);
+            const int si1 = S[i + 1], sj1 = S[j - 1];
+            int e = min(min(aI[0], aI[1]), min(aI[2], aI[3])) + __ldg(&sp.mmI[type][si1][sj1]);
+            e = min(e, a1 + __ldg(&sp.mm1nI[type][si1][sj1]));
+            e = min(e, aB + (type > 2 ? tau : 0));
+            part[(par * kSlots + r) * np + x] = (ST)min(e, kInfS);
           }
         } else if (k < nI + nT) {
           // ---------------- T(b): the 9 tabulated shapes of diagonal d
@@ -360,7 +387,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
                 }
               }
             }
-            part[(par * kSlots + kParts * 3) * np + x] = (ST)min(best, kInfS);
+            part[(par * kSlots + kParts) * np + x] = (ST)min(best, kInfS);
           }
         } else if (k < nI + nT + nM) {
           // ---------------- M(b,m): multibranch split points t0..t1-1 of diagonal d
@@ -373,17 +400,27 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           const ST *Fx = F + xc;
           int acc0 = kInf, acc1 = kInf;
           int t = t0;
-#pragma unroll 2
-          for (; t + 1 < t1; t += 2) {
-            const int oa2 = oa + sa, ob2 = ob - sb;
-            acc0 = __viaddmin_s32((int)Fx[oa], (int)Fx[ob], acc0);
-            acc1 = __viaddmin_s32((int)Fx[oa2], (int)Fx[ob2], acc1);
-            oa = oa2 + sa - 1;
-            ob = ob2 - sb - 1;
-            sa -= 2;
-            sb += 2;
+          for (; t + 4 <= t1; t += 4) {  // offsets of steps t..t+3: second-order progression, all warp-uniform
+            const int a0 = (int)Fx[oa], b0 = (int)Fx[ob];
+            const int a1 = (int)Fx[oa + sa], b1 = (int)Fx[ob - sb];
+            const int a2 = (int)Fx[oa + 2 * sa - 1], b2 = (int)Fx[ob - 2 * sb - 1];
+            const int a3 = (int)Fx[oa + 3 * sa - 3], b3 = (int)Fx[ob - 3 * sb - 3];
+            acc0 = __viaddmin_s32(a0, b0, acc0);
+            acc1 = __viaddmin_s32(a1, b1, acc1);
+            acc0 = __viaddmin_s32(a2, b2, acc0);
+            acc1 = __viaddmin_s32(a3, b3, acc1);
+            oa += 4 * sa - 6;
+            ob -= 4 * sb + 6;
+            sa -= 4;
+            sb += 4;
           }
-          if (t < t1) acc0 = __viaddmin_s32((int)Fx[oa], (int)Fx[ob], acc0);
+          for (; t < t1; ++t) {
+            acc0 = __viaddmin_s32((int)Fx[oa], (int)Fx[ob], acc0);
+            oa += sa;
+            ob -= sb;
+            --sa;
+            ++sb;
+          }
           if (x < cells_d) mlp[(par * mlparts + m) * np + x] = min(acc0, acc1);
         } else if (k < nI + nT + nM + nF) {
           // ---------------- F(b): finalise diagonal d1
@@ -400,16 +437,8 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
               cij = e_hairpin(sp, gp, S, i, j, type);
               const int np1 = nparts_of(d1, n);
               const ST *src = part + (par1 * kSlots) * np + x;
-              int pI = kInfS, p1 = kInfS, pB = kInfS;
-              for (int r = 0; r < np1; ++r) {
-                pI = min(pI, (int)src[(r * 3) * np]);
-                p1 = min(p1, (int)src[(r * 3 + 1) * np]);
-                pB = min(pB, (int)src[(r * 3 + 2) * np]);
-              }
-              cij = min(cij, pI + __ldg(&sp.mmI[type][si1][sj1]));
-              cij = min(cij, p1 + __ldg(&sp.mm1nI[type][si1][sj1]));
-              cij = min(cij, pB + (type > 2 ? tau : 0));
-              if (d1 >= 6) cij = min(cij, (int)src[(kParts * 3) * np]);
+              for (int r = 0; r < np1; ++r) cij = min(cij, (int)src[r * np]);
+              if (d1 >= 6) cij = min(cij, (int)src[kParts * np]);
               if (d1 >= 2 * kTurn + 4)
                 cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
               const int rt = rtype_of(type);
