@@ -134,7 +134,10 @@ void init_host_params(HostParams *hp) {
 const int kWaveClasses[] = {32, 48, 64, 80, 100, 128, 160, 200, 256};
 const int kLegacySmemLimit = 232;
 
-enum { kKindWave = 0, kKindLegacySmem = 1, kKindLegacyGlobal = 2 };
+const int kClusterClasses[] = {288, 320, 352, 400, 432, 464};
+const size_t kClusterWorkspaceCap = (size_t)24 << 30;  // bytes of global tables per cluster launch
+
+enum { kKindWave = 0, kKindLegacySmem = 1, kKindLegacyGlobal = 2, kKindCluster = 3 };
 struct Launch {
   int begin, end;  // slice of the length-sorted order
   int nmax;
@@ -191,9 +194,26 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     int wave_limit = 0;
     for (int k = 0; k < ncls; ++k)
       if (wave_smem_bytes(kWaveClasses[k], wave_esz) + 1024 <= (size_t)c->max_smem_optin) wave_limit = kWaveClasses[k];
+    // longest first: beyond every shared-memory design -> int32 CTA kernel with global tables
+    const int nccls = (int)(sizeof(kClusterClasses) / sizeof(int));
+    int cluster_limit = wave_limit;
+    if (wave_esz == 2)
+      for (int q = 0; q < nccls; ++q)
+        if (cluster_smem_bytes(kClusterClasses[q], 2) + 1024 <= (size_t)c->max_smem_optin) cluster_limit = kClusterClasses[q];
     int k = 0;
-    while (k < B && len_at(k) > wave_limit) ++k;
+    while (k < B && len_at(k) > cluster_limit) ++k;
     if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal});
+    // 2-CTA cluster kernel (tables split over DSMEM) for lengths above the single-CTA kernel's reach
+    for (int q = nccls - 1; q >= 0 && k < B; --q) {
+      if (kClusterClasses[q] > cluster_limit) continue;
+      const int lo = q > 0 ? std::max(kClusterClasses[q - 1], wave_limit) : wave_limit;
+      int e = k;
+      while (e < B && len_at(e) > lo) ++e;
+      const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q]) * sizeof(int16_t);
+      const int chunk = (int)std::max<size_t>(1, kClusterWorkspaceCap / per_seq);
+      for (int s0 = k; s0 < e; s0 += chunk) launches.push_back(Launch{s0, std::min(e, s0 + chunk), kClusterClasses[q], kKindCluster});
+      k = e;
+    }
     for (int cls = ncls - 1; cls >= 0 && k < B; --cls) {
       if (kWaveClasses[cls] > wave_limit) continue;
       const int lo = cls > 0 ? kWaveClasses[cls - 1] : -1;
@@ -313,6 +333,18 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
         int rc = legacy(L, a, L.nmax <= kLegacySmemLimit, d_ctl + 2 * li + 1);
         if (rc) return rc;
       }
+    } else if (L.kind == kKindCluster) {
+      const size_t stride = cluster_table_stride(L.nmax);
+      CUDA_TRY(c->d_ws.reserve(2 * stride * sizeof(int16_t) * (size_t)count));
+      int16_t *cbg = (int16_t *)c->d_ws.p, *fg = cbg + stride * (size_t)count;
+      const int ncl = std::max(1, std::min(count, cluster_max_active(L.nmax)));
+      CUDA_TRY(launch_fold_cluster(c->d_params, a, L.nmax, ncl, d_ctl + 2 * li, cbg, fg, st));
+      CUDA_TRY(launch_f5_backtrack(c->d_params, a, L.nmax, cbg, fg, st));
+      c->last_launches += 2;
+      c->last_routed[1] += count;
+      a.redo_filter = 1;  // int16 range violations -> int32 kernel with global tables
+      int rc = legacy(L, a, false, d_ctl + 2 * li + 1);
+      if (rc) return rc;
     } else {
       int rc = legacy(L, a, L.kind == kKindLegacySmem, d_ctl + 2 * li);
       if (rc) return rc;

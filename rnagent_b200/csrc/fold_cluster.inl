@@ -1,0 +1,355 @@
+// fold_cluster.inl -- long sequences: one thread-block cluster (2 CTAs on 2 SMs) per sequence.
+// Included by fold_wave.cu (same translation unit: shares cW, the table helpers and backtrack_warp).
+//
+// At n = 400 one sequence needs 157 KB for fML alone (int16), so the tables are split by ROLE across
+// the distributed shared memory of a 2-CTA cluster, and only the wavefront rows cross between them:
+//
+//   rank 0 "pair CTA"       32-diagonal windows of cB, cI, c1; interior-loop / tabulated-shape work
+//                           items over the list of pairable cells; finalises c of diagonal d-1 and
+//                           PUSHES the row  c + E_MLstem  into rank 1's shared memory (DSMEM store).
+//   rank 1 "multiloop CTA"  the full fML triangle; multibranch split work items; finalises fML of
+//                           diagonal d-2 and PUSHES the row DML (best split) into rank 0's shared memory,
+//                           where it closes multiloops two diagonals later.
+//
+// One cluster barrier per anti-diagonal orders the pushes.  Both CTAs also stream their finished
+// rows (cB, fML) to a global workspace; the exterior recursion f5, the backtrack and the Hamming
+// distance then run in a second kernel with one WARP per sequence (f5_backtrack_kernel), so the long
+// serial tail of a fold never idles a cluster.
+namespace cg = cooperative_groups;
+
+constexpr int kClusterThreads = 512;
+
+struct ClusterSmem {
+  // common
+  int misc_off, ptab_off, S_off;
+  // rank 0
+  int wB_off, wI_off, w1_off, part_off, dml_off, pl_off, plc_off;
+  // rank 1 (overlays rank 0's region)
+  int F_off, mlp_off, cst_off;
+  int total, rs, mlparts, np;
+  __host__ __device__ static ClusterSmem make(int nmax, int esz) {
+    ClusterSmem L;
+    int o = 0;
+    auto take = [&](int bytes) { int r = o; o += (bytes + 15) / 16 * 16; return r; };
+    L.np = wave_np(nmax);
+    L.rs = (nmax + 7) / 8 * 8;
+    L.mlparts = (nmax + kMlChunk - 1) / kMlChunk;
+    L.misc_off = take(64);
+    L.ptab_off = take(64);
+    L.S_off = take(L.np);
+    const int base = o;
+    L.wB_off = take((kWin * L.rs + 64) * esz);
+    L.wI_off = take((kWin * L.rs + 64) * esz);
+    L.w1_off = take((kWin * L.rs + 64) * esz);
+    L.part_off = take(2 * kSlots * L.np * esz);
+    L.dml_off = take(3 * L.np * 4);
+    L.pl_off = take(2 * L.np * 2);
+    L.plc_off = take(16);
+    const int end0 = o;
+    o = base;
+    L.F_off = take((fold_rows(L.rs) * L.rs + 64) * esz);  // folded layout, pitch rs
+    L.mlp_off = take(3 * L.mlparts * L.np * 4);
+    L.cst_off = take(2 * L.np * 4);
+    L.total = o > end0 ? o : end0;
+    return L;
+  }
+};
+
+template <typename ST>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads)
+fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *__restrict__ queue,
+                    ST *__restrict__ CBg, ST *__restrict__ Fg, long long gstride) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const ClusterSmem Ls = ClusterSmem::make(nmax, (int)sizeof(ST));
+  int *misc = reinterpret_cast<int *>(smem + Ls.misc_off);
+  unsigned char *ptab = smem + Ls.ptab_off;
+  unsigned char *S = smem + Ls.S_off;
+  ST *wB = reinterpret_cast<ST *>(smem + Ls.wB_off);
+  ST *wI = reinterpret_cast<ST *>(smem + Ls.wI_off);
+  ST *w1 = reinterpret_cast<ST *>(smem + Ls.w1_off);
+  ST *part = reinterpret_cast<ST *>(smem + Ls.part_off);
+  int *dml = reinterpret_cast<int *>(smem + Ls.dml_off);
+  unsigned short *pl = reinterpret_cast<unsigned short *>(smem + Ls.pl_off);
+  int *plc = reinterpret_cast<int *>(smem + Ls.plc_off);
+  ST *F = reinterpret_cast<ST *>(smem + Ls.F_off);
+  int *mlp = reinterpret_cast<int *>(smem + Ls.mlp_off);
+  int *cst = reinterpret_cast<int *>(smem + Ls.cst_off);
+  // the peer's copies of the rows this CTA pushes
+  int *peer_cst = cluster.map_shared_rank(cst, 1);
+  int *peer_dml = cluster.map_shared_rank(dml, 0);
+  int *peer_misc = cluster.map_shared_rank(misc, 1);
+  const int np = Ls.np, rs = Ls.rs, mlparts = Ls.mlparts;
+  const int tid = threadIdx.x, lane = tid & 31, NW = kClusterThreads >> 5, NT = kClusterThreads;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const SmallParams &sp = gp->s;
+  constexpr int kInfS = Store<ST>::kInfS;
+  const int tau = cW.TerminalAU;
+
+  if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
+  auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
+  auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
+
+  for (;;) {
+    cluster.sync();
+    if (rank == 0 && tid == 0) {
+      const int s = atomicAdd(queue, 1);
+      misc[0] = s;
+      peer_misc[0] = s;
+    }
+    cluster.sync();
+    const int slot = misc[0];
+    if (slot >= a.B) break;
+    const int b = a.order ? a.order[slot] : slot;
+    const int beg = a.off[b];
+    const int n = a.off[b + 1] - beg;
+    ST *cbg = CBg + (long long)slot * gstride;
+    ST *fg = Fg + (long long)slot * gstride;
+    int flag = 0;
+
+    for (int k = tid; k < n; k += NT) S[k + 1] = (unsigned char)enc_base(a.seq[beg + k]);
+    __syncthreads();
+    if (tid == 0 && n > 0) {
+      S[0] = S[n];
+      S[n + 1] = S[1];
+    }
+    cluster.sync();
+
+    for (int d = kTurn + 1; d <= n + 1; ++d) {
+      const int par = d & 1, par1 = par ^ 1;
+      const int cells_d = (d < n) ? n - d : 0;
+      const int nb_d = (cells_d + 31) >> 5;
+      const int lmax = min(kMaxLoop, d - 6);
+      if (rank == 0) {
+        // ================= pair CTA
+        const int npd = nparts_of(d, n);
+        const int d1 = d - 1;
+        const int cells_1 = (d1 >= kTurn + 1 && d1 < n) ? n - d1 : 0;
+        const int nb_1 = (cells_1 + 31) >> 5;
+        const int npair = (lmax >= 0 && d < n) ? plc[par] : 0;
+        const unsigned short *pld = pl + par * np;
+        const int nbI = (npair + 31) >> 5;
+        const int nP = (d + 1 < n && d + 1 >= 6) ? 1 : 0;
+        const int nI = nbI * npd, nT = (lmax >= 0) ? nbI : 0, nF = nb_1;
+        const int total = nI + nT + nF + nP;
+        for (int k = warp; k < total; k += NW) {
+          if (k < nI) {
+            // ---- I(b,r)
+            const int r = div_small(k, nbI, kParts), blk = k - r * nbI;
+            const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
+            const int idx = blk * 32 + lane;
+            const int x = pld[min(idx, npair - 1)];
+            int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
+            interior_item<ST, false, true>(wI + x + 1, w1 + x + 1, wB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
+            if (idx < npair) {
+              const int i = x + 1, j = i + d;
+              const int type = PT(S[i], S[j]);
+              const int si1 = S[i + 1], sj1 = S[j - 1];
+              int e = min(min(aI[0], aI[1]), min(aI[2], aI[3])) + __ldg(&sp.mmI[type][si1][sj1]);
+              e = min(e, a1 + __ldg(&sp.mm1nI[type][si1][sj1]));
+              e = min(e, aB + (type > 2 ? tau : 0));
+              part[(par * kSlots + r) * np + x] = (ST)min(e, kInfS);
+            }
+          } else if (k < nI + nT) {
+            // ---- T(b): tabulated shapes, inner pairs from the cB window
+            const int idx = (k - nI) * 32 + lane;
+            if (idx < npair) {
+              const int x = pld[idx];
+              const int i = x + 1, j = i + d;
+              const int type = PT(S[i], S[j]);
+              int best = kInfS;
+              int si[5], sj[5];
+#pragma unroll
+              for (int u = 0; u < 5; ++u) {
+                si[u] = S[i + u];
+                sj[u] = S[j - u];
+              }
+#pragma unroll
+              for (int s = 0; s < 9; ++s) {
+                constexpr int kN1[9] = {0, 0, 1, 1, 1, 2, 2, 2, 3};
+                constexpr int kN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
+                const int n1 = kN1[s], n2 = kN2[s];
+                if (n1 + n2 <= d - 6) {
+                  const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
+                  if (t2) {
+                    const int cpq = craw((int)wB[((d - 2 - n1 - n2) & (kWin - 1)) * rs + x + 1 + n1], t2);
+                    best = min(best, cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]));
+                  }
+                }
+              }
+              part[(par * kSlots + kParts) * np + x] = (ST)min(best, kInfS);
+            }
+          } else if (k < nI + nT + nF) {
+            // ---- Fp(b): finalise c of diagonal d1, push c + E_MLstem to the multiloop CTA
+            const int x = (k - nI - nT) * 32 + lane;
+            if (x < cells_1) {
+              const int i = x + 1, j = i + d1;
+              const int type = PT(S[i], S[j]);
+              const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+              const int wrow = (d1 & (kWin - 1)) * rs + x;
+              int stem = kInf;
+              ST cb = (ST)kInfS;
+              if (type) {
+                int cij = e_hairpin(sp, gp, S, i, j, type);
+                const int np1 = nparts_of(d1, n);
+                const ST *src = part + (par1 * kSlots) * np + x;
+                for (int r = 0; r < np1; ++r) cij = min(cij, (int)src[r * np]);
+                if (d1 >= 6) cij = min(cij, (int)src[kParts * np]);
+                if (d1 >= 2 * kTurn + 4)
+                  cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
+                const int rt = rtype_of(type);
+                cb = put<ST>(cij + (type > 2 ? tau : 0), flag);
+                wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
+                w1[wrow] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
+                stem = cij + e_mlstem(sp, type, sim1, sjp1);
+              } else {
+                wI[wrow] = (ST)kInfS;
+                w1[wrow] = (ST)kInfS;
+              }
+              wB[wrow] = cb;
+              cbg[tri(n, d1) + x] = cb;
+              peer_cst[(d1 & 1) * np + x] = stem;
+            }
+          } else {
+            // ---- P: list of the pairable cells of diagonal d+1 (used by the next phase)
+            const int dn = d + 1, cells_n = n - dn;
+            unsigned short *dst = pl + par1 * np;
+            int pos = 0;
+            for (int base = 0; base < cells_n; base += 32) {
+              const int x = base + lane;
+              const bool pr = x < cells_n && PT(S[x + 1], S[x + 1 + dn]) != 0;
+              const unsigned m = __ballot_sync(0xffffffffu, pr);
+              if (pr) dst[pos + __popc(m & ((1u << lane) - 1u))] = (unsigned short)x;
+              pos += __popc(m);
+            }
+            if (lane == 0) plc[par1] = pos;
+          }
+        }
+      } else {
+        // ================= multiloop CTA
+        const int mpd = mlparts_of(d, n);
+        const int d2 = d - 2;
+        const int cells_2 = (d2 >= kTurn + 1 && d2 < n) ? n - d2 : 0;
+        const int nb_2 = (cells_2 + 31) >> 5;
+        const int nM = nb_d * mpd;
+        const int total = nM + nb_2;
+        for (int k = warp; k < total; k += NW) {
+          if (k < nM) {
+            // ---- M(b,m)
+            const int m = (mpd == 1) ? 0 : div_small(k, nb_d, kMaxMlParts), blk = k - m * nb_d;
+            const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
+            const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
+            const int best = split_scan<ST>(F, rs, d, xc, t0, t1);
+            if (x < cells_d) mlp[((d % 3) * mlparts + m) * np + x] = best;
+          } else {
+            // ---- Fm(b): finalise fML of diagonal d2, push DML to the pair CTA
+            const int x = (k - nM) * 32 + lane;
+            if (x < cells_2) {
+              int e = kInf;
+              if (d2 > kTurn + 1) {
+                const int pb = fold_idx(rs, d2 - 1, x);
+                e = min((int)F[pb + 1], (int)F[pb]) + cW.MLbase;
+              }
+              e = min(e, cst[(d2 & 1) * np + x]);
+              int dm = kInf;
+              const int mp2 = mlparts_of(d2, n);
+              for (int m = 0; m < mp2; ++m) dm = min(dm, mlp[((d2 % 3) * mlparts + m) * np + x]);
+              peer_dml[(d2 % 3) * np + x] = dm;
+              const ST f = put<ST>(min(e, dm), flag);
+              F[fold_idx(rs, d2, x)] = f;
+              fg[tri(n, d2) + x] = f;
+            }
+          }
+        }
+      }
+      cluster.sync();
+    }
+    if (Store<ST>::kChecked && flag && a.redo) a.redo[b] = 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// f5 + backtrack + Hamming/reward from the global tables: one warp per sequence.
+// ---------------------------------------------------------------------------------------------
+constexpr int kBtWarps = 4;
+
+__host__ __device__ inline int bt_warp_bytes(int nmax) {
+  const int np = wave_np(nmax);
+  return ((np * 4 + 15) / 16 * 16) * 2 + ((np + 15) / 16 * 16) * 2;  // f5, bt (int) + S, db (bytes)
+}
+
+template <typename ST>
+__global__ void __launch_bounds__(kBtWarps * 32)
+f5_backtrack_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, const ST *__restrict__ CBg,
+                    const ST *__restrict__ Fg, long long gstride) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = blockIdx.x * kBtWarps + warp;
+  if (slot >= a.B) return;
+  const int b = a.order ? a.order[slot] : slot;
+  if (a.redo && a.redo[b]) return;  // left to the int32 re-run
+  const int np = wave_np(nmax);
+  unsigned char *base = smem + (size_t)warp * bt_warp_bytes(nmax);
+  int *f5 = reinterpret_cast<int *>(base);
+  int *bt = f5 + ((np * 4 + 15) / 16 * 16) / 4;
+  unsigned char *S = reinterpret_cast<unsigned char *>(bt) + (np * 4 + 15) / 16 * 16;
+  unsigned char *db = S + (np + 15) / 16 * 16;
+  const SmallParams &sp = gp->s;
+  const int tau = cW.TerminalAU;
+  const int beg = a.off[b];
+  const int n = a.off[b + 1] - beg;
+  const ST *CB = CBg + (long long)slot * gstride;
+  const ST *F = Fg + (long long)slot * gstride;
+
+  for (int k = lane; k < n; k += 32) {
+    S[k + 1] = (unsigned char)enc_base(a.seq[beg + k]);
+    db[k] = '.';
+  }
+  for (int k = lane; k <= n; k += 32) f5[k] = 0;
+  __syncwarp();
+  if (lane == 0 && n > 0) {
+    S[0] = S[n];
+    S[n + 1] = S[1];
+  }
+  __syncwarp();
+  for (int j = kTurn + 2; j <= n; ++j) {
+    const int s3 = (j < n) ? (int)S[j + 1] : -1;
+    int best = kInf;
+    for (int i = j - kTurn - 1 - lane; i >= 1; i -= 32) {
+      const int type = pair_type(S[i], S[j]);
+      if (!type) continue;
+      const int c = (int)CB[tri(n, j - i) + i - 1] - (type > 2 ? tau : 0);
+      best = min(best, f5[i - 1] + c + e_extloop(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
+    }
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) f5[j] = min(f5[j - 1], best);
+    __syncwarp();
+  }
+  const int failc = backtrack_warp<ST, false>(n, S, f5, CB, F, 0, bt, db, gp, lane);
+  __syncwarp();
+
+  int hd = 0;
+  for (int k = lane; k < n; k += 32) {
+    const unsigned char ch = db[k];
+    if (a.db) a.db[beg + k] = ch;
+    if (a.target) {
+      const int mm = a.target[beg + k] != ch;
+      hd += mm;
+      if (a.mismatch) a.mismatch[beg + k] = (unsigned char)mm;
+    }
+  }
+  for (int o = 16; o; o >>= 1) hd += __shfl_xor_sync(0xffffffffu, hd, o);
+  if (lane == 0) {
+    if (a.mfe) a.mfe[b] = (n > 0) ? f5[n] : 0;
+    if (a.target) {
+      if (a.hd) a.hd[b] = hd;
+      if (a.reward) {
+        double r = (n > 0) ? pow(1.0 - (double)hd / (double)n, a.reward_exp) : 0.0;
+        if (hd == 0) r += 0.25;
+        a.reward[b] = r;
+      }
+    }
+    if (failc) atomicExch(a.status, failc);
+  }
+}

@@ -44,6 +44,16 @@ cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st);
 cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax, int esz, int grid, int threads,
                              int *queue, cudaStream_t st);
 
+// cluster path for long sequences: 2-CTA cluster per sequence (DSMEM row exchange) + warp-per-sequence
+// f5/backtrack kernel over the global tables (int16 tables; cluster_table_stride elements per table)
+size_t cluster_smem_bytes(int nmax, int esz);
+size_t cluster_table_stride(int nmax);
+int cluster_max_active(int nmax);
+cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nmax, int num_clusters, int *queue,
+                                void *cbg, void *fg, cudaStream_t st);
+cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
+                                cudaStream_t st);
+
 // peaks.cu: on-box shared-memory-load and min-plus (ALU) peak rates, whole device, per second
 cudaError_t measure_onchip_peaks(int num_sms, cudaStream_t st, double *lds_per_s, double *minplus_per_s);
 

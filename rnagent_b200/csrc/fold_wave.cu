@@ -21,6 +21,7 @@
 // Replaces ViennaRNA 2.4.14 fill_arrays + backtrack behind `RNA.fold` (rlif/settings.py:63-64;
 // recursions SURVEY.md 8a' F3-F7), fused with hamming_distance (rlif/rna/utils.py:67-75) and the
 // reward of Solution.evaluate (rlif/rna/solution.py:145-148).
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -87,6 +88,52 @@ __device__ __forceinline__ int tri(int n, int d) {
   return k * (n - 4) - (k * (k - 1)) / 2;
 }
 
+// fML lives in a FOLDED diagonal-major layout with a fixed row pitch rp (a function of the launch's
+// length class only, hence warp-uniform and known at kernel entry): row r holds diagonal r followed
+// by diagonal rp+4-r, so the triangle still packs into ~rp*rp/2 cells, but stepping from one diagonal
+// to the next is a CONSTANT stride (+rp, or 1-rp in the folded half).  The multibranch split scan
+// min_t fML(i,i+t) + fML(i+t+1,j) walks both operands diagonal by diagonal, so with this layout its
+// addresses are base + k*stride and the loop body is 2 LDS + 1 VIADDMNMX per candidate.
+__host__ __device__ __forceinline__ int fold_rows(int rp) { return rp / 2 - 1; }
+__device__ __forceinline__ int fold_idx(int rp, int t, int x) {
+  return (t <= rp / 2 + 2) ? (t - 4) * rp + x : (rp - t) * rp + (t - 4) + x;
+}
+
+template <typename ST, bool UPA, bool UPB>
+__device__ __forceinline__ void split_run(const ST *__restrict__ pa, const ST *__restrict__ pb, int cnt, int rp,
+                                          int &acc0, int &acc1) {
+  const int sA = UPA ? rp : 1 - rp, sB = UPB ? rp : 1 - rp;
+  int k = 0;
+  for (; k + 8 <= cnt; k += 8) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (u & 1) acc1 = __viaddmin_s32((int)pa[u * sA], (int)pb[u * sB], acc1);
+      else acc0 = __viaddmin_s32((int)pa[u * sA], (int)pb[u * sB], acc0);
+    }
+    pa += 8 * sA;
+    pb += 8 * sB;
+  }
+  for (; k < cnt; ++k) {
+    acc0 = __viaddmin_s32((int)*pa, (int)*pb, acc0);
+    pa += sA;
+    pb += sB;
+  }
+}
+
+// min over split points t in [t0, t1) of fML(diag t, x) + fML(diag d-1-t, x+t+1) for the lane's cell x
+template <typename ST>
+__device__ __forceinline__ int split_scan(const ST *__restrict__ F, int rp, int d, int x, int t0, int t1) {
+  const int T0 = rp / 2 + 2;
+  int acc0 = kInf, acc1 = kInf;
+  // operand B = diagonal d-1-t sits in the folded half while t < d-1-T0; operand A (diagonal t) while t > T0
+  const int tb = min(max(d - 1 - T0, t0), t1);  // [t0, tb): A plain, B folded
+  const int ta = min(max(T0 + 1, tb), t1);      // [tb, ta): both plain; [ta, t1): A folded, B plain
+  if (tb > t0) split_run<ST, true, true>(F + fold_idx(rp, t0, x), F + fold_idx(rp, d - 1 - t0, x + t0 + 1), tb - t0, rp, acc0, acc1);
+  if (ta > tb) split_run<ST, true, false>(F + fold_idx(rp, tb, x), F + fold_idx(rp, d - 1 - tb, x + tb + 1), ta - tb, rp, acc0, acc1);
+  if (t1 > ta) split_run<ST, false, false>(F + fold_idx(rp, ta, x), F + fold_idx(rp, d - 1 - ta, x + ta + 1), t1 - ta, rp, acc0, acc1);
+  return min(acc0, acc1);
+}
+
 __device__ __forceinline__ int enc_base(unsigned char ch) {
   switch (ch) {
     case 'A': case 'a': return 1;
@@ -131,7 +178,7 @@ struct WaveSmem {
     L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
     const int cells = table_cells(nmax) + 64;
     L.C_off = take(cells * esz);
-    L.F_off = take(cells * esz);
+    L.F_off = take((fold_rows(L.rs) * L.rs + 64) * esz);  // folded layout, pitch rs
     const int wcells = nmax <= kFullWinMax ? cells : kWin * L.rs + 64;
     L.wI_off = take(wcells * esz);
     L.w1_off = take((kWin * L.rs + 64) * esz);  // c1 is only read at the two ends of a row: always a window
@@ -156,7 +203,7 @@ __device__ __forceinline__ void generic_body(const ST *__restrict__ row, const i
   for (int k = 0; k < W; ++k) a[k & 3] = __viaddmin_s32((int)row[k], g[k], a[k & 3]);
 }
 
-template <typename ST, bool FULLW>
+template <typename ST, bool FULLW, bool BWIN = false>
 __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const ST *__restrict__ p1,
                                               const ST *__restrict__ pB, int d, int n, int rs, int l0, int l1,
                                               int (&aI)[4], int &a1, int &aB) {
@@ -166,8 +213,9 @@ __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const S
     const int offw = ((d - 2 - L) & (kWin - 1)) * rs;
     const int offi = FULLW ? off : offw;
     const int gb = cW.GB[L], g1 = cW.G1[L];
-    aB = __viaddmin_s32((int)pB[off], gb, aB);
-    aB = __viaddmin_s32((int)pB[off + L], gb, aB);
+    const int offb = BWIN ? offw : off;
+    aB = __viaddmin_s32((int)pB[offb], gb, aB);
+    aB = __viaddmin_s32((int)pB[offb + L], gb, aB);
     a1 = __viaddmin_s32((int)p1[offw + 1], g1, a1);
     a1 = __viaddmin_s32((int)p1[offw + L - 1], g1, a1);
     if (L >= 6) {  // generic shapes n1 = 2 .. L-2: smallest unrolled body that covers them
@@ -220,6 +268,174 @@ __device__ __forceinline__ int div_small(int k, int nb, int qmax) {
   int q = 0;
   for (int t = 1; t < qmax; ++t) q += (k >= t * nb) ? 1 : 0;
   return q;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backtrack in ViennaRNA's deterministic order (SURVEY.md 8a' F7), run by ONE warp: the sector
+// stack is warp-uniform and the lanes probe the candidates of each decision in ViennaRNA's scan
+// order, the first hit (ballot + ffs) wins.  Tables may live in shared or global memory.
+// Returns 0 or a failure code (no decomposition found -- would mean a fill error).
+// ---------------------------------------------------------------------------------------------
+template <typename ST, bool FOLDED>
+__device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, const ST *CB, const ST *F, int rp, int *bt,
+                              unsigned char *db, const FoldParams *__restrict__ gp, int lane) {
+  const SmallParams &sp = gp->s;
+  auto fx = [&](int t, int x) -> int { return FOLDED ? fold_idx(rp, t, x) : tri(n, t) + x; };
+  const int tau = cW.TerminalAU;
+  auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
+  const unsigned full = 0xffffffffu;
+  int top = 0, failc = 0;
+  if (n > 0) {
+    if (lane == 0) bt[0] = (1 << 14) | (n << 2) | 0;
+    top = 1;
+  }
+  __syncwarp();
+  while (top > 0 && !failc) {
+    const int w = bt[--top];
+    __syncwarp();
+    int i = w >> 14, j = (w >> 2) & 0xfff;
+    const int ml = w & 3;
+    if (ml == 0) {
+      // largest jj <= j with f5[jj] != f5[jj-1]
+      int jj = 0;
+      for (int base = j; base >= 1 && !jj; base -= 32) {
+        const int k = base - lane;
+        const unsigned m = __ballot_sync(full, k >= 1 && f5[k] != f5[k - 1]);
+        if (m) jj = base - (__ffs(m) - 1);
+      }
+      if (jj < kTurn + 2) continue;
+      const int fij = f5[jj];
+      const int s3 = (jj < n) ? (int)S[jj + 1] : -1;
+      int u = 0;
+      for (int base = jj - kTurn - 1; base >= 1 && !u; base -= 32) {
+        const int k = base - lane;
+        bool hit = false;
+        if (k >= 1) {
+          const int type = pair_type(S[k], S[jj]);
+          if (type) {
+            const int e = craw((int)CB[tri(n, jj - k) + k - 1], type) + e_extloop(sp, type, k > 1 ? (int)S[k - 1] : -1, s3);
+            hit = (fij == e + f5[k - 1]);
+          }
+        }
+        const unsigned m = __ballot_sync(full, hit);
+        if (m) u = base - (__ffs(m) - 1);
+      }
+      if (!u) { failc = 1; break; }
+      if (u - 1 > 0) {
+        if (lane == 0) bt[top] = (1 << 14) | ((u - 1) << 2) | 0;
+        top++;
+      }
+      i = u;
+      j = jj;
+    } else {
+      // fML sector: strip 3' bases, then 5' bases, then stem or split
+      int ii = i, jj = 0;
+      for (int base = j; base >= ii + kTurn + 1 && !jj; base -= 32) {
+        const int k = base - lane;
+        bool stop = false;
+        if (k >= ii + kTurn + 1) {
+          const int fij = (int)F[fx(k - ii, ii - 1)];
+          const int fi = (k - 1 - ii > kTurn) ? (int)F[fx(k - 1 - ii, ii - 1)] + cW.MLbase : kInf;
+          stop = (fij != fi);
+        }
+        const unsigned m = __ballot_sync(full, stop);
+        if (m) jj = base - (__ffs(m) - 1);
+      }
+      if (!jj) { failc = 2; break; }
+      int i2 = 0;
+      for (int base = ii; base <= jj - kTurn - 1 && !i2; base += 32) {
+        const int k = base + lane;
+        bool stop = false;
+        if (k <= jj - kTurn - 1) {
+          const int fij = (int)F[fx(jj - k, k - 1)];
+          const int fi = (jj - k - 1 > kTurn) ? (int)F[fx(jj - k - 1, k)] + cW.MLbase : kInf;
+          stop = (fij != fi);
+        }
+        const unsigned m = __ballot_sync(full, stop);
+        if (m) i2 = base + (__ffs(m) - 1);
+      }
+      if (!i2) { failc = 2; break; }
+      ii = i2;
+      const int fij = (int)F[fx(jj - ii, ii - 1)];
+      const int type = pair_type(S[ii], S[jj]);
+      if (type && fij == craw((int)CB[tri(n, jj - ii) + ii - 1], type) + e_mlstem(sp, type, S[ii - 1], S[jj + 1])) {
+        i = ii;
+        j = jj;
+      } else {
+        int u = 0;
+        for (int base = ii + 1 + kTurn; base <= jj - 2 - kTurn && !u; base += 32) {
+          const int k = base + lane;
+          bool hit = false;
+          if (k <= jj - 2 - kTurn)
+            hit = (fij == (int)F[fx(k - ii, ii - 1)] + (int)F[fx(jj - k - 1, k)]);
+          const unsigned m = __ballot_sync(full, hit);
+          if (m) u = base + (__ffs(m) - 1);
+        }
+        if (!u) { failc = 3; break; }
+        if (lane == 0) {
+          bt[top] = (ii << 14) | (u << 2) | 1;
+          bt[top + 1] = ((u + 1) << 14) | (jj << 2) | 1;
+        }
+        top += 2;
+        __syncwarp();
+        continue;
+      }
+    }
+    // (i,j) pairs: walk down the helix / interior loops until a hairpin or a multiloop
+    for (;;) {
+      if (lane == 0) {
+        db[i - 1] = '(';
+        db[j - 1] = ')';
+      }
+      const int d = j - i;
+      const int type = pair_type(S[i], S[j]);
+      const int cij = craw((int)CB[tri(n, d) + i - 1], type);
+      if (cij == e_hairpin(sp, gp, S, i, j, type)) break;
+      const int si1 = S[i + 1], sj1 = S[j - 1];
+      bool found = false;
+      const int amax = min(kMaxLoop, d - 6);
+      for (int n1 = 0; n1 <= amax && !found; ++n1) {
+        const int p = i + 1 + n1;
+        const int bmax = min(kMaxLoop - n1, d - 6 - n1);
+        const int n2 = lane, q = j - 1 - n2;
+        bool hit = false;
+        if (n2 <= bmax) {
+          const int t2 = pair_type(S[p], S[q]);
+          if (t2) {
+            const int e = craw((int)CB[tri(n, q - p) + p - 1], t2) +
+                          e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si1, sj1, S[p - 1], S[q + 1]);
+            hit = (e == cij);
+          }
+        }
+        const unsigned m = __ballot_sync(full, hit);
+        if (m) {
+          i = p;
+          j = j - 1 - (__ffs(m) - 1);
+          found = true;
+        }
+      }
+      if (found) continue;
+      const int e = cij - e_mlstem(sp, rtype_of(type), sj1, si1) - cW.MLclosing;
+      const int p = i + 1, q = j - 1;
+      int u = 0;
+      for (int base = p + kTurn + 1; base < q - kTurn - 1 && !u; base += 32) {
+        const int k = base + lane;
+        bool hit = false;
+        if (k < q - kTurn - 1) hit = (e == (int)F[fx(k - p, p - 1)] + (int)F[fx(q - k - 1, k)]);
+        const unsigned m = __ballot_sync(full, hit);
+        if (m) u = base + (__ffs(m) - 1);
+      }
+      if (!u) { failc = 4; break; }
+      if (lane == 0) {
+        bt[top] = (p << 14) | (u << 2) | 1;
+        bt[top + 1] = ((u + 1) << 14) | (q << 2) | 1;
+      }
+      top += 2;
+      break;
+    }
+    __syncwarp();
+  }
+  return failc;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -395,33 +611,8 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
           const int m = (mpd == 1) ? 0 : div_small(kk, nb_d, kMaxMlParts), blk = kk - m * nb_d;
           const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
           const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
-          int oa = tri(n, t0), ob = tri(n, d - 1 - t0) + t0 + 1;  // warp-uniform offsets
-          int sa = n - t0, sb = n - (d - 1 - t0);
-          const ST *Fx = F + xc;
-          int acc0 = kInf, acc1 = kInf;
-          int t = t0;
-          for (; t + 4 <= t1; t += 4) {  // offsets of steps t..t+3: second-order progression, all warp-uniform
-            const int a0 = (int)Fx[oa], b0 = (int)Fx[ob];
-            const int a1 = (int)Fx[oa + sa], b1 = (int)Fx[ob - sb];
-            const int a2 = (int)Fx[oa + 2 * sa - 1], b2 = (int)Fx[ob - 2 * sb - 1];
-            const int a3 = (int)Fx[oa + 3 * sa - 3], b3 = (int)Fx[ob - 3 * sb - 3];
-            acc0 = __viaddmin_s32(a0, b0, acc0);
-            acc1 = __viaddmin_s32(a1, b1, acc1);
-            acc0 = __viaddmin_s32(a2, b2, acc0);
-            acc1 = __viaddmin_s32(a3, b3, acc1);
-            oa += 4 * sa - 6;
-            ob -= 4 * sb + 6;
-            sa -= 4;
-            sb += 4;
-          }
-          for (; t < t1; ++t) {
-            acc0 = __viaddmin_s32((int)Fx[oa], (int)Fx[ob], acc0);
-            oa += sa;
-            ob -= sb;
-            --sa;
-            ++sb;
-          }
-          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = min(acc0, acc1);
+          const int best = split_scan<ST>(F, rs, d, xc, t0, t1);
+          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = best;
         } else if (k < nI + nT + nM + nF) {
           // ---------------- F(b): finalise diagonal d1
           const int blk = k - nI - nT - nM;
@@ -452,7 +643,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             }
             int e = kInf;
             if (d1 > kTurn + 1) {
-              const int pb = tri(n, d1 - 1) + x;
+              const int pb = fold_idx(rs, d1 - 1, x);
               e = min((int)F[pb + 1], (int)F[pb]) + cW.MLbase;
             }
             if (type) e = min(e, cij + e_mlstem(sp, type, sim1, sjp1));
@@ -460,7 +651,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             const int mp1 = mlparts_of(d1, n);
             for (int m = 0; m < mp1; ++m) dm = min(dm, mlp[(par1 * mlparts + m) * np + x]);
             dml[(d1 % 3) * np + x] = dm;
-            F[tri(n, d1) + x] = put<ST>(min(e, dm), flag);
+            F[fold_idx(rs, d1, x)] = put<ST>(min(e, dm), flag);
           }
         } else {
           // ---------------- X: f5[d1]
@@ -485,158 +676,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
 
     // ---- backtrack (ViennaRNA's deterministic order); warp 0, lanes scan candidates in that order
     if (warp == 0 && !misc[3]) {
-      const unsigned full = 0xffffffffu;
-      int top = 0, failc = 0;
-      if (n > 0) {
-        if (lane == 0) bt[0] = (1 << 14) | (n << 2) | 0;
-        top = 1;
-      }
-      __syncwarp();
-      while (top > 0 && !failc) {
-        const int w = bt[--top];
-        __syncwarp();
-        int i = w >> 14, j = (w >> 2) & 0xfff;
-        const int ml = w & 3;
-        if (ml == 0) {
-          // largest jj <= j with f5[jj] != f5[jj-1]
-          int jj = 0;
-          for (int base = j; base >= 1 && !jj; base -= 32) {
-            const int k = base - lane;
-            const unsigned m = __ballot_sync(full, k >= 1 && f5[k] != f5[k - 1]);
-            if (m) jj = base - (__ffs(m) - 1);
-          }
-          if (jj < kTurn + 2) continue;
-          const int fij = f5[jj];
-          const int s3 = (jj < n) ? (int)S[jj + 1] : -1;
-          int u = 0;
-          for (int base = jj - kTurn - 1; base >= 1 && !u; base -= 32) {
-            const int k = base - lane;
-            bool hit = false;
-            if (k >= 1) {
-              const int type = pair_type(S[k], S[jj]);
-              if (type) {
-                const int e = craw((int)CB[tri(n, jj - k) + k - 1], type) + e_extloop(sp, type, k > 1 ? (int)S[k - 1] : -1, s3);
-                hit = (fij == e + f5[k - 1]);
-              }
-            }
-            const unsigned m = __ballot_sync(full, hit);
-            if (m) u = base - (__ffs(m) - 1);
-          }
-          if (!u) { failc = 1; break; }
-          if (u - 1 > 0) {
-            if (lane == 0) bt[top] = (1 << 14) | ((u - 1) << 2) | 0;
-            top++;
-          }
-          i = u;
-          j = jj;
-        } else {
-          // fML sector: strip 3' bases, then 5' bases, then stem or split
-          int ii = i, jj = 0;
-          for (int base = j; base >= ii + kTurn + 1 && !jj; base -= 32) {
-            const int k = base - lane;
-            bool stop = false;
-            if (k >= ii + kTurn + 1) {
-              const int fij = (int)F[tri(n, k - ii) + ii - 1];
-              const int fi = (k - 1 - ii > kTurn) ? (int)F[tri(n, k - 1 - ii) + ii - 1] + cW.MLbase : kInf;
-              stop = (fij != fi);
-            }
-            const unsigned m = __ballot_sync(full, stop);
-            if (m) jj = base - (__ffs(m) - 1);
-          }
-          if (!jj) { failc = 2; break; }
-          int i2 = 0;
-          for (int base = ii; base <= jj - kTurn - 1 && !i2; base += 32) {
-            const int k = base + lane;
-            bool stop = false;
-            if (k <= jj - kTurn - 1) {
-              const int fij = (int)F[tri(n, jj - k) + k - 1];
-              const int fi = (jj - k - 1 > kTurn) ? (int)F[tri(n, jj - k - 1) + k] + cW.MLbase : kInf;
-              stop = (fij != fi);
-            }
-            const unsigned m = __ballot_sync(full, stop);
-            if (m) i2 = base + (__ffs(m) - 1);
-          }
-          if (!i2) { failc = 2; break; }
-          ii = i2;
-          const int fij = (int)F[tri(n, jj - ii) + ii - 1];
-          const int type = pair_type(S[ii], S[jj]);
-          if (type && fij == craw((int)CB[tri(n, jj - ii) + ii - 1], type) + e_mlstem(sp, type, S[ii - 1], S[jj + 1])) {
-            i = ii;
-            j = jj;
-          } else {
-            int u = 0;
-            for (int base = ii + 1 + kTurn; base <= jj - 2 - kTurn && !u; base += 32) {
-              const int k = base + lane;
-              bool hit = false;
-              if (k <= jj - 2 - kTurn)
-                hit = (fij == (int)F[tri(n, k - ii) + ii - 1] + (int)F[tri(n, jj - k - 1) + k]);
-              const unsigned m = __ballot_sync(full, hit);
-              if (m) u = base + (__ffs(m) - 1);
-            }
-            if (!u) { failc = 3; break; }
-            if (lane == 0) {
-              bt[top] = (ii << 14) | (u << 2) | 1;
-              bt[top + 1] = ((u + 1) << 14) | (jj << 2) | 1;
-            }
-            top += 2;
-            __syncwarp();
-            continue;
-          }
-        }
-        // (i,j) pairs: walk down the helix / interior loops until a hairpin or a multiloop
-        for (;;) {
-          if (lane == 0) {
-            db[i - 1] = '(';
-            db[j - 1] = ')';
-          }
-          const int d = j - i;
-          const int type = pair_type(S[i], S[j]);
-          const int cij = craw((int)CB[tri(n, d) + i - 1], type);
-          if (cij == e_hairpin(sp, gp, S, i, j, type)) break;
-          const int si1 = S[i + 1], sj1 = S[j - 1];
-          bool found = false;
-          const int amax = min(kMaxLoop, d - 6);
-          for (int n1 = 0; n1 <= amax && !found; ++n1) {
-            const int p = i + 1 + n1;
-            const int bmax = min(kMaxLoop - n1, d - 6 - n1);
-            const int n2 = lane, q = j - 1 - n2;
-            bool hit = false;
-            if (n2 <= bmax) {
-              const int t2 = pair_type(S[p], S[q]);
-              if (t2) {
-                const int e = craw((int)CB[tri(n, q - p) + p - 1], t2) +
-                              e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si1, sj1, S[p - 1], S[q + 1]);
-                hit = (e == cij);
-              }
-            }
-            const unsigned m = __ballot_sync(full, hit);
-            if (m) {
-              i = p;
-              j = j - 1 - (__ffs(m) - 1);
-              found = true;
-            }
-          }
-          if (found) continue;
-          const int e = cij - e_mlstem(sp, rtype_of(type), sj1, si1) - cW.MLclosing;
-          const int p = i + 1, q = j - 1;
-          int u = 0;
-          for (int base = p + kTurn + 1; base < q - kTurn - 1 && !u; base += 32) {
-            const int k = base + lane;
-            bool hit = false;
-            if (k < q - kTurn - 1) hit = (e == (int)F[tri(n, k - p) + p - 1] + (int)F[tri(n, q - k - 1) + k]);
-            const unsigned m = __ballot_sync(full, hit);
-            if (m) u = base + (__ffs(m) - 1);
-          }
-          if (!u) { failc = 4; break; }
-          if (lane == 0) {
-            bt[top] = (p << 14) | (u << 2) | 1;
-            bt[top + 1] = ((u + 1) << 14) | (q << 2) | 1;
-          }
-          top += 2;
-          break;
-        }
-        __syncwarp();
-      }
+      const int failc = backtrack_warp<ST, true>(n, S, f5, CB, F, rs, bt, db, gp, lane);
       if (lane == 0 && failc) misc[1] = failc;
     }
     __syncthreads();
@@ -673,6 +713,8 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
     }
   }
 }
+
+#include "fold_cluster.inl"
 
 }  // namespace
 
@@ -754,5 +796,56 @@ cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax,
 }
 
 int wave_occupancy(int nmax, int esz, int threads) { return WAVE_DISPATCH(occupancy_t, nmax); }
+
+// ---- cluster path (long sequences)
+size_t cluster_smem_bytes(int nmax, int esz) { return (size_t)ClusterSmem::make(nmax, esz).total; }
+size_t cluster_table_stride(int nmax) { return (size_t)(table_cells(nmax) + 64) / 8 * 8; }  // elements per table per sequence
+
+int cluster_max_active(int nmax) {
+  // co-resident 2-CTA clusters on the device for this length class
+  const size_t smem = cluster_smem_bytes(nmax, 2);
+  if (cudaFuncSetAttribute(fold_cluster_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * 1024, 1, 1);
+  cfg.blockDim = dim3(kClusterThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2;
+  attr.val.clusterDim.y = 1;
+  attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  int nc = 0;
+  if (cudaOccupancyMaxActiveClusters(&nc, fold_cluster_kernel<int16_t>, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return nc;
+}
+
+cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nmax, int num_clusters, int *queue,
+                                void *cbg, void *fg, cudaStream_t st) {
+  const size_t smem = cluster_smem_bytes(nmax, 2);
+  cudaError_t err = cudaFuncSetAttribute(fold_cluster_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (err != cudaSuccess) return err;
+  fold_cluster_kernel<int16_t><<<2 * num_clusters, kClusterThreads, smem, st>>>(
+      gp, a, nmax, queue, (int16_t *)cbg, (int16_t *)fg, (long long)cluster_table_stride(nmax));
+  return cudaGetLastError();
+}
+
+cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
+                                cudaStream_t st) {
+  const size_t smem = (size_t)kBtWarps * bt_warp_bytes(nmax);
+  cudaError_t err = cudaFuncSetAttribute(f5_backtrack_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (err != cudaSuccess) return err;
+  const int grid = (a.B + kBtWarps - 1) / kBtWarps;
+  f5_backtrack_kernel<int16_t><<<grid, kBtWarps * 32, smem, st>>>(gp, a, nmax, (const int16_t *)cbg, (const int16_t *)fg,
+                                                                 (long long)cluster_table_stride(nmax));
+  return cudaGetLastError();
+}
 
 }  // namespace rnafold

@@ -58,7 +58,7 @@ def test_golden_rows_both_parameter_sets(engine, golden_rows, golden_folds):
             r = (1 - want_hd / len(s)) ** 9 + (0.25 if want_hd == 0 else 0)
             assert abs(reward[n] - r) < 1e-12
         launches, routed = _lib.last_launch_info()
-        assert launches >= 2 and routed[0] > 0 and routed[2] > 0   # both kernel families exercised
+        assert launches >= 3 and routed[0] > 0 and routed[1] > 0   # single-CTA and cluster kernels both exercised
     engine.set_vienna_params(1)
 
 
@@ -75,10 +75,31 @@ def test_random_n100_block(engine, oracle_params):
     _check(engine, oracle_params("turner2004"), _rand_batch(rng, 4096, 100, 100))
 
 
-def test_random_long_global_kernel(engine, oracle_params):
+def test_random_long_cluster_kernel(engine, oracle_params):
+    """257..432 nt: 2-CTA cluster kernel (DSMEM row exchange) + warp-per-sequence f5/backtrack kernel."""
+    from rnagent_b200 import _lib
     engine.set_vienna_params(1)
     rng = np.random.default_rng(400)
-    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 96, 233, 460))
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 160, 257, 432))
+    assert _lib.last_launch_info()[1][1] == 160
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 64, 400, 400))
+    engine.set_vienna_params(2)
+    _check(engine, oracle_params("turner1999"), _rand_batch(rng, 64, 300, 420, alphabet="GGCCAU"))
+    engine.set_vienna_params(1)
+
+
+def test_beyond_cluster_reach_uses_global_tables(engine, oracle_params):
+    from rnagent_b200 import _lib
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(600)
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 12, 470, 620))
+    assert _lib.last_launch_info()[1][2] == 12
+
+
+def test_long_gc_rich_overflows_int16_in_cluster_path(engine, oracle_params):
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(17)
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 24, 300, 440, alphabet="GC") + _rand_batch(rng, 24, 300, 440))
 
 
 def test_biased_composition_and_unknown_letters(engine, oracle_params):
