@@ -97,6 +97,34 @@ int rnafold_set_timing(int enabled);
  * the kernels were launched on (synchronises the stream). */
 int rnafold_last_kernel_ms(float *ms);
 
+/* Device the context is bound to (-1 before rnafold_init). */
+int rnafold_current_device(void);
+
+/* ---- Batched RnaDesign environment on the device -------------------------------------------------
+ * Replaces N reference environments (rlif/environments/RLIFenv.py:6-114, one per forked worker of
+ * SubprocVecEnv, rlif/learning/trainer.py:523-565) by one lock-step batch.  Per-environment logic is
+ * Solution.insert_nucleotide / find_next_unfilled / get_state / evaluate (rlif/rna/solution.py:84-155)
+ * over targets parsed like DotBracket (rlif/rna/dotbracket.py:94-111, 171-211, encoding_type 2).
+ * Observations are uint8 [N][10][2*kernel_size] (6 motif rows O C I H M E + 4 nucleotide rows A C G U),
+ * the window encoding[:, i:i+2k] of the reference.  Buffers may be host or device pointers. */
+int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle);
+int rnafold_env_destroy(int32_t handle);
+/* auto_reset: re-arm finished environments inside step (VecEnv behaviour); randomize: hashed random target
+ * choice instead of round-robin (RLIFenv.py:87-92; Python's RNG stream is not reproduced). */
+int rnafold_env_config(int32_t handle, int32_t auto_reset, int32_t randomize, uint64_t seed);
+/* RnaDesign.set_data: CSR list of dot-bracket targets (host pointers). */
+int rnafold_env_set_targets(int32_t handle, const uint8_t *bytes, const int32_t *off, int32_t n_targets);
+int rnafold_env_reset(int32_t handle, uint8_t *obs_out);
+/* actions int32[N] in 0..3; reward_out float64[N]; done_out uint8[N]; any output may be NULL. */
+int rnafold_env_step(int32_t handle, const int32_t *actions, double reward_exp, uint8_t *obs_out,
+                     double *reward_out, uint8_t *done_out);
+/* istat = {episodes, solved, sum HD, env steps}; fstat = {sum reward, sum MFE kcal/mol}. */
+int rnafold_env_stats(int32_t handle, uint64_t istat[4], double fstat[2], int32_t clear);
+int rnafold_env_snapshot(int32_t handle, uint8_t *seq, int32_t *idx, int32_t *cur, int32_t *ep, uint8_t *last_seq,
+                         uint8_t *last_db, int32_t *last_hd, int32_t *last_mfe, int32_t *last_t, int32_t *lmax_out);
+/* Host-only: base-pair partners (opener -> closer, -1 elsewhere) and motif codes 0..5 of one target. */
+int rnafold_parse_target(const uint8_t *dotbracket, int32_t n, int16_t *pair_out, uint8_t *motif_out);
+
 /* Measurement helper (bench.py): on-box peaks of the two on-chip resources that bound the fold DP,
  * whole device: conflict-free 4-byte shared-memory loads per second and integer add+min
  * (min-plus candidate) updates per second. */

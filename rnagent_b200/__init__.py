@@ -4,9 +4,12 @@ Batched Zuker MFE folding + dot-bracket Hamming distance behind the reference's 
 signatures.  Import is cheap and GPU-free; the first fold binds the CUDA library
 (rnagent_b200/librnafold_b200.so) and raises if it, or a B200, is missing.
 """
+from .dotbracket import DotBracket
+from .environments import RnaDesignBatch, RolloutStats, create_env, rollout, shard_targets
 from .utils import hamming_distance
 from .vienna import (PARAM_FILES, PARAMETERS, config_vienna, cvar, fold, fold_batch, fold_hamming_batch,
                      read_parameter_file, set_vienna_params)
 
 __all__ = ["fold", "fold_batch", "fold_hamming_batch", "read_parameter_file", "set_vienna_params",
-           "config_vienna", "cvar", "hamming_distance", "PARAMETERS", "PARAM_FILES"]
+           "config_vienna", "cvar", "hamming_distance", "PARAMETERS", "PARAM_FILES", "DotBracket", "RnaDesignBatch",
+           "RolloutStats", "create_env", "rollout", "shard_targets"]

@@ -17,7 +17,9 @@ EXPORTS = [
     "rnafold_read_parameter_file", "rnafold_export_params", "rnafold_parse_params", "rnafold_set_md", "rnafold_get_md",
     "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch",
     "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
-    "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes",
+    "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes", "rnafold_current_device",
+    "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_set_targets", "rnafold_env_reset",
+    "rnafold_env_step", "rnafold_env_stats", "rnafold_env_snapshot", "rnafold_parse_target",
 ]
 
 _lock = threading.Lock()
@@ -58,6 +60,16 @@ def load_library():
         L.rnafold_measure_onchip_peaks.argtypes = [ctypes.POINTER(cd), ctypes.POINTER(cd)]
         L.rnafold_wave_smem_bytes.argtypes = [ci, ci]
         L.rnafold_device_info.argtypes = [ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+        i32p, u64 = ctypes.POINTER(ctypes.c_int32), ctypes.c_uint64
+        L.rnafold_env_create.argtypes = [ci, ci, i32p]
+        L.rnafold_env_destroy.argtypes = [ci]
+        L.rnafold_env_config.argtypes = [ci, ci, ci, u64]
+        L.rnafold_env_set_targets.argtypes = [ci, vp, vp, ci]
+        L.rnafold_env_reset.argtypes = [ci, vp]
+        L.rnafold_env_step.argtypes = [ci, vp, cd, vp, vp, vp]
+        L.rnafold_env_stats.argtypes = [ci, vp, vp, ci]
+        L.rnafold_env_snapshot.argtypes = [ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32p]
+        L.rnafold_parse_target.argtypes = [vp, ci, vp, vp]
         _cdll = L
         return L
 

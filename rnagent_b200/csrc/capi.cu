@@ -398,9 +398,18 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
 
 }  // namespace
 
+namespace rnafold {
+// error channel shared with env.cu
+int set_error(int code, const char *msg) {
+  g_err = msg ? msg : "";
+  return code;
+}
+}  // namespace rnafold
+
 extern "C" {
 
 const char *rnafold_last_error(void) { return g_err.c_str(); }
+int rnafold_current_device(void) { return g_ctx ? g_ctx->device : -1; }
 const char *rnafold_version(void) { return "rnafold_b200 0.1 (sm_100a)"; }
 
 int rnafold_init(int device) {

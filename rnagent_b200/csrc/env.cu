@@ -1,0 +1,554 @@
+// env.cu -- batched RnaDesign environment on the device (reference: rlif/environments/RLIFenv.py:6-114,
+// rlif/rna/solution.py:84-155, rlif/rna/dotbracket.py:94-211).
+//
+// N environments advance in lock-step: one kernel applies the N actions (insert_nucleotide +
+// find_next_unfilled), the environments that reached their last position are compacted into a CSR
+// batch and folded by the library's own fold kernels (fold + Hamming + reward), the results are
+// scattered back, finished environments are optionally re-armed with their next target (the
+// auto-reset of the reference's VecEnv), and one kernel emits the [N, 10, 2k] observation windows.
+// Nothing here runs on the CPU except target parsing (once per data set) and launch bookkeeping.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/rnafold_b200.h"
+#include "fold_kernels.h"
+
+namespace {
+
+using rnafold::set_error;
+
+#define ENV_TRY(expr)                                                                   \
+  do {                                                                                  \
+    cudaError_t e_ = (expr);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      char buf_[256];                                                                   \
+      std::snprintf(buf_, sizeof(buf_), "%s: %s", #expr, cudaGetErrorString(e_));       \
+      return set_error(RNAFOLD_ECUDA, buf_);                                            \
+    }                                                                                   \
+  } while (0)
+
+constexpr int kRows = 10;  // 6 structure-motif rows (O C I H M E) + 4 nucleotide rows (A C G U)
+
+struct Env {
+  int n_envs = 0, k = 25, n_targets = 0, lmax = 0;
+  bool auto_reset = true, randomize = false;
+  uint64_t seed = 0;
+  cudaStream_t stream = nullptr;
+  // data set (device, CSR over targets)
+  uint8_t *d_tgt = nullptr, *d_mot = nullptr;
+  int16_t *d_pair = nullptr;
+  int32_t *d_toff = nullptr;
+  // per-environment state
+  int32_t *d_cur = nullptr, *d_idx = nullptr, *d_ep = nullptr, *d_act = nullptr;
+  uint8_t *d_seq = nullptr, *d_mask = nullptr, *d_done = nullptr;
+  double *d_reward = nullptr;
+  // terminal batch
+  int32_t *d_list = nullptr, *d_off = nullptr, *d_hd = nullptr, *d_mfe = nullptr;
+  uint8_t *d_bseq = nullptr, *d_btgt = nullptr, *d_bdb = nullptr;
+  double *d_brw = nullptr;
+  int32_t *h_off = nullptr;  // pinned: [0] = count, [1..] offsets
+  // statistics: episodes, solved, sum_hd, steps (int64) ; sum_reward, sum_mfe_kcal (double)
+  unsigned long long *d_istat = nullptr;
+  double *d_fstat = nullptr;
+  uint8_t *d_obs = nullptr;
+  // last folded structures of each env (for get_attr('prev_solution'))
+  uint8_t *d_last_db = nullptr, *d_last_seq = nullptr;
+  int32_t *d_last_hd = nullptr, *d_last_mfe = nullptr, *d_last_t = nullptr;
+};
+
+std::mutex g_env_mu;
+std::vector<Env *> g_envs;
+
+// ---- host: parse one dot-bracket target (rlif/rna/dotbracket.py:94-111 and :171-211)
+void parse_target(const std::string &s, std::vector<int16_t> &pair, std::vector<uint8_t> &mot) {
+  const int n = (int)s.size();
+  pair.assign(n, -1);
+  std::vector<int> stack;
+  for (int i = 0; i < n; ++i) {
+    if (s[i] == '(') stack.push_back(i);
+    else if (s[i] == ')' && !stack.empty()) {  // unbalanced closers are ignored like the reference's try/except
+      const int b = stack.back();
+      stack.pop_back();
+      pair[b] = (int16_t)i;  // base_pair_indices maps opener -> closer only
+    }
+  }
+  // motif markers: O C I H M E = 0..5; mapping {'()':H, ')(':M, '((':I, '))':I, 'X(':E, ')X':E, 'XX':E}
+  mot.assign(n, 5);
+  char prev = 'X';
+  int run = 0;
+  auto motif = [](char a, char b) -> int {
+    if (a == '(' && b == ')') return 3;
+    if (a == ')' && b == '(') return 4;
+    if ((a == '(' && b == '(') || (a == ')' && b == ')')) return 2;
+    return 5;
+  };
+  for (int i = 0; i <= n; ++i) {
+    const char c = i < n ? s[i] : 'X';
+    if (c == '.') {
+      ++run;
+    } else if (c == 'X') {
+      const int m = motif(prev, c);
+      for (int q = i - run; q < i; ++q) mot[q] = (uint8_t)m;
+    } else {
+      mot[i] = c == '(' ? 0 : 1;
+      if (run > 0) {
+        const int m = motif(prev, c);
+        for (int q = i - run; q < i; ++q) mot[q] = (uint8_t)m;
+      }
+      run = 0;
+      prev = c;
+    }
+  }
+}
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+  x += 0x9e3779b97f4a7c15ull;
+  x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+  x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+  return x ^ (x >> 31);
+}
+
+// (re)arm environments: next target (round-robin per env, or hashed random), empty sequence
+__global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int randomize, unsigned long long seed,
+                                 const uint8_t *__restrict__ only_done, int32_t *cur, int32_t *idx, int32_t *ep,
+                                 uint8_t *seq, uint8_t *mask) {
+  const int e = blockIdx.x;
+  if (e >= n_envs) return;
+  if (only_done && !only_done[e]) return;
+  __shared__ int t_next;
+  if (threadIdx.x == 0) {
+    const int epn = ep[e] + 1;
+    int t;
+    if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
+    else t = (cur[e] + 1) % n_targets;
+    cur[e] = t;
+    idx[e] = 0;
+    ep[e] = epn;
+    t_next = t;
+  }
+  __syncthreads();
+  for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
+    seq[(size_t)e * lmax + q] = '-';
+    mask[(size_t)e * lmax + q] = 0;
+  }
+}
+
+// insert_nucleotide + find_next_unfilled (solution.py:84-114) and the terminal test of RnaDesign.step
+__global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict__ act, const int32_t *__restrict__ cur,
+                                const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
+                                const int16_t *__restrict__ pair, int32_t *idx, uint8_t *seq, uint8_t *mask,
+                                uint8_t *done, double *reward, unsigned long long *istat) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_envs) return;
+  const int t = cur[e];
+  const int base = toff[t], n = toff[t + 1] - base;
+  uint8_t *s = seq + (size_t)e * lmax, *m = mask + (size_t)e * lmax;
+  const int i = idx[e];
+  const int a = act[e] & 3;
+  m[i] |= (uint8_t)(1u << a);
+  s[i] = "ACGU"[a];
+  if (tgt[base + i] == '(') {
+    const int p = pair[base + i];
+    if (p >= 0) {
+      m[p] |= (uint8_t)(1u << (3 - a));  // reverse_action: the Watson-Crick partner
+      s[p] = "UGCA"[a];
+    }
+  }
+  reward[e] = 0.0;  // Solution.r stays 0 until evaluate()
+  if (i < n - 1) {
+    int q = i;
+    while (q < n - 1 && s[q] != '-') ++q;  // stops at n-1 even if that slot is filled (reference quirk)
+    idx[e] = q;
+    done[e] = 0;
+  } else {
+    done[e] = 1;
+  }
+  atomicAdd(&istat[3], 1ull);
+}
+
+// compact the terminal environments into a CSR batch (single CTA; N is a few thousand)
+__global__ void env_compact_kernel(int n_envs, int lmax, const uint8_t *__restrict__ done, const int32_t *__restrict__ cur,
+                                   const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
+                                   const uint8_t *__restrict__ seq, int32_t *list, int32_t *off, uint8_t *bseq,
+                                   uint8_t *btgt) {
+  __shared__ int s_cnt[32], s_len[32];
+  __shared__ int base_cnt, base_len;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  if (tid == 0) {
+    base_cnt = 0;
+    base_len = 0;
+  }
+  __syncthreads();
+  for (int e0 = 0; e0 < n_envs; e0 += blockDim.x) {
+    const int e = e0 + tid;
+    const int is = (e < n_envs && done[e]) ? 1 : 0;
+    int len = 0;
+    if (is) len = toff[cur[e] + 1] - toff[cur[e]];
+    int c = is, l = len;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int tc = __shfl_up_sync(0xffffffffu, c, o), tl = __shfl_up_sync(0xffffffffu, l, o);
+      if (lane >= o) {
+        c += tc;
+        l += tl;
+      }
+    }
+    if (lane == 31) {
+      s_cnt[warp] = c;
+      s_len[warp] = l;
+    }
+    __syncthreads();
+    int pc = base_cnt, plen = base_len;
+    for (int w = 0; w < warp; ++w) {
+      pc += s_cnt[w];
+      plen += s_len[w];
+    }
+    if (is) {
+      const int slot = pc + c - 1, o0 = plen + l - len;
+      list[slot] = e;
+      off[1 + slot] = o0;  // off[0] holds the count; offsets start at off[1]
+      const int tb = toff[cur[e]];
+      for (int q = 0; q < len; ++q) {
+        bseq[o0 + q] = seq[(size_t)e * lmax + q];
+        btgt[o0 + q] = tgt[tb + q];
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      for (int w = 0; w < nw; ++w) {
+        base_cnt += s_cnt[w];
+        base_len += s_len[w];
+      }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    off[0] = base_cnt;
+    off[1 + base_cnt] = base_len;
+  }
+}
+
+// scatter fold results back to their environments and update the rollout statistics
+__global__ void env_scatter_kernel(int count, int lmax, const int32_t *__restrict__ list, const int32_t *__restrict__ off,
+                                   const double *__restrict__ brw, const int32_t *__restrict__ bhd,
+                                   const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb,
+                                   const uint8_t *__restrict__ bseq, const int32_t *__restrict__ cur, double *reward,
+                                   uint8_t *last_db, uint8_t *last_seq, int32_t *last_hd, int32_t *last_mfe,
+                                   int32_t *last_t, unsigned long long *istat, double *fstat) {
+  const int s = blockIdx.x;
+  if (s >= count) return;
+  const int e = list[s];
+  const int o0 = off[1 + s], len = off[2 + s] - o0;
+  for (int q = threadIdx.x; q < len; q += blockDim.x) {
+    last_db[(size_t)e * lmax + q] = bdb[o0 + q];
+    last_seq[(size_t)e * lmax + q] = bseq[o0 + q];
+  }
+  if (threadIdx.x == 0) {
+    reward[e] = brw[s];
+    last_hd[e] = bhd[s];
+    last_mfe[e] = bmfe[s];
+    last_t[e] = cur[e];
+    atomicAdd(&istat[0], 1ull);
+    if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
+    atomicAdd(&istat[2], (unsigned long long)bhd[s]);
+    atomicAdd(&fstat[0], brw[s]);
+    atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
+  }
+}
+
+// observation window encoding[:, i:i+2k] of the zero-padded [10, len+2k] encoding (solution.py:62-75,116-123)
+__global__ void env_obs_kernel(int n_envs, int lmax, int k, const int32_t *__restrict__ cur, const int32_t *__restrict__ idx,
+                               const int32_t *__restrict__ toff, const uint8_t *__restrict__ mot,
+                               const uint8_t *__restrict__ mask, uint8_t *obs) {
+  const int e = blockIdx.x;
+  if (e >= n_envs) return;
+  const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
+  const int w = 2 * k;
+  for (int q = threadIdx.x; q < kRows * w; q += blockDim.x) {
+    const int row = q / w, col = q - row * w;
+    const int pos = i - k + col;
+    uint8_t v = 0;
+    if (pos >= 0 && pos < n) v = row < 6 ? (mot[base + pos] == row) : ((mask[(size_t)e * lmax + pos] >> (row - 6)) & 1);
+    obs[(size_t)e * kRows * w + q] = v;
+  }
+}
+
+Env *get_env(int h) {
+  if (h < 0 || h >= (int)g_envs.size()) return nullptr;
+  return g_envs[h];
+}
+
+template <typename T>
+cudaError_t dalloc(T **p, size_t n) {
+  return cudaMalloc((void **)p, sizeof(T) * (n ? n : 1));
+}
+
+}  // namespace
+
+static bool env_is_device_ptr(const void *p) {
+  if (!p) return false;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+static cudaError_t copy_out(void *user, const void *dev, size_t bytes, cudaStream_t st) {
+  if (!user || !bytes) return cudaSuccess;
+  return cudaMemcpyAsync(user, dev, bytes, env_is_device_ptr(user) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st);
+}
+
+static void env_free(Env *e) {
+  void *ptrs[] = {e->d_tgt, e->d_mot, e->d_pair, e->d_toff, e->d_cur, e->d_idx, e->d_ep, e->d_act, e->d_seq, e->d_mask,
+                  e->d_done, e->d_reward, e->d_list, e->d_off, e->d_hd, e->d_mfe, e->d_bseq, e->d_btgt, e->d_bdb,
+                  e->d_brw, e->d_istat, e->d_fstat, e->d_obs, e->d_last_db, e->d_last_seq, e->d_last_hd,
+                  e->d_last_mfe, e->d_last_t};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  if (e->h_off) cudaFreeHost(e->h_off);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+extern "C" {
+
+int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
+  if (n_envs <= 0 || kernel_size <= 0 || kernel_size > 512 || !handle) return set_error(RNAFOLD_EINVAL, "bad env arguments");
+  const int dev = rnafold_current_device();
+  if (dev < 0) return set_error(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  ENV_TRY(cudaSetDevice(dev));
+  Env *e = new Env();
+  e->n_envs = n_envs;
+  e->k = kernel_size;
+  const size_t N = (size_t)n_envs;
+  ENV_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  ENV_TRY(dalloc(&e->d_cur, N));
+  ENV_TRY(dalloc(&e->d_idx, N));
+  ENV_TRY(dalloc(&e->d_ep, N));
+  ENV_TRY(dalloc(&e->d_act, N));
+  ENV_TRY(dalloc(&e->d_done, N));
+  ENV_TRY(dalloc(&e->d_reward, N));
+  ENV_TRY(dalloc(&e->d_list, N));
+  ENV_TRY(dalloc(&e->d_off, N + 2));
+  ENV_TRY(dalloc(&e->d_hd, N));
+  ENV_TRY(dalloc(&e->d_mfe, N));
+  ENV_TRY(dalloc(&e->d_brw, N));
+  ENV_TRY(dalloc(&e->d_last_hd, N));
+  ENV_TRY(dalloc(&e->d_last_mfe, N));
+  ENV_TRY(dalloc(&e->d_last_t, N));
+  ENV_TRY(dalloc(&e->d_istat, 4));
+  ENV_TRY(dalloc(&e->d_fstat, 2));
+  ENV_TRY(dalloc(&e->d_obs, N * kRows * 2 * (size_t)kernel_size));
+  ENV_TRY(cudaMallocHost((void **)&e->h_off, sizeof(int32_t) * (N + 2)));
+  ENV_TRY(cudaMemset(e->d_istat, 0, 4 * sizeof(unsigned long long)));
+  ENV_TRY(cudaMemset(e->d_fstat, 0, 2 * sizeof(double)));
+  ENV_TRY(cudaMemset(e->d_cur, 0xff, N * sizeof(int32_t)));  // current_sequence = -1 (RLIFenv.py:25)
+  ENV_TRY(cudaMemset(e->d_ep, 0, N * sizeof(int32_t)));
+  ENV_TRY(cudaMemset(e->d_last_hd, 0, N * sizeof(int32_t)));
+  ENV_TRY(cudaMemset(e->d_last_mfe, 0, N * sizeof(int32_t)));
+  ENV_TRY(cudaMemset(e->d_last_t, 0xff, N * sizeof(int32_t)));
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  g_envs.push_back(e);
+  *handle = (int32_t)g_envs.size() - 1;
+  return RNAFOLD_OK;
+}
+
+int rnafold_env_destroy(int32_t h) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  cudaStreamSynchronize(e->stream);
+  env_free(e);
+  g_envs[h] = nullptr;
+  return RNAFOLD_OK;
+}
+
+int rnafold_env_config(int32_t h, int32_t auto_reset, int32_t randomize, uint64_t seed) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  e->auto_reset = auto_reset != 0;
+  e->randomize = randomize != 0;
+  e->seed = seed;
+  return RNAFOLD_OK;
+}
+
+// RnaDesign.set_data (RLIFenv.py:106-109): install a data set of dot-bracket targets; every environment
+// starts over at current_sequence = -1 and takes its first target.
+int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off, int32_t n_targets) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e || !bytes || !off || n_targets <= 0) return set_error(RNAFOLD_EINVAL, "bad env targets");
+  std::vector<int16_t> pair_all;
+  std::vector<uint8_t> mot_all;
+  int lmax = 0;
+  for (int t = 0; t < n_targets; ++t) {
+    const int n = off[t + 1] - off[t];
+    if (n <= 0 || n > RNAFOLD_MAX_LEN) return set_error(RNAFOLD_EINVAL, "target length out of range");
+    std::string s((const char *)bytes + off[t], (size_t)n);
+    for (char c : s)
+      if (c != '(' && c != ')' && c != '.') return set_error(RNAFOLD_EINVAL, "targets must be dot-bracket strings");
+    std::vector<int16_t> pr;
+    std::vector<uint8_t> mo;
+    parse_target(s, pr, mo);
+    pair_all.insert(pair_all.end(), pr.begin(), pr.end());
+    mot_all.insert(mot_all.end(), mo.begin(), mo.end());
+    lmax = n > lmax ? n : lmax;
+  }
+  const size_t total = (size_t)off[n_targets], N = (size_t)e->n_envs;
+  for (void *p : {(void *)e->d_tgt, (void *)e->d_mot, (void *)e->d_pair, (void *)e->d_toff, (void *)e->d_seq, (void *)e->d_mask,
+                  (void *)e->d_bseq, (void *)e->d_btgt, (void *)e->d_bdb, (void *)e->d_last_db, (void *)e->d_last_seq})
+    if (p) cudaFree(p);
+  ENV_TRY(dalloc(&e->d_tgt, total));
+  ENV_TRY(dalloc(&e->d_mot, total));
+  ENV_TRY(dalloc(&e->d_pair, total));
+  ENV_TRY(dalloc(&e->d_toff, (size_t)n_targets + 1));
+  ENV_TRY(dalloc(&e->d_seq, N * lmax));
+  ENV_TRY(dalloc(&e->d_mask, N * lmax));
+  ENV_TRY(dalloc(&e->d_bseq, N * lmax + 16));
+  ENV_TRY(dalloc(&e->d_btgt, N * lmax + 16));
+  ENV_TRY(dalloc(&e->d_bdb, N * lmax + 16));
+  ENV_TRY(dalloc(&e->d_last_db, N * lmax));
+  ENV_TRY(dalloc(&e->d_last_seq, N * lmax));
+  ENV_TRY(cudaMemcpy(e->d_tgt, bytes, total, cudaMemcpyHostToDevice));
+  ENV_TRY(cudaMemcpy(e->d_mot, mot_all.data(), total, cudaMemcpyHostToDevice));
+  ENV_TRY(cudaMemcpy(e->d_pair, pair_all.data(), total * sizeof(int16_t), cudaMemcpyHostToDevice));
+  ENV_TRY(cudaMemcpy(e->d_toff, off, sizeof(int32_t) * ((size_t)n_targets + 1), cudaMemcpyHostToDevice));
+  ENV_TRY(cudaMemset(e->d_last_db, '.', N * lmax));
+  ENV_TRY(cudaMemset(e->d_last_seq, '-', N * lmax));
+  e->n_targets = n_targets;
+  e->lmax = lmax;
+  ENV_TRY(cudaMemset(e->d_cur, 0xff, N * sizeof(int32_t)));
+  ENV_TRY(cudaMemset(e->d_ep, 0xff, N * sizeof(int32_t)));  // the constructor's next_target_structure() is not an episode
+  env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
+                                                     e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
+  ENV_TRY(cudaGetLastError());
+  ENV_TRY(cudaStreamSynchronize(e->stream));
+  return RNAFOLD_OK;
+}
+
+static int env_emit_obs(Env *e, uint8_t *obs_out) {
+  env_obs_kernel<<<e->n_envs, 128, 0, e->stream>>>(e->n_envs, e->lmax, e->k, e->d_cur, e->d_idx, e->d_toff, e->d_mot,
+                                                    e->d_mask, e->d_obs);
+  ENV_TRY(cudaGetLastError());
+  ENV_TRY(copy_out(obs_out, e->d_obs, (size_t)e->n_envs * kRows * 2 * e->k, e->stream));
+  return RNAFOLD_OK;
+}
+
+// RnaDesign.reset for every environment (RLIFenv.py:34-57): next target, empty solution, first observation
+int rnafold_env_reset(int32_t h, uint8_t *obs_out) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
+  ENV_TRY(cudaSetDevice(rnafold_current_device()));
+  env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
+                                                     e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
+  ENV_TRY(cudaGetLastError());
+  int rc = env_emit_obs(e, obs_out);
+  if (rc) return rc;
+  ENV_TRY(cudaStreamSynchronize(e->stream));
+  return RNAFOLD_OK;
+}
+
+// RnaDesign.step for every environment (RLIFenv.py:59-81) + the VecEnv auto-reset when enabled
+int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8_t *obs_out, double *reward_out,
+                     uint8_t *done_out) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e || !e->n_targets || !actions) return set_error(RNAFOLD_EINVAL, "bad env handle, no targets set or null actions");
+  ENV_TRY(cudaSetDevice(rnafold_current_device()));
+  const int N = e->n_envs;
+  cudaStream_t st = e->stream;
+  const int32_t *d_act = actions;
+  if (!env_is_device_ptr(actions)) {
+    ENV_TRY(cudaMemcpyAsync(e->d_act, actions, sizeof(int32_t) * (size_t)N, cudaMemcpyHostToDevice, st));
+    d_act = e->d_act;
+  }
+  env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
+                                                   e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat);
+  env_compact_kernel<<<1, 1024, 0, st>>>(N, e->lmax, e->d_done, e->d_cur, e->d_toff, e->d_tgt, e->d_seq, e->d_list, e->d_off,
+                                         e->d_bseq, e->d_btgt);
+  ENV_TRY(cudaGetLastError());
+  ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t) * ((size_t)N + 2), cudaMemcpyDeviceToHost, st));
+  ENV_TRY(cudaStreamSynchronize(st));
+  const int count = e->h_off[0];
+  if (count > 0) {
+    int rc = rnafold_fold_hamming_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
+                                        nullptr, reward_exp, (void *)st);
+    if (rc) return rc;
+    env_scatter_kernel<<<count, 64, 0, st>>>(count, e->lmax, e->d_list, e->d_off, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb,
+                                             e->d_bseq, e->d_cur, e->d_reward, e->d_last_db, e->d_last_seq, e->d_last_hd,
+                                             e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat);
+    ENV_TRY(cudaGetLastError());
+    if (e->auto_reset) {
+      env_reset_kernel<<<N, 64, 0, st>>>(N, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, e->d_done, e->d_cur, e->d_idx,
+                                         e->d_ep, e->d_seq, e->d_mask);
+      ENV_TRY(cudaGetLastError());
+    }
+  }
+  int rc = env_emit_obs(e, obs_out);
+  if (rc) return rc;
+  ENV_TRY(copy_out(reward_out, e->d_reward, sizeof(double) * (size_t)N, st));
+  ENV_TRY(copy_out(done_out, e->d_done, (size_t)N, st));
+  ENV_TRY(cudaStreamSynchronize(st));
+  return RNAFOLD_OK;
+}
+
+// rollout statistics since the last clear: istat = {episodes, solved (HD == 0), sum HD, env steps},
+// fstat = {sum reward, sum MFE (kcal/mol)}
+int rnafold_env_stats(int32_t h, uint64_t istat[4], double fstat[2], int32_t clear) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e || !istat || !fstat) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  ENV_TRY(cudaMemcpyAsync(istat, e->d_istat, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
+  ENV_TRY(cudaMemcpyAsync(fstat, e->d_fstat, 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  if (clear) {
+    ENV_TRY(cudaMemsetAsync(e->d_istat, 0, 4 * sizeof(uint64_t), e->stream));
+    ENV_TRY(cudaMemsetAsync(e->d_fstat, 0, 2 * sizeof(double), e->stream));
+  }
+  ENV_TRY(cudaStreamSynchronize(e->stream));
+  return RNAFOLD_OK;
+}
+
+// state snapshot for get_attr: current sequences ('-' = unfilled), cursors, target indices, episode counters
+// and the last evaluated solution of every environment (sequence, folded structure, HD, MFE dcal, target)
+int rnafold_env_snapshot(int32_t h, uint8_t *seq, int32_t *idx, int32_t *cur, int32_t *ep, uint8_t *last_seq,
+                         uint8_t *last_db, int32_t *last_hd, int32_t *last_mfe, int32_t *last_t, int32_t *lmax_out) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
+  const size_t N = (size_t)e->n_envs, NL = N * (size_t)e->lmax;
+  cudaStream_t st = e->stream;
+  ENV_TRY(copy_out(seq, e->d_seq, NL, st));
+  ENV_TRY(copy_out(idx, e->d_idx, 4 * N, st));
+  ENV_TRY(copy_out(cur, e->d_cur, 4 * N, st));
+  ENV_TRY(copy_out(ep, e->d_ep, 4 * N, st));
+  ENV_TRY(copy_out(last_seq, e->d_last_seq, NL, st));
+  ENV_TRY(copy_out(last_db, e->d_last_db, NL, st));
+  ENV_TRY(copy_out(last_hd, e->d_last_hd, 4 * N, st));
+  ENV_TRY(copy_out(last_mfe, e->d_last_mfe, 4 * N, st));
+  ENV_TRY(copy_out(last_t, e->d_last_t, 4 * N, st));
+  if (lmax_out) *lmax_out = e->lmax;
+  ENV_TRY(cudaStreamSynchronize(st));
+  return RNAFOLD_OK;
+}
+
+// host-only: the reference's target parsing (base pairs + motif markers) for the CPU test-suite
+int rnafold_parse_target(const uint8_t *dotbracket, int32_t n, int16_t *pair_out, uint8_t *motif_out) {
+  if (!dotbracket || n < 0 || !pair_out || !motif_out) return set_error(RNAFOLD_EINVAL, "bad arguments");
+  std::vector<int16_t> pr;
+  std::vector<uint8_t> mo;
+  parse_target(std::string((const char *)dotbracket, (size_t)n), pr, mo);
+  std::memcpy(pair_out, pr.data(), sizeof(int16_t) * (size_t)n);
+  std::memcpy(motif_out, mo.data(), (size_t)n);
+  return RNAFOLD_OK;
+}
+
+}  // extern "C"

@@ -54,6 +54,9 @@ cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nm
 cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
                                 cudaStream_t st);
 
+// capi.cu: records the message returned by rnafold_last_error() and passes `code` through
+int set_error(int code, const char *msg);
+
 // peaks.cu: on-box shared-memory-load and min-plus (ALU) peak rates, whole device, per second
 cudaError_t measure_onchip_peaks(int num_sms, cudaStream_t st, double *lds_per_s, double *minplus_per_s);
 

@@ -1,0 +1,224 @@
+"""Batched drop-in for the reference's environment layer, running on the B200.
+
+Reference                                               here
+------------------------------------------------------  -------------------------------------------
+RnaDesign(config, rank).reset()/step(a)                 RnaDesignBatch(config, n_envs).reset()/step(actions)
+  rlif/environments/RLIFenv.py:6-114                      N environments in lock-step on one GPU
+create_env(...) -> SubprocVecEnv / DummyVecEnv          the same VecEnv-shaped surface: step/reset/get_attr/set_attr,
+  rlif/learning/trainer.py:523-565                        finished environments re-armed inside step (auto_reset)
+while not done: a = model.predict(s); s,_,done,_ =      rollout(env, policy, n_steps)
+  env.step(a)   trainer.py:307-309, tester.py:85-87
+Solution.evaluate reward                                fused into the fold kernels (fold + Hamming + reward)
+
+Every per-step operation is a CUDA kernel behind the C ABI (rnafold_env_*); there is no CPU path.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from .dotbracket import DotBracket
+
+ROWS = 10
+
+
+class _PrevSolution(object):
+    """What callers read from env.get_attr('prev_solution') (rlif/learning/trainer.py:311-313)."""
+
+    def __init__(self, target, string, folded, hd, fe, reward_exp):
+        self.target, self.string, self.folded_structure, self.hd, self.fe = target, string, folded, hd, fe
+        n = max(1, len(string))
+        self.r = (1 - float(hd) / float(n)) ** reward_exp + (0.25 if hd == 0 else 0.0)
+        self.source = 'rlif'
+
+    def __repr__(self):
+        return f"<solution hd={self.hd} fe={self.fe:.2f} {self.string}>"
+
+
+class RnaDesignBatch(object):
+    """N RnaDesign environments stepped in lock-step on one GPU.
+
+    config keys read (same names as rlif/config/RnaDesign.yml `environment`): kernel_size, reward_exp, permute,
+    encoding_type, use_nucleotides.  permute=True / boosting / testing-mode statistics are not part of this
+    path and raise NotImplementedError instead of silently returning something else.
+    """
+
+    def __init__(self, config, n_envs, targets=None, rank=0, auto_reset=True, randomize=False, seed=0):
+        self.config = dict(config)
+        if self.config.get('permute'):
+            raise NotImplementedError("permute=True (Solution.permute local search) is not on the batched path")
+        if self.config.get('encoding_type', 2) != 2 or not self.config.get('use_nucleotides', True):
+            raise NotImplementedError("only encoding_type=2 with use_nucleotides=True is implemented")
+        self.n_envs = int(n_envs)
+        self.env_id = rank
+        self.kernel_size = int(self.config.get('kernel_size', 25))
+        self.reward_exp = float(self.config.get('reward_exp', 9))
+        self.randomize = bool(randomize)
+        self.meta_learning = True
+        self.permute = False
+        self.testing_mode = False
+        self.verbose = False
+        self.seed = int(seed) + 7919 * int(rank)
+        self.auto_reset = bool(auto_reset)
+        self.L = _lib.lib()
+        h = ctypes.c_int32(-1)
+        _lib.check(self.L.rnafold_env_create(self.n_envs, self.kernel_size, ctypes.byref(h)))
+        self._h = h.value
+        self._configure()
+        self.observation_shape = (ROWS, 2 * self.kernel_size, 1)
+        self.dataset = []
+        self._obs = np.zeros((self.n_envs, ROWS, 2 * self.kernel_size, 1), dtype=np.uint8)
+        self._rew = np.zeros(self.n_envs, dtype=np.float64)
+        self._done = np.zeros(self.n_envs, dtype=np.uint8)
+        self._infos = [{} for _ in range(self.n_envs)]
+        if targets is not None:
+            self.set_data(targets)
+
+    def _configure(self):
+        _lib.check(self.L.rnafold_env_config(self._h, int(self.auto_reset), int(self.randomize), self.seed))
+
+    # ---- RnaDesign.set_data / set_sequence (RLIFenv.py:106-113)
+    def set_data(self, data):
+        seqs = [d.seq if hasattr(d, 'seq') else str(d) for d in (data.sequences if hasattr(data, 'sequences') else data)]
+        if not seqs:
+            raise ValueError("empty data set")
+        self.dataset = seqs
+        raw = np.frombuffer(''.join(seqs).encode(), dtype=np.uint8).copy()
+        off = np.zeros(len(seqs) + 1, dtype=np.int32)
+        off[1:] = np.cumsum([len(s) for s in seqs])
+        self._configure()
+        _lib.check(self.L.rnafold_env_set_targets(self._h, raw.ctypes.data, off.ctypes.data, len(seqs)))
+
+    def set_sequence(self, sequence):
+        self.set_data([sequence])
+
+    # ---- VecEnv surface
+    def reset(self):
+        _lib.check(self.L.rnafold_env_reset(self._h, self._obs.ctypes.data))
+        return self._obs
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, dtype=np.int32)
+        if a.shape != (self.n_envs,):
+            raise ValueError(f"expected {self.n_envs} actions")
+        _lib.check(self.L.rnafold_env_step(self._h, a.ctypes.data, self.reward_exp, self._obs.ctypes.data,
+                                           self._rew.ctypes.data, self._done.ctypes.data))
+        return self._obs, self._rew, self._done.view(np.bool_), self._infos
+
+    def step_device(self, actions, obs=None, reward=None, done=None):
+        """Same step with torch CUDA tensors (int32 actions; uint8 obs [N,10,2k], float64 reward, uint8 done)."""
+        p = lambda t: None if t is None else t.data_ptr()
+        _lib.check(self.L.rnafold_env_step(self._h, actions.data_ptr(), self.reward_exp, p(obs), p(reward), p(done)))
+
+    def stats(self, clear=False):
+        """Rollout statistics accumulated on the device since the last clear."""
+        ist = np.zeros(4, dtype=np.uint64)
+        fst = np.zeros(2, dtype=np.float64)
+        _lib.check(self.L.rnafold_env_stats(self._h, ist.ctypes.data, fst.ctypes.data, int(clear)))
+        return RolloutStats(int(ist[0]), int(ist[1]), int(ist[2]), int(ist[3]), float(fst[0]), float(fst[1]))
+
+    def snapshot(self):
+        N = self.n_envs
+        lmax = max(len(s) for s in self.dataset)
+        buf = {k: np.zeros((N, lmax), dtype=np.uint8) for k in ('seq', 'last_seq', 'last_db')}
+        ints = {k: np.zeros(N, dtype=np.int32) for k in ('idx', 'cur', 'ep', 'last_hd', 'last_mfe', 'last_t')}
+        lm = ctypes.c_int32(0)
+        _lib.check(self.L.rnafold_env_snapshot(self._h, buf['seq'].ctypes.data, ints['idx'].ctypes.data, ints['cur'].ctypes.data,
+                                               ints['ep'].ctypes.data, buf['last_seq'].ctypes.data, buf['last_db'].ctypes.data,
+                                               ints['last_hd'].ctypes.data, ints['last_mfe'].ctypes.data,
+                                               ints['last_t'].ctypes.data, ctypes.byref(lm)))
+        buf.update(ints)
+        return buf
+
+    def get_attr(self, name):
+        if name in ('ep', 'current_sequence'):
+            return list(self.snapshot()['ep' if name == 'ep' else 'cur'])
+        if name == 'prev_solution':
+            s = self.snapshot()
+            out = []
+            for e in range(self.n_envs):
+                t = int(s['last_t'][e])
+                if t < 0:
+                    out.append(None)
+                    continue
+                n = len(self.dataset[t])
+                out.append(_PrevSolution(self.dataset[t], s['last_seq'][e, :n].tobytes().decode(),
+                                         s['last_db'][e, :n].tobytes().decode(), int(s['last_hd'][e]),
+                                         float(np.float32(s['last_mfe'][e] / 100.0)), self.reward_exp))
+            return out
+        if name == 'target_structure':
+            return [DotBracket(self.dataset[int(t)]) for t in self.snapshot()['cur']]
+        return [getattr(self, name)] * self.n_envs
+
+    def set_attr(self, name, value):
+        if name == 'dataset':
+            return self.set_data(value)
+        if name in ('permute', 'boosting') and value:
+            raise NotImplementedError(f"{name}=True is not on the batched path")
+        if name == 'testing_mode' and value:
+            raise NotImplementedError("testing_mode=True (partition-function statistics) is not on the batched path")
+        setattr(self, name, value)
+        if name in ('randomize', 'auto_reset', 'seed'):
+            self._configure()
+
+    def close(self):
+        if self._h is not None and self._h >= 0:
+            self.L.rnafold_env_destroy(self._h)
+            self._h = -1
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class RolloutStats(object):
+    """Per-GPU counters of a rollout; `all_reduce` sums them over the ranks of a torch.distributed group
+    (NCCL on GPUs, gloo in the CPU tests) -- the only collective on this path."""
+    FIELDS = ('episodes', 'solved', 'sum_hd', 'steps', 'sum_reward', 'sum_mfe')
+
+    def __init__(self, episodes=0, solved=0, sum_hd=0, steps=0, sum_reward=0.0, sum_mfe=0.0):
+        self.episodes, self.solved, self.sum_hd, self.steps = episodes, solved, sum_hd, steps
+        self.sum_reward, self.sum_mfe = sum_reward, sum_mfe
+
+    def as_vector(self):
+        return [float(getattr(self, f)) for f in self.FIELDS]
+
+    def all_reduce(self, device=None, group=None):
+        import torch
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()):
+            return self
+        t = torch.tensor(self.as_vector(), dtype=torch.float64, device=device or 'cpu')
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        v = t.tolist()
+        return RolloutStats(int(v[0]), int(v[1]), int(v[2]), int(v[3]), v[4], v[5])
+
+    def summary(self):
+        e = max(1, self.episodes)
+        return dict(episodes=self.episodes, steps=self.steps, solved_frac=self.solved / e, mean_hd=self.sum_hd / e,
+                    mean_reward=self.sum_reward / e, mean_mfe=self.sum_mfe / e)
+
+
+def shard_targets(targets, rank, world):
+    """Environment shard of one rank: target k lives on rank k mod world."""
+    return list(targets[rank::world]) or list(targets)
+
+
+def create_env(env_name, config, n_workers=1, targets=None, **kw):
+    """rlif/learning/trainer.py:523-565 shaped factory: one batched environment replaces the n_workers processes."""
+    if env_name != 'RnaDesign':
+        raise NotImplementedError(env_name)
+    return RnaDesignBatch(config, n_workers, targets=targets, **kw)
+
+
+def rollout(env, policy, n_steps):
+    """The reference's vectorised loop (trainer.py:307-309): a, _ = policy(state); state, r, done, _ = env.step(a)."""
+    state = env.reset()
+    total_r = 0.0
+    for _ in range(n_steps):
+        actions = policy(state)
+        state, r, done, _ = env.step(actions)
+        total_r += float(r.sum())
+    return env.stats(), total_r

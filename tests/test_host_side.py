@@ -1,0 +1,110 @@
+"""CPU-only checks: the C-ABI library loads and exports every declared symbol, the host-side target
+parser matches the reference's DotBracket on the golden episodes, the parameter loader matches the
+oracle's, and the rollout statistics reduce over a 2-rank gloo group."""
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+
+from conftest import GOLDEN, ROOT, param_file
+
+
+def test_library_exports_every_declared_symbol():
+    from rnagent_b200 import _lib
+    L = _lib.load_library()
+    hdr = open(os.path.join(ROOT, "include", "rnafold_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(rnafold_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 25
+    for n in sorted(names):
+        assert hasattr(L, n), n
+    assert names <= set(_lib.EXPORTS) | {"rnafold_version", "rnafold_last_error"}, names - set(_lib.EXPORTS)
+
+
+def test_version_and_errors_without_device():
+    from rnagent_b200 import _lib
+    L = _lib.load_library()
+    assert b"sm_100a" in L.rnafold_version()
+    assert L.rnafold_current_device() == -1 or L.rnafold_current_device() >= 0
+    assert L.rnafold_wave_smem_bytes(100, 2) > 0 and L.rnafold_wave_smem_bytes(100, 3) < 0
+
+
+def test_parameter_loader_matches_oracle(oracle_params):
+    from rnagent_b200 import _lib
+    for name in ("turner2004", "turner1999", "andronescu2007", "langdon2018"):
+        ours = _lib.parse_params(param_file(name))
+        want = oracle_params(name).export()
+        assert np.array_equal(ours, want), name
+    assert np.array_equal(_lib.parse_params(None), oracle_params("turner2004").export())  # built-in default
+
+
+def test_target_parser_matches_reference_dotbracket():
+    from rnagent_b200 import DotBracket
+    eps = json.load(open(os.path.join(GOLDEN, "env_episodes.json")))["episodes"]
+    for e in eps:
+        t = DotBracket(e["target"])
+        assert t.struct_motifs == e["motifs"]
+        assert sorted([a, b] for a, b in t.base_pair_indices.items()) == e["pairs"]
+        assert t.structure_encoding.shape == (6, len(e["target"])) and t.structure_encoding.sum() == len(e["target"])
+    t = DotBracket("..((..((...))..((...))..))")
+    assert t.struct_motifs == "EEOOIIOOHHHCCMMOOHHHCCIICC"
+    assert t.rev_base_pair_indices[25] == 2
+
+
+def test_hamming_distance_signature():
+    from rnagent_b200 import hamming_distance
+    hd, idx = hamming_distance("((..))", "(....)")
+    assert hd == 2 and list(idx) == [1, 4]
+    assert hamming_distance("((..))", "((")[0] == 0          # zip-truncating like the reference
+
+
+def test_work_model_and_workloads():
+    from rnagent_b200 import synth
+    assert synth.work_candidates(100) == 1538430 and synth.work_candidates(400) == 45149380
+    seq, off = synth.random_sequences(16, 100, 100)
+    assert seq.shape == (1600,) and off[-1] == 1600 and set(seq.tobytes()) <= set(b"ACGU")
+    lens = synth.eterna_mixed_lengths(1000)
+    assert lens.min() >= 12 and lens.max() <= 400
+    tg = synth.random_targets(off, 1)
+    for k in range(16):
+        s = tg[off[k]:off[k + 1]].tobytes().decode()
+        depth = 0
+        for c in s:
+            depth += (c == "(") - (c == ")")
+            assert depth >= 0
+        assert depth == 0
+
+
+_GLOO_WORKER = r"""
+import os, sys
+sys.path.insert(0, {root!r})
+import torch.distributed as dist
+from rnagent_b200 import RolloutStats, shard_targets
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+targets = ["t%d" % k for k in range(7)]
+mine = shard_targets(targets, rank, world)
+local = RolloutStats(episodes=len(mine), solved=rank, sum_hd=10 * (rank + 1), steps=100 + rank, sum_reward=0.5 * (rank + 1), sum_mfe=-1.5 * (rank + 1))
+tot = local.all_reduce()
+assert tot.episodes == 7 and tot.solved == 1 and tot.sum_hd == 30 and tot.steps == 201, vars(tot)
+assert abs(tot.sum_reward - 1.5) < 1e-12 and abs(tot.sum_mfe + 4.5) < 1e-12
+assert sorted(mine + shard_targets(targets, 1 - rank, world)) == sorted(targets)
+dist.destroy_process_group()
+print("ok", rank)
+"""
+
+
+def test_rollout_stats_all_reduce_gloo_world2(tmp_path):
+    port = 29500 + os.getpid() % 400
+    script = tmp_path / "w.py"
+    script.write_text(_GLOO_WORKER.format(root=ROOT, port=port))
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r))
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    for p in procs:
+        out, _ = p.communicate(timeout=120)
+        assert p.returncode == 0, out.decode()
