@@ -29,8 +29,7 @@ def test_replays_reference_episodes_bit_for_bit(golden):
     for e in eps:                       # the recording walked its target list round-robin, starting at index 1
         if e["target"] not in targets:
             targets.append(e["target"])
-    first = targets.index(eps[0]["target"])
-    targets = targets[first - 1:] + targets[:first - 1] if first else targets
+    targets = targets[-1:] + targets[:-1]      # the constructor takes target 0, the first reset() moves on to 1
     n_envs = 3
     env = rnagent_b200.RnaDesignBatch(golden["config"], n_envs, targets=targets, auto_reset=False)
     for e in eps:
