@@ -104,6 +104,7 @@ __device__ __forceinline__ void split_run(const ST *__restrict__ pa, const ST *_
                                           int &acc0, int &acc1) {
   const int sA = UPA ? rp : 1 - rp, sB = UPB ? rp : 1 - rp;
   int k = 0;
+#pragma unroll 1
   for (; k + 8 <= cnt; k += 8) {
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
@@ -113,6 +114,7 @@ __device__ __forceinline__ void split_run(const ST *__restrict__ pa, const ST *_
     pa += 8 * sA;
     pb += 8 * sB;
   }
+#pragma unroll 1
   for (; k < cnt; ++k) {
     acc0 = __viaddmin_s32((int)*pa, (int)*pb, acc0);
     pa += sA;
