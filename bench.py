@@ -225,14 +225,20 @@ def run_ours(args):
     resident_ms = max_over_ranks(sum(step_ms))
     checksum = int(d_mfe.sum().item())
 
-    # ---- end-to-end leg: HOST buffers through the C ABI (pinned staging, H2D, kernels, D2H)
-    h_db = np.empty_like(seq)
-    h_mfe = np.empty(B, dtype=np.int32)
-    h_hd = np.empty(B, dtype=np.int32)
-    h_rw = np.empty(B, dtype=np.float64)
+    # ---- end-to-end leg: HOST buffers through the C ABI (pinned host memory, H2D, kernels, D2H in the timed region)
+    def pinned(arr):
+        t = torch.empty(arr.shape, dtype=torch.from_numpy(arr[:0].copy()).dtype, pin_memory=True)
+        t.numpy()[...] = arr
+        return t
+    p_seq, p_tgt = pinned(seq), pinned(tgt)
+    p_db = torch.empty(total, dtype=torch.uint8, pin_memory=True)
+    p_mfe = torch.empty(B, dtype=torch.int32, pin_memory=True)
+    p_hd = torch.empty(B, dtype=torch.int32, pin_memory=True)
+    p_rw = torch.empty(B, dtype=torch.float64, pin_memory=True)
+    h_mfe = p_mfe.numpy()
 
     def step_e2e():
-        _lib.fold_hamming_raw(seq, off, B, target=tgt, db=h_db, mfe=h_mfe, hd=h_hd, reward=h_rw, reward_exp=9.0)
+        _lib.fold_hamming_raw(p_seq, off, B, target=p_tgt, db=p_db, mfe=p_mfe, hd=p_hd, reward=p_rw, reward_exp=9.0)
 
     for _ in range(max(1, min(args.warmup, 2))):
         step_e2e()
@@ -246,6 +252,11 @@ def run_ours(args):
     assert int(h_mfe.astype(np.int64).sum()) == checksum, "host-buffer and device-buffer legs disagree"
     h2d = 2 * total + 4 * (2 * B + 1)            # sequences, targets, offsets + processing order
     d2h = total + 4 * B + 4 * B + 8 * B + 4      # structures, mfe, hd, reward, status
+
+    # ---- the other two figures BASELINE.json's metric names: folds/s at n=400 and RL env steps/s
+    extra = {}
+    if args.workload == "c2" and not args.no_extra:
+        extra = secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_over_ranks)
 
     if rank != 0:
         if world > 1:
@@ -294,10 +305,76 @@ def run_ours(args):
         "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
         "checksum_mfe_dcal": checksum,
     }
+    line.update(extra)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_over_ranks):
+    """n=400 fold rate (config C3) and RL environment steps/s (config C4), every rank on its own shard."""
+    import rnagent_b200
+    out = {}
+    # C3: 8192 x n=400 per GPU, device-resident, 2 timed passes
+    seq, off, tgt, setno, desc = make_workload("c3", rank)
+    vienna.set_vienna_params(setno)
+    B = len(off) - 1
+    st = torch.cuda.Stream(device=dev)
+    d_seq, d_off, d_tgt = (torch.from_numpy(x).to(dev) for x in (seq, off, tgt))
+    d_db = torch.empty_like(d_seq)
+    d_mfe = torch.empty(B, dtype=torch.int32, device=dev)
+    d_hd = torch.empty(B, dtype=torch.int32, device=dev)
+    d_rw = torch.empty(B, dtype=torch.float64, device=dev)
+
+    def run():
+        _lib.fold_hamming_raw(d_seq, d_off, B, target=d_tgt, db=d_db, mfe=d_mfe, hd=d_hd, reward=d_rw, reward_exp=9.0,
+                              stream=st.cuda_stream)
+    with torch.cuda.stream(st):
+        run()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        run()
+        run()
+        e1.record(st)
+        e1.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    W = total_work(off)
+    out["n400"] = {"metric": "mfe_folds_per_sec_n400", "value": world * 2 * B / (ms * 1e-3), "unit": "folds/s",
+                   "workload": desc, "ms_per_pass": ms / 2, "candidates_per_s": world * 2 * W / (ms * 1e-3),
+                   "routed": _lib.last_launch_info()[1]}
+    # C4: 4096 environments per GPU, n=100 targets (folds of random sequences), random actions, auto-reset
+    vienna.set_vienna_params(1)
+    sseq, soff = synth.random_sequences(256, 100, 4100 + rank)
+    targets, _ = rnagent_b200.fold_batch([sseq[soff[k]:soff[k + 1]].tobytes().decode() for k in range(256)])
+    cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True)
+    N, steps = 4096, 300
+    env = rnagent_b200.RnaDesignBatch(cfg, N, targets=targets, rank=rank, auto_reset=True, randomize=True, seed=rank)
+    g = torch.Generator(device=dev)
+    g.manual_seed(rank)
+    acts = torch.randint(0, 4, (steps + 20, N), dtype=torch.int32, device=dev, generator=g)
+    d_obs = torch.empty((N, 10, 50), dtype=torch.uint8, device=dev)
+    d_r = torch.empty(N, dtype=torch.float64, device=dev)
+    d_done = torch.empty(N, dtype=torch.uint8, device=dev)
+    env.reset()
+    for k in range(20):
+        env.step_device(acts[k], d_obs, d_r, d_done)
+    env.stats(clear=True)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(steps):
+        env.step_device(acts[20 + k], d_obs, d_r, d_done)
+    torch.cuda.synchronize()
+    secs = max_over_ranks(time.perf_counter() - t0)
+    stats = env.stats().all_reduce(device=dev)          # the path's only collective: rollout statistics over NCCL
+    env.close()
+    out["env"] = {"metric": "rl_env_steps_per_sec", "value": stats.steps / secs, "unit": "env steps/s",
+                  "episodes_per_s": stats.episodes / secs, "envs_per_gpu": N, "steps_timed": steps,
+                  "workload": "4096 RnaDesign envs per GPU, n=100 targets (folds of random sequences), uniform random actions, "
+                              "auto-reset; observations, rewards and dones stay on the device",
+                  "stats": stats.summary()}
+    return out
 
 
 def main():
@@ -309,6 +386,7 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the n=400 and env-steps measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -115,6 +115,17 @@ bool is_device_ptr(const void *p) {
   return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
 }
 
+bool is_pinned_host_ptr(const void *p) {
+  // page-locked host memory (cudaMallocHost / cudaHostRegister / torch pin_memory): DMA-able in place
+  if (!p) return false;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
 int upload_params(Context *c) {
   CUDA_TRY(cudaMemcpyAsync(c->d_params, &c->hp.dev, sizeof(FoldParams), cudaMemcpyHostToDevice, c->stream));
   CUDA_TRY(wave_upload_constants(c->hp, c->stream));
@@ -230,17 +241,25 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   const uint8_t *d_target = target;
   if (!seq_dev) {
     CUDA_TRY(c->d_seq.reserve(total + 16));
-    CUDA_TRY(c->h_in.reserve(2 * total + 32));
-    std::memcpy(c->h_in.p, seq, total);
-    CUDA_TRY(cudaMemcpyAsync(c->d_seq.p, c->h_in.p, total, cudaMemcpyHostToDevice, st));
+    const void *src = seq;
+    if (!is_pinned_host_ptr(seq)) {  // pageable memory is staged through the library's pinned block
+      CUDA_TRY(c->h_in.reserve(2 * total + 32));
+      std::memcpy(c->h_in.p, seq, total);
+      src = c->h_in.p;
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->d_seq.p, src, total, cudaMemcpyHostToDevice, st));
     d_seq = (const uint8_t *)c->d_seq.p;
   }
   if (target && !tgt_dev) {
     CUDA_TRY(c->d_target.reserve(total + 16));
-    CUDA_TRY(c->h_in.reserve(2 * total + 32));
-    uint8_t *stage = (uint8_t *)c->h_in.p + total + 16;
-    std::memcpy(stage, target, total);
-    CUDA_TRY(cudaMemcpyAsync(c->d_target.p, stage, total, cudaMemcpyHostToDevice, st));
+    const void *src = target;
+    if (!is_pinned_host_ptr(target)) {
+      CUDA_TRY(c->h_in.reserve(2 * total + 32));
+      uint8_t *stage = (uint8_t *)c->h_in.p + total + 16;
+      std::memcpy(stage, target, total);
+      src = stage;
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->d_target.p, src, total, cudaMemcpyHostToDevice, st));
     d_target = (const uint8_t *)c->d_target.p;
   }
   {
@@ -370,7 +389,8 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     uint8_t *ho = (uint8_t *)c->h_out.p;
     auto back = [&](void *user, void *dev, size_t off_b, size_t bytes) -> cudaError_t {
       if (!user || is_device_ptr(user) || bytes == 0) return cudaSuccess;
-      return cudaMemcpyAsync(ho + off_b, dev, bytes, cudaMemcpyDeviceToHost, st);
+      // pinned user buffers receive the DMA directly; pageable ones go through the pinned block
+      return cudaMemcpyAsync(is_pinned_host_ptr(user) ? user : (void *)(ho + off_b), dev, bytes, cudaMemcpyDeviceToHost, st);
     };
     CUDA_TRY(back(db_out, v_db, o_db, total));
     CUDA_TRY(back(mfe_out, v_mfe, o_mfe, 4 * (size_t)B));
@@ -381,7 +401,7 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     CUDA_TRY(cudaMemcpyAsync(&status, d_ctl + 2 * nl, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     auto fin = [&](void *user, size_t off_b, size_t bytes) {
-      if (user && !is_device_ptr(user) && bytes) std::memcpy(user, ho + off_b, bytes);
+      if (user && !is_device_ptr(user) && !is_pinned_host_ptr(user) && bytes) std::memcpy(user, ho + off_b, bytes);
     };
     fin(db_out, o_db, total);
     fin(mfe_out, o_mfe, 4 * (size_t)B);

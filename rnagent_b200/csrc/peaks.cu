@@ -19,8 +19,8 @@ constexpr int kPeakIters = 512;
 constexpr int kPeakUnroll = 16;
 
 __global__ void __launch_bounds__(kPeakThreads) lds_stream_kernel(int *out, int iters) {
-  __shared__ int buf[kPeakThreads * 4];
-  for (int k = threadIdx.x; k < kPeakThreads * 4; k += kPeakThreads) buf[k] = k * 7 + blockIdx.x;
+  __shared__ int buf[kPeakThreads * kPeakUnroll];
+  for (int k = threadIdx.x; k < kPeakThreads * kPeakUnroll; k += kPeakThreads) buf[k] = k * 7 + blockIdx.x;
   __syncthreads();
   const unsigned base = (unsigned)__cvta_generic_to_shared(buf) + 4u * threadIdx.x;
   int acc[kPeakUnroll];
@@ -31,8 +31,8 @@ __global__ void __launch_bounds__(kPeakThreads) lds_stream_kernel(int *out, int 
     for (int u = 0; u < kPeakUnroll; ++u) {
       int v;
       // consecutive lanes -> consecutive words (conflict free); rows rotate so loads stay distinct
-      // the address changes every iteration so no load can be hoisted or merged
-      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + 4u * kPeakThreads * (unsigned)((u + it) & 3)));
+      // 16 distinct rows per iteration, rotating with `it`: no two loads of an iteration share an address
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + 4u * kPeakThreads * (unsigned)((u + it) & (kPeakUnroll - 1))));
       acc[u] += v;
     }
   }
@@ -61,6 +61,7 @@ __global__ void __launch_bounds__(kPeakThreads) minplus_stream_kernel(int *out, 
 
 // Returns per-second rates over the whole device (all SMs busy, 8 CTAs of 256 threads per SM).
 cudaError_t measure_onchip_peaks(int num_sms, cudaStream_t st, double *lds_per_s, double *minplus_per_s) {
+  // 256 threads x 16 KB static shared memory: 8 CTAs per SM stay resident (128 KB)
   int *d_out = nullptr;
   cudaError_t e = cudaMalloc((void **)&d_out, 64);
   if (e != cudaSuccess) return e;
