@@ -108,7 +108,9 @@ def cpu_fold_rate(seq, off, tgt, setno, budget_s, nthreads=0):
     """Oracle port of RNA.fold on the host cores over a bounded sample -> (folds/s, cores, sample B, seconds)."""
     import oracle
     P = oracle.Params(os.path.join(ROOT, "rnagent_b200", "data", f"{PARAM_NAMES[setno]}_37.par"))
-    cores = nthreads or (os.cpu_count() or 1)
+    # explicit thread count: torchrun exports OMP_NUM_THREADS=1, which would silently serialise the OpenMP driver
+    cores = nthreads or len(os.sched_getaffinity(0)) or 1
+    nthreads = cores
     B = len(off) - 1
     probe = min(B, max(2 * cores, 16))
     t0 = time.perf_counter()
