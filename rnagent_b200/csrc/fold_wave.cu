@@ -62,10 +62,14 @@ __host__ __device__ constexpr int part_beg(int r) {
 #endif
 }
 __device__ __forceinline__ int part_beg_rt(int r) { return part_beg(r); }
+constexpr int kEParts = 3;            // loop-size ranges of the bulge / 1xn work items of the wave kernel
+constexpr int kWSlots = 2 + kEParts;  // wave kernel scratch rows: generic shapes, tabulated shapes, one per E part
+__host__ __device__ constexpr int epart_beg(int r) { return r == 0 ? 2 : r == 1 ? 12 : r == 2 ? 22 : 31; }
 constexpr int kMaxMlParts = 4;
 constexpr int kBig = 10000000;  // additive term that can never win a minimum
 constexpr int kFullWinMax = 128;  // up to this length the cI / c1 tables are full triangles (cheaper row offsets)
 constexpr int kMlChunk = 128;  // split points per multiloop work item
+constexpr int kGenSlots = 12 * 32;  // lane slots of the shape-parallel generic interior item (375 shapes + padding)
 
 template <typename ST> struct Store;
 template <> struct Store<int16_t> {
@@ -159,7 +163,7 @@ __host__ __device__ constexpr int shape_class(int n1, int n2) {
 __host__ __device__ constexpr int wave_np(int nmax) { return (nmax + 9) & ~1; }  // even row pitch of the scratch rows
 
 struct WaveSmem {
-  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, pl_off, plo_off, total;
+  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, pl_off, plo_off, gd_off, total;
   int rs;        // window row stride (elements)
   int mlparts;   // max multiloop parts per cell
   __host__ __device__ static WaveSmem make(int nmax, int esz) {
@@ -175,7 +179,7 @@ struct WaveSmem {
     L.ptab_off = take(64);
     L.S_off = take(np);
     L.db_off = take(np);
-    L.part_off = take(2 * kSlots * np * esz);       // [parity][slot][cell]; slot = part, last = tabulated shapes
+    L.part_off = take(2 * kWSlots * np * esz);      // [parity][slot][cell]; slot 0 generic, 1 tabulated, 2.. bulge/1xn parts
     L.bt_off = L.part_off;                          // the backtrack stack reuses the scratch rows after the fill
     L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
     const int cells = table_cells(nmax) + 64;
@@ -186,6 +190,7 @@ struct WaveSmem {
     L.w1_off = take((kWin * L.rs + 64) * esz);  // c1 is only read at the two ends of a row: always a window
     L.pl_off = take(nmax * nmax / 4 + 64);          // cells whose ends can pair, diagonal by diagonal (uint8 index)
     L.plo_off = take(np * 2);                       // first list entry of each diagonal (+ total at [n])
+    L.gd_off = take(kGenSlots * 2);                 // (L, n1) of the generic shape in each lane slot
     L.total = o;
     return L;
   }
@@ -205,7 +210,7 @@ __device__ __forceinline__ void generic_body(const ST *__restrict__ row, const i
   for (int k = 0; k < W; ++k) a[k & 3] = __viaddmin_s32((int)row[k], g[k], a[k & 3]);
 }
 
-template <typename ST, bool FULLW, bool BWIN = false>
+template <typename ST, bool FULLW, bool BWIN = false, bool GEN = true>
 __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const ST *__restrict__ p1,
                                               const ST *__restrict__ pB, int d, int n, int rs, int l0, int l1,
                                               int (&aI)[4], int &a1, int &aB) {
@@ -220,7 +225,7 @@ __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const S
     aB = __viaddmin_s32((int)pB[offb + L], gb, aB);
     a1 = __viaddmin_s32((int)p1[offw + 1], g1, a1);
     a1 = __viaddmin_s32((int)p1[offw + L - 1], g1, a1);
-    if (L >= 6) {  // generic shapes n1 = 2 .. L-2: smallest unrolled body that covers them
+    if (GEN && L >= 6) {  // generic shapes n1 = 2 .. L-2: smallest unrolled body that covers them
       const ST *row = pI + offi + 2;
       const int *g = &cW.GI[L][2];
 #if !WAVE_FINE
@@ -243,6 +248,55 @@ __device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const S
     off -= step;
     ++step;
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// G(cell): the generic interior shapes (n1, n2 >= 2, not 2x2 / 2x3 / 3x2) of ONE pairable cell, lanes
+// across SHAPES.  The 375 shapes with loop size 6..30 are numbered by (L, n1) ascending; lane l owns
+// shapes l, l+32, ... (12 register slots: element offset into the cI table, its per-diagonal step and
+// the shape's size + asymmetry term).  Offsets follow the quadratic recurrence of the diagonal-major
+// layout (off += step, step -= 1 per diagonal), so a candidate costs one address add, one LDS and
+// one VIADDMNMX with every lane busy, however few pairable cells a diagonal has.  Shapes with
+// L > d-6 are not valid yet: because the numbering is L-major they are exactly the slots >= nvalid(d).
+// ---------------------------------------------------------------------------------------------
+constexpr int kGenShapes = 375;
+constexpr int kGenIters = 12;
+static_assert(kGenIters * 32 == kGenSlots, "slot bookkeeping");
+__host__ __device__ constexpr int gen_before(int L) { return L <= 6 ? 0 : (L - 4) * (L - 3) / 2 - 3; }  // shapes with size < L
+__device__ __forceinline__ int gen_valid(int d) {
+  const int lmax = min(kMaxLoop, d - 6);
+  return lmax < 6 ? 0 : (lmax == kMaxLoop ? kGenIters * 32 : gen_before(lmax + 1));
+}
+
+template <typename ST, bool ALL>
+__device__ __forceinline__ int gen_cell(const unsigned char *__restrict__ tab, int xb, const int (&goff)[kGenIters],
+                                        const int (&g)[kGenIters], int nvalid, int lane) {
+  // goff[] are BYTE offsets into the table, xb the (warp-uniform) byte offset of the cell
+  const unsigned char *base = tab + xb;
+  int a0 = Store<ST>::kInfS, a1 = Store<ST>::kInfS, a2 = Store<ST>::kInfS, a3 = Store<ST>::kInfS;
+  if (ALL) {
+#pragma unroll
+    for (int k = 0; k < kGenIters; ++k) {
+      const int v = (int)*reinterpret_cast<const ST *>(base + goff[k]);
+      if ((k & 3) == 0) a0 = __viaddmin_s32(v, g[k], a0);
+      else if ((k & 3) == 1) a1 = __viaddmin_s32(v, g[k], a1);
+      else if ((k & 3) == 2) a2 = __viaddmin_s32(v, g[k], a2);
+      else a3 = __viaddmin_s32(v, g[k], a3);
+    }
+  } else {
+    const int nv = nvalid - lane;
+#pragma unroll
+    for (int k = 0; k < kGenIters; ++k) {
+      if (32 * k < nvalid) {           // warp-uniform early out
+        if (32 * k < nv) {             // this lane's slot is a valid shape on this diagonal
+          const int v = (int)*reinterpret_cast<const ST *>(base + goff[k]);
+          if (k & 1) a1 = __viaddmin_s32(v, g[k], a1);
+          else a0 = __viaddmin_s32(v, g[k], a0);
+        }
+      }
+    }
+  }
+  return __reduce_min_sync(0xffffffffu, min(min(a0, a1), min(a2, a3)));
 }
 
 template <typename ST>
@@ -443,8 +497,15 @@ __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, cons
 // ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
+// Register budgets: 96 registers keep the 5 CTAs/SM that shared memory allows at n = 100 (128-thread
+// instance); 128 keep 2 CTAs of 256 threads (n <= 160) and the single 512-thread CTA.  __maxnreg__ is used
+// instead of __launch_bounds__' minBlocks because the latter changes ptxas' unrolling heuristics as well
+// (measured: +20 % instructions, instruction-cache misses).
+#ifndef WAVE_MAXREG128
+#define WAVE_MAXREG128 96
+#endif
 template <typename ST, int MAXT>
-__global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
+__global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128 : 128) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
                                                         int *__restrict__ queue) {
   extern __shared__ __align__(16) unsigned char smem[];
   const WaveSmem Ls = WaveSmem::make(nmax, (int)sizeof(ST));
@@ -472,6 +533,21 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
   const int tau = cW.TerminalAU;
 
   if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
+  // generic interior shapes, numbered by (L, n1): slot s -> L | n1 << 8 (padding slots repeat the last shape)
+  unsigned short *gdesc = reinterpret_cast<unsigned short *>(smem + Ls.gd_off);
+  for (int sidx = tid; sidx < kGenSlots; sidx += NT) {
+    const int sc = min(sidx, kGenShapes - 1);
+    int L = 6;
+    while (gen_before(L + 1) <= sc) ++L;
+    gdesc[sidx] = (unsigned short)(L | ((2 + sc - gen_before(L)) << 8));
+  }
+  __syncthreads();
+  int gterm[kGenIters], goff[kGenIters], gstep[kGenIters];
+#pragma unroll
+  for (int k = 0; k < kGenIters; ++k) {
+    const int ds = gdesc[32 * k + lane];
+    gterm[k] = (32 * k + lane < kGenShapes) ? cW.GI[ds & 255][ds >> 8] : kBig;
+  }
   auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
   auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
 
@@ -542,12 +618,26 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
     }
     __syncthreads();
 
+    // generic-shape slots at d = 4: element offset of (row d-2-L, column 1+n1) and its per-diagonal step
+#pragma unroll
+    for (int k = 0; k < kGenIters; ++k) {
+      const int ds = gdesc[32 * k + lane];
+      const int L = ds & 255, n1 = ds >> 8;
+      if (kFullW) {
+        goff[k] = (tri(n, kTurn + 1 - 2 - L) + 1 + n1) * (int)sizeof(ST);
+        gstep[k] = (n - (kTurn + 1) + 2 + L) * (int)sizeof(ST);
+      } else {
+        goff[k] = (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);
+        gstep[k] = (1 + n1) * (int)sizeof(ST);
+      }
+    }
+
     for (int d = kTurn + 1; d <= n + 1; ++d) {
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
       const int nb_d = (cells_d + 31) >> 5;
       const int lmax = min(kMaxLoop, d - 6);
-      const int npd = nparts_of(d, n), mpd = mlparts_of(d, n);
+      const int mpd = mlparts_of(d, n);
       const int d1 = d - 1;
       const int cells_1 = (d1 >= kTurn + 1 && d1 < n) ? n - d1 : 0;
       const int nb_1 = (cells_1 + 31) >> 5;
@@ -555,26 +645,62 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
       const int pl0 = (d < n) ? (int)plo[d] : 0;
       const int npair = (d < n) ? (int)plo[d + 1] - pl0 : 0;
       const int nbI = (npair + 31) >> 5;
-      const int nI = nbI * npd, nT = (lmax >= 0) ? nbI : 0, nM = nb_d * mpd, nF = nb_1;
+      // ---------------- G(cell): generic interior shapes, lanes across shapes, one pairable cell at a time
+      const int nvalid = (d < n) ? gen_valid(d) : 0;
+      if (nvalid == kGenSlots) {
+#pragma unroll 1
+        for (int c = warp; c < npair; c += NW) {
+          // the reduction returns the (already uniform) cell index in a uniform register: addresses become [R + UR]
+          const int xv = pl[pl0 + c];
+          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int r = gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
+          if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
+        }
+      } else if (nvalid > 0) {
+#pragma unroll 1
+        for (int c = warp; c < npair; c += NW) {
+          // the reduction returns the (already uniform) cell index in a uniform register: addresses become [R + UR]
+          const int xv = pl[pl0 + c];
+          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int r = gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
+          if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
+        }
+      }
+      // next diagonal: every slot moves one row down its table
+#pragma unroll
+      for (int k = 0; k < kGenIters; ++k) {
+        if (kFullW) {
+          goff[k] += gstep[k];
+          gstep[k] -= (int)sizeof(ST);
+        } else {
+          const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
+          goff[k] = (u >= gstep[k]) ? u : t;
+        }
+      }
+      // the block items start with the warp after the last one that took a cell, to even out the phase
+      const int nG = nvalid > 0 ? npair : 0;
+      int neparts = 0;
+#pragma unroll
+      for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
+      const int nI = nbI * neparts, nT = (lmax >= 0) ? nbI : 0, nM = nb_d * mpd, nF = nb_1;
       const int total = nI + nT + nM + nF + has_x;
-      for (int k = warp; k < total; k += NW) {
+      int k0 = warp - (nG & (NW - 1));
+      if (k0 < 0) k0 += NW;
+      for (int k = k0; k < total; k += NW) {
         if (k < nI) {
-          // ---------------- I(b,r): generic / 1xn / bulge shapes of loop sizes in part r
-          const int r = div_small(k, nbI, kParts), blk = k - r * nbI;
-          const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
+          // ---------------- E(b,r): bulges and 1xn loops of the loop sizes in part r, lanes across pairable cells
+          const int r = div_small(k, nbI, kEParts), blk = k - r * nbI;
+          const int l0 = r == 0 ? epart_beg(0) : r == 1 ? epart_beg(1) : epart_beg(2);
+          const int l1 = min((r == 0 ? epart_beg(1) : r == 1 ? epart_beg(2) : epart_beg(3)) - 1, lmax);
           const int idx = blk * 32 + lane;
-          const int x = pl[pl0 + min(idx, npair - 1)];  // only cells whose ends can pair are scanned
+          const int x = pl[pl0 + min(idx, npair - 1)];
           int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
-          interior_item<ST, kFullW>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
+          interior_item<ST, kFullW, false, false>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
           if (idx < npair) {
-            // close the three shape classes with the outer pair's terms: one candidate minimum per part
             const int i = x + 1, j = i + d;
             const int type = PT(S[i], S[j]);
-            const int si1 = S[i + 1], sj1 = S[j - 1];
-            int e = min(min(aI[0], aI[1]), min(aI[2], aI[3])) + __ldg(&sp.mmI[type][si1][sj1]);
-            e = min(e, a1 + __ldg(&sp.mm1nI[type][si1][sj1]));
-            e = min(e, aB + (type > 2 ? tau : 0));
-            part[(par * kSlots + r) * np + x] = (ST)min(e, kInfS);
+            const int e = min(a1 + __ldg(&sp.mm1nI[type][S[i + 1]][S[j - 1]]), aB + (type > 2 ? tau : 0));
+            part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
           }
         } else if (k < nI + nT) {
           // ---------------- T(b): the 9 tabulated shapes of diagonal d
@@ -605,7 +731,7 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
                 }
               }
             }
-            part[(par * kSlots + kParts) * np + x] = (ST)min(best, kInfS);
+            part[(par * kWSlots + 1) * np + x] = (ST)min(best, kInfS);
           }
         } else if (k < nI + nT + nM) {
           // ---------------- M(b,m): multibranch split points t0..t1-1 of diagonal d
@@ -628,10 +754,12 @@ __global__ void __launch_bounds__(MAXT) fold_wave_kernel(const FoldParams *__res
             const int wrow = kFullW ? tri(n, d1) + x : wrow1;
             if (type) {
               cij = e_hairpin(sp, gp, S, i, j, type);
-              const int np1 = nparts_of(d1, n);
-              const ST *src = part + (par1 * kSlots) * np + x;
-              for (int r = 0; r < np1; ++r) cij = min(cij, (int)src[r * np]);
-              if (d1 >= 6) cij = min(cij, (int)src[kParts * np]);
+              const ST *src = part + (par1 * kWSlots) * np + x;
+              if (d1 >= 12) cij = min(cij, (int)src[0] + __ldg(&sp.mmI[type][si1][sj1]));  // generic shapes (L >= 6)
+              if (d1 >= 6) cij = min(cij, (int)src[np]);                                    // tabulated shapes
+#pragma unroll
+              for (int r = 0; r < kEParts; ++r)                                             // bulges, 1xn of loop sizes >= epart_beg(r)
+                if (d1 - 6 >= epart_beg(r)) cij = min(cij, (int)src[(2 + r) * np]);
               if (d1 >= 2 * kTurn + 4)
                 cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
               const int rt = rtype_of(type);

@@ -5,7 +5,7 @@ lines_file, src = sys.argv[1], sys.argv[2]
 text = open(src).read().splitlines()
 marks = []
 for k, ln in enumerate(text, 1):
-    m = re.search(r"// -+ ([ITMFX])\(?.*?:|// ---- (backtrack|emit)|for \(int d = kTurn \+ 1; d <= n \+ 1", ln)
+    m = re.search(r"// -+ ([ITMFXGE])\(?.*?:|// ---- (backtrack|emit)|for \(int d = kTurn \+ 1; d <= n \+ 1", ln)
     if m:
         marks.append((k, m.group(1) or m.group(2) or "phase ovh"))
     if re.match(r"(template|__device__ __forceinline__|__global__)", ln):
