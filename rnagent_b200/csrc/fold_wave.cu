@@ -41,6 +41,19 @@ struct WaveConst {
 };
 __constant__ WaveConst cW;
 
+#ifdef WAVE_PHASE_CLK  // debug builds only: cycles per phase, summed over all folds (tools/phase_clocks.py)
+__device__ unsigned long long g_phase_clk[640];
+#ifndef WAVE_SKIP
+#define WAVE_SKIP 0  // debug: bit mask of item kinds to skip (timing experiments only, results are wrong): 1 G, 2 E, 4 T, 8 M, 16 F, 32 X
+#endif
+#define PHASE_CLK_BEGIN() long long clk_t0 = (tid == 0) ? clock64() : 0
+#define PHASE_CLK_END(slot) do { if (tid == 0) { const long long t1 = clock64(); atomicAdd(&g_phase_clk[slot], (unsigned long long)(t1 - clk_t0)); clk_t0 = t1; } } while (0)
+#else
+#define WAVE_SKIP 0
+#define PHASE_CLK_BEGIN() do { } while (0)
+#define PHASE_CLK_END(slot) do { } while (0)
+#endif
+
 namespace {
 
 constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are read by phase d)
@@ -49,6 +62,9 @@ constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are r
 #endif
 #ifndef WAVE_FINE
 #define WAVE_FINE 0
+#endif
+#ifndef WAVE_DYN
+#define WAVE_DYN 0  // 1: work items of a phase are claimed dynamically (shared-memory counter) instead of round-robin
 #endif
 constexpr int kParts = WAVE_PARTS;   // loop-size ranges of the interior work items
 constexpr int kSlots = kParts + 1;  // one candidate minimum per part + the tabulated shapes
@@ -504,8 +520,12 @@ __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, cons
 #ifndef WAVE_MAXREG128
 #define WAVE_MAXREG128 96
 #endif
+#ifndef WAVE_T128
+#define WAVE_T128 128  // threads per CTA of the short-sequence instance (n <= 128)
+#endif
+constexpr int kSmallThreads = WAVE_T128;
 template <typename ST, int MAXT>
-__global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128 : 128) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
+__global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && sizeof(ST) == 2 ? WAVE_MAXREG128 : 128) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
                                                         int *__restrict__ queue) {
   extern __shared__ __align__(16) unsigned char smem[];
   const WaveSmem Ls = WaveSmem::make(nmax, (int)sizeof(ST));
@@ -529,7 +549,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
   const SmallParams &sp = gp->s;
   constexpr int kInfS = Store<ST>::kInfS;
-  constexpr bool kFullW = (MAXT == 128);  // wave_threads(): 128 threads <=> nmax <= kFullWinMax
+  constexpr bool kFullW = (MAXT == kSmallThreads);  // wave_threads(): the short-sequence instance <=> nmax <= kFullWinMax
   const int tau = cW.TerminalAU;
 
   if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
@@ -542,12 +562,6 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
     gdesc[sidx] = (unsigned short)(L | ((2 + sc - gen_before(L)) << 8));
   }
   __syncthreads();
-  int gterm[kGenIters], goff[kGenIters], gstep[kGenIters];
-#pragma unroll
-  for (int k = 0; k < kGenIters; ++k) {
-    const int ds = gdesc[32 * k + lane];
-    gterm[k] = (32 * k + lane < kGenShapes) ? cW.GI[ds & 255][ds >> 8] : kBig;
-  }
   auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
   auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
 
@@ -558,10 +572,12 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
       misc[1] = 0;  // backtrack failure code
       misc[2] = 0;  // Hamming accumulator
       misc[3] = 0;  // range-check flag
+      misc[8] = misc[9] = misc[10] = misc[11] = 0;  // per-phase work counters (WAVE_DYN)
     }
     __syncthreads();
     const int slot = misc[0];
     if (slot >= a.B) break;
+    PHASE_CLK_BEGIN();
     const int b = a.order ? a.order[slot] : slot;
     const int beg = a.off[b];
     const int n = a.off[b + 1] - beg;
@@ -618,17 +634,22 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
     }
     __syncthreads();
 
-    // generic-shape slots at d = 4: element offset of (row d-2-L, column 1+n1) and its per-diagonal step
+    PHASE_CLK_END(600);  // prologue
+    // generic-shape slots at d = 4: element offset of (row d-2-L, column 1+n1), its per-diagonal step and
+    // the shape's size + asymmetry term (nothing of this is live across the backtrack)
+    int gterm[kGenIters], goff[kGenIters];
+    unsigned gpack[kGenIters / 4] = {};  // one byte per slot: L * esz (full tables) or (1 + n1) * esz (windows)
 #pragma unroll
     for (int k = 0; k < kGenIters; ++k) {
       const int ds = gdesc[32 * k + lane];
       const int L = ds & 255, n1 = ds >> 8;
+      gterm[k] = (32 * k + lane < kGenShapes) ? cW.GI[L][n1] : kBig;
       if (kFullW) {
         goff[k] = (tri(n, kTurn + 1 - 2 - L) + 1 + n1) * (int)sizeof(ST);
-        gstep[k] = (n - (kTurn + 1) + 2 + L) * (int)sizeof(ST);
+        gpack[k >> 2] |= (unsigned)(L * (int)sizeof(ST)) << (8 * (k & 3));
       } else {
         goff[k] = (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);
-        gstep[k] = (1 + n1) * (int)sizeof(ST);
+        gpack[k >> 2] |= (unsigned)((1 + n1) * (int)sizeof(ST)) << (8 * (k & 3));
       }
     }
 
@@ -646,47 +667,56 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
       const int npair = (d < n) ? (int)plo[d + 1] - pl0 : 0;
       const int nbI = (npair + 31) >> 5;
       // ---------------- G(cell): generic interior shapes, lanes across shapes, one pairable cell at a time
-      const int nvalid = (d < n) ? gen_valid(d) : 0;
+      const int nvalid = (d < n && !(WAVE_SKIP & 1)) ? gen_valid(d) : 0;
+#if !WAVE_DYN
       if (nvalid == kGenSlots) {
 #pragma unroll 1
         for (int c = warp; c < npair; c += NW) {
-          // the reduction returns the (already uniform) cell index in a uniform register: addresses become [R + UR]
           const int xv = pl[pl0 + c];
-          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int xb = xv * (int)sizeof(ST);
           const int r = gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
           if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
         }
       } else if (nvalid > 0) {
 #pragma unroll 1
         for (int c = warp; c < npair; c += NW) {
-          // the reduction returns the (already uniform) cell index in a uniform register: addresses become [R + UR]
           const int xv = pl[pl0 + c];
-          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int xb = xv * (int)sizeof(ST);
           const int r = gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
           if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
         }
       }
-      // next diagonal: every slot moves one row down its table
-#pragma unroll
-      for (int k = 0; k < kGenIters; ++k) {
-        if (kFullW) {
-          goff[k] += gstep[k];
-          gstep[k] -= (int)sizeof(ST);
-        } else {
-          const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
-          goff[k] = (u >= gstep[k]) ? u : t;
-        }
-      }
+#endif
       // the block items start with the warp after the last one that took a cell, to even out the phase
       const int nG = nvalid > 0 ? npair : 0;
       int neparts = 0;
 #pragma unroll
       for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
-      const int nI = nbI * neparts, nT = (lmax >= 0) ? nbI : 0, nM = nb_d * mpd, nF = nb_1;
-      const int total = nI + nT + nM + nF + has_x;
-      int k0 = warp - (nG & (NW - 1));
+      const int nI = (WAVE_SKIP & 2) ? 0 : nbI * neparts, nT = (lmax >= 0 && !(WAVE_SKIP & 4)) ? nbI : 0, nM = (WAVE_SKIP & 8) ? 0 : nb_d * mpd, nF = (WAVE_SKIP & 16) ? 0 : nb_1;
+      const int total = nI + nT + nM + nF + ((WAVE_SKIP & 32) ? 0 : has_x);
+#if WAVE_DYN
+      // items are claimed from a per-phase counter, heaviest kinds first, the single-cell G items last as filler
+      int *qc = misc + 8 + (d & 3);
+      if (tid == 0) misc[8 + ((d + 1) & 3)] = 0;
+      for (;;) {
+        int k = 0;
+        if (lane == 0) k = atomicAdd(qc, 1);
+        k = __shfl_sync(0xffffffffu, k, 0);
+        if (k >= total + nG) break;
+        if (k >= total) {
+          const int xv = pl[pl0 + k - total];
+          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int r = (nvalid == kGenSlots)
+                            ? gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane)
+                            : gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
+          if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
+          continue;
+        }
+#else
+      int k0 = warp - (nG % NW);
       if (k0 < 0) k0 += NW;
       for (int k = k0; k < total; k += NW) {
+#endif
         if (k < nI) {
           // ---------------- E(b,r): bulges and 1xn loops of the loop sizes in part r, lanes across pairable cells
           const int r = div_small(k, nbI, kEParts), blk = k - r * nbI;
@@ -717,18 +747,18 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
                 si[u] = S[i + u];
                 sj[u] = S[j - u];
               }
+              // branch-free: every shape's table lookups are issued unconditionally (safe indices), invalid
+              // shapes are masked at the end -- the nine dependent load chains overlap instead of serialising
 #pragma unroll
               for (int s = 0; s < 9; ++s) {
                 constexpr int kN1[9] = {0, 0, 1, 1, 1, 2, 2, 2, 3};
                 constexpr int kN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
                 const int n1 = kN1[s], n2 = kN2[s];
-                if (n1 + n2 <= d - 6) {
-                  const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
-                  if (t2) {
-                    const int cpq = craw((int)CB[tri(n, d - 2 - n1 - n2) + x + 1 + n1], t2);
-                    best = min(best, cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]));
-                  }
-                }
+                const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
+                const int row = max(d - 2 - n1 - n2, kTurn + 1);
+                const int cpq = craw((int)CB[tri(n, row) + x + 1 + n1], t2);
+                const int e = cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]);
+                best = (n1 + n2 <= d - 6 && t2 != 0) ? min(best, e) : best;
               }
             }
             part[(par * kWSlots + 1) * np + x] = (ST)min(best, kInfS);
@@ -798,7 +828,22 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
           if (lane == 0) f5[j] = min(f5[j - 1], best);
         }
       }
+      // next diagonal: every slot moves one row down its table (row d-2-L has n-d+2+L cells)
+      {
+        const int ustep = (n - d + 2) * (int)sizeof(ST);
+#pragma unroll
+        for (int k = 0; k < kGenIters; ++k) {
+          const int b = (int)((gpack[k >> 2] >> (8 * (k & 3))) & 0xffu);
+          if (kFullW) {
+            goff[k] += ustep + b;
+          } else {
+            const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
+            goff[k] = (u >= b) ? u : t;
+          }
+        }
+      }
       __syncthreads();
+      PHASE_CLK_END(d);
     }
 
     if (flag) misc[3] = 1;
@@ -811,6 +856,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
     }
     __syncthreads();
 
+    PHASE_CLK_END(601);  // backtrack
     // ---- emit structure, energy, Hamming distance, reward
     int local_hd = 0;
     for (int k = tid; k < n; k += NT) {
@@ -841,6 +887,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == 128 ? WAVE_MAXREG128
       if (Store<ST>::kChecked && a.redo) a.redo[b] = misc[3];
       if (misc[1] && !misc[3]) atomicExch(a.status, misc[1]);
     }
+    PHASE_CLK_END(602);  // emit
   }
 }
 
@@ -865,7 +912,7 @@ bool wave_int16_ok(const HostParams &hp) {
   return hi < 2700 && lo > -7000 && s.ninio >= 0;
 }
 
-int wave_threads(int nmax) { return nmax <= 128 ? 128 : (nmax <= 224 ? 256 : 512); }
+int wave_threads(int nmax) { return nmax <= kFullWinMax ? kSmallThreads : (nmax <= 224 ? 256 : 512); }
 
 cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
   static WaveConst w;  // staging must outlive the async copy
@@ -913,10 +960,10 @@ static int occupancy_t(int nmax) {
 }
 
 #define WAVE_DISPATCH(FN, ...)                                                        \
-  (esz == 2 ? (threads == 128   ? FN<int16_t, 128>(__VA_ARGS__)                        \
+  (esz == 2 ? (threads == kSmallThreads ? FN<int16_t, kSmallThreads>(__VA_ARGS__)      \
                : threads == 256 ? FN<int16_t, 256>(__VA_ARGS__)                        \
                                 : FN<int16_t, 512>(__VA_ARGS__))                       \
-            : (threads == 128   ? FN<int32_t, 128>(__VA_ARGS__)                        \
+            : (threads == kSmallThreads ? FN<int32_t, kSmallThreads>(__VA_ARGS__)      \
                : threads == 256 ? FN<int32_t, 256>(__VA_ARGS__)                        \
                                 : FN<int32_t, 512>(__VA_ARGS__)))
 
@@ -926,6 +973,18 @@ cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax,
 }
 
 int wave_occupancy(int nmax, int esz, int threads) { return WAVE_DISPATCH(occupancy_t, nmax); }
+
+#ifdef WAVE_PHASE_CLK
+extern "C" int rnafold_debug_phase_clocks(unsigned long long *out, int count, int reset) {
+  if (count > 640) count = 640;
+  cudaError_t e = cudaMemcpyFromSymbol(out, g_phase_clk, sizeof(unsigned long long) * count);
+  if (e == cudaSuccess && reset) {
+    static unsigned long long zeros[640];
+    e = cudaMemcpyToSymbol(g_phase_clk, zeros, sizeof(zeros));
+  }
+  return e == cudaSuccess ? 0 : -1;
+}
+#endif
 
 // ---- cluster path (long sequences)
 size_t cluster_smem_bytes(int nmax, int esz) { return (size_t)ClusterSmem::make(nmax, esz).total; }
