@@ -597,13 +597,36 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 
     // ---- lists of the cells whose ends can pair, one list per diagonal (at most n*n/4 entries in all):
     // the interior-loop and tabulated-shape work items run over these lists, not over all cells.
-    for (int d = kTurn + 1 + warp; d < n; d += NW) {
-      int cnt = 0;
-      for (int base = 0; base < n - d; base += 32) {
-        const int x = base + lane;
-        cnt += __popc(__ballot_sync(0xffffffffu, x < n - d && PT(S[x + 1], S[x + 1 + d]) != 0));
+    // Bit masks of the positions holding each base (one ballot per 32 positions), then one THREAD per
+    // diagonal: pairable(i, i+d) for 32 values of i is six AND/ORs of mask words against funnel-shifted
+    // mask words, so counting and listing a diagonal is a few dozen instructions, not a pass over its cells.
+    const int mstride = (n >> 5) + 3;
+    unsigned *bm = reinterpret_cast<unsigned *>(dml);  // [4][mstride], dml is idle until the first phases
+    for (int w = warp; w < mstride; w += NW) {
+      const int pp = w * 32 + lane;
+      const int code = (pp >= 1 && pp <= n) ? (int)S[pp] : 0;
+#pragma unroll
+      for (int c = 1; c <= 4; ++c) {
+        const unsigned m = __ballot_sync(0xffffffffu, code == c);
+        if (lane == 0) bm[(c - 1) * mstride + w] = m;
       }
-      if (lane == 0) plo[d] = (unsigned short)cnt;
+    }
+    __syncthreads();
+    auto dword = [&](int d, int w) -> unsigned {  // bit b: positions i = 32w+b and i+d can pair, 1 <= i <= n-d
+      const int sh = d & 31, wo = w + (d >> 5);
+      const unsigned *mA = bm, *mC = bm + mstride, *mG = bm + 2 * mstride, *mU = bm + 3 * mstride;
+      const unsigned sA = __funnelshift_r(mA[wo], mA[wo + 1], sh), sC = __funnelshift_r(mC[wo], mC[wo + 1], sh);
+      const unsigned sG = __funnelshift_r(mG[wo], mG[wo + 1], sh), sU = __funnelshift_r(mU[wo], mU[wo + 1], sh);
+      unsigned m = (mA[w] & sU) | (mC[w] & sG) | (mG[w] & (sC | sU)) | (mU[w] & (sA | sG));
+      const int hi = n - d - 32 * w;  // highest valid bit
+      if (hi < 31) m &= (hi < 0) ? 0u : ((2u << hi) - 1u);
+      if (w == 0) m &= ~1u;
+      return m;
+    };
+    for (int d = kTurn + 1 + tid; d < n; d += NT) {
+      int cnt = 0;
+      for (int w = 0; w <= (n - d) >> 5; ++w) cnt += __popc(dword(d, w));
+      plo[d] = (unsigned short)cnt;
     }
     __syncthreads();
     if (warp == 0) {
@@ -622,14 +645,14 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       if (lane == 0 && n > kTurn + 1) plo[n] = (unsigned short)carry;
     }
     __syncthreads();
-    for (int d = kTurn + 1 + warp; d < n; d += NW) {
+    for (int d = kTurn + 1 + tid; d < n; d += NT) {
       int pos = plo[d];
-      for (int base = 0; base < n - d; base += 32) {
-        const int x = base + lane;
-        const bool pr = x < n - d && PT(S[x + 1], S[x + 1 + d]) != 0;
-        const unsigned m = __ballot_sync(0xffffffffu, pr);
-        if (pr) pl[pos + __popc(m & ((1u << lane) - 1u))] = (unsigned char)x;
-        pos += __popc(m);
+      for (int w = 0; w <= (n - d) >> 5; ++w) {
+        unsigned m = dword(d, w);
+        while (m) {
+          pl[pos++] = (unsigned char)(32 * w + __ffs(m) - 2);  // cell index x = i - 1
+          m &= m - 1;
+        }
       }
     }
     __syncthreads();
