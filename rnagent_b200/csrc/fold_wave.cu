@@ -462,8 +462,18 @@ __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, cons
       const int d = j - i;
       const int type = pair_type(S[i], S[j]);
       const int cij = craw((int)CB[tri(n, d) + i - 1], type);
-      if (cij == e_hairpin(sp, gp, S, i, j, type)) break;
+      // hairpin first (ViennaRNA's order), then the stacked pair -- by far the most frequent step -- as a
+      // lane-uniform check whose lookups are issued together with the hairpin's
       const int si1 = S[i + 1], sj1 = S[j - 1];
+      const int hp = e_hairpin(sp, gp, S, i, j, type);
+      const int t2s = (d >= 6) ? pair_type(si1, sj1) : 0;
+      const int st = craw((int)CB[tri(n, max(d - 2, kTurn + 1)) + i], t2s) + sp.stack[type][rtype_of(t2s)];
+      if (cij == hp) break;
+      if (t2s && cij == st) {
+        ++i;
+        --j;
+        continue;
+      }
       bool found = false;
       const int amax = min(kMaxLoop, d - 6);
       for (int n1 = 0; n1 <= amax && !found; ++n1) {
