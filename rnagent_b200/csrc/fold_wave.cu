@@ -179,7 +179,7 @@ __host__ __device__ constexpr int shape_class(int n1, int n2) {
 __host__ __device__ constexpr int wave_np(int nmax) { return (nmax + 9) & ~1; }  // even row pitch of the scratch rows
 
 struct WaveSmem {
-  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, pl_off, plo_off, gd_off, total;
+  int f5_off, dml_off, bt_off, misc_off, ptab_off, S_off, db_off, part_off, mlp_off, C_off, F_off, wI_off, w1_off, pl_off, plo_off, gd_off, mlf_off, total;
   int rs;        // window row stride (elements)
   int mlparts;   // max multiloop parts per cell
   __host__ __device__ static WaveSmem make(int nmax, int esz) {
@@ -197,7 +197,7 @@ struct WaveSmem {
     L.db_off = take(np);
     L.part_off = take(2 * kWSlots * np * esz);      // [parity][slot][cell]; slot 0 generic, 1 tabulated, 2.. bulge/1xn parts
     L.bt_off = L.part_off;                          // the backtrack stack reuses the scratch rows after the fill
-    L.mlp_off = take(2 * L.mlparts * np * 4);       // [parity][mlpart][cell]
+    L.mlp_off = take(2 * L.mlparts * np * esz);     // [parity][mlpart][cell]
     const int cells = table_cells(nmax) + 64;
     L.C_off = take(cells * esz);
     L.F_off = take((fold_rows(L.rs) * L.rs + 64) * esz);  // folded layout, pitch rs
@@ -207,6 +207,7 @@ struct WaveSmem {
     L.pl_off = take(nmax * nmax / 4 + 64);          // cells whose ends can pair, diagonal by diagonal (uint8 index)
     L.plo_off = take(np * 2);                       // first list entry of each diagonal (+ total at [n])
     L.gd_off = take(kGenSlots * 2);                 // (L, n1) of the generic shape in each lane slot
+    L.mlf_off = take((table_cells(nmax) + 31) / 32 * 4);  // one bit per cell: "closed by a multiloop and by nothing else"
     L.total = o;
     return L;
   }
@@ -350,7 +351,8 @@ __device__ __forceinline__ int div_small(int k, int nb, int qmax) {
 // ---------------------------------------------------------------------------------------------
 template <typename ST, bool FOLDED>
 __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, const ST *CB, const ST *F, int rp, int *bt,
-                              unsigned char *db, const FoldParams *__restrict__ gp, int lane) {
+                              unsigned char *db, const FoldParams *__restrict__ gp, int lane,
+                              const unsigned *mlf = nullptr) {
   const SmallParams &sp = gp->s;
   auto fx = [&](int t, int x) -> int { return FOLDED ? fold_idx(rp, t, x) : tri(n, t) + x; };
   const int tau = cW.TerminalAU;
@@ -475,7 +477,9 @@ __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, cons
         continue;
       }
       bool found = false;
-      const int amax = min(kMaxLoop, d - 6);
+      const int cidx = tri(n, d) + i - 1;
+      const bool ml_only = mlf != nullptr && ((mlf[cidx >> 5] >> (cidx & 31)) & 1u);  // recorded by the fill
+      const int amax = ml_only ? -1 : min(kMaxLoop, d - 6);
       for (int n1 = 0; n1 <= amax && !found; ++n1) {
         const int p = i + 1 + n1;
         const int bmax = min(kMaxLoop - n1, d - 6 - n1);
@@ -546,7 +550,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
   unsigned char *S = smem + Ls.S_off;
   unsigned char *db = smem + Ls.db_off;
   ST *part = reinterpret_cast<ST *>(smem + Ls.part_off);
-  int *mlp = reinterpret_cast<int *>(smem + Ls.mlp_off);
+  ST *mlp = reinterpret_cast<ST *>(smem + Ls.mlp_off);
   ST *CB = reinterpret_cast<ST *>(smem + Ls.C_off);
   ST *F = reinterpret_cast<ST *>(smem + Ls.F_off);
   ST *wI = reinterpret_cast<ST *>(smem + Ls.wI_off);
@@ -554,6 +558,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
   unsigned char *ptab = smem + Ls.ptab_off;
   unsigned char *pl = smem + Ls.pl_off;
   unsigned short *plo = reinterpret_cast<unsigned short *>(smem + Ls.plo_off);
+  unsigned *mlf = reinterpret_cast<unsigned *>(smem + Ls.mlf_off);
   const int np = wave_np(nmax), rs = Ls.rs, mlparts = Ls.mlparts;
   const int tid = threadIdx.x, lane = tid & 31, NW = blockDim.x >> 5, NT = blockDim.x;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
@@ -598,6 +603,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       db[k] = '.';
     }
     for (int k = tid; k <= n; k += NT) f5[k] = 0;
+    for (int k = tid; k < (tri(n, n) + 31) / 32; k += NT) mlf[k] = 0;
     __syncthreads();
     if (tid == 0 && n > 0) {
       S[0] = S[n];
@@ -803,7 +809,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
           const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
           const int best = split_scan<ST>(F, rs, d, xc, t0, t1);
-          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = best;
+          if (x < cells_d) mlp[(par * mlparts + m) * np + x] = put<ST>(best, flag);
         } else if (k < nI + nT + nM + nF) {
           // ---------------- F(b): finalise diagonal d1
           const int blk = k - nI - nT - nM;
@@ -823,8 +829,16 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 #pragma unroll
               for (int r = 0; r < kEParts; ++r)                                             // bulges, 1xn of loop sizes >= epart_beg(r)
                 if (d1 - 6 >= epart_beg(r)) cij = min(cij, (int)src[(2 + r) * np]);
-              if (d1 >= 2 * kTurn + 4)
-                cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
+              if (d1 >= 2 * kTurn + 4) {
+                const int eml = dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing;
+                if (eml < cij) {
+                  // strictly better than the hairpin and every interior loop: the backtrack may skip its
+                  // search for an interior loop here (the long search that would end empty-handed)
+                  cij = eml;
+                  const int cidx = tri(n, d1) + x;
+                  atomicOr(&mlf[cidx >> 5], 1u << (cidx & 31));
+                }
+              }
               const int rt = rtype_of(type);
               CB[tri(n, d1) + x] = put<ST>(cij + (type > 2 ? tau : 0), flag);
               wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
@@ -842,7 +856,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
             if (type) e = min(e, cij + e_mlstem(sp, type, sim1, sjp1));
             int dm = kInf;
             const int mp1 = mlparts_of(d1, n);
-            for (int m = 0; m < mp1; ++m) dm = min(dm, mlp[(par1 * mlparts + m) * np + x]);
+            for (int m = 0; m < mp1; ++m) dm = min(dm, (int)mlp[(par1 * mlparts + m) * np + x]);
+            if (dm >= Store<ST>::kThr) dm = kInf;
             dml[(d1 % 3) * np + x] = dm;
             F[fold_idx(rs, d1, x)] = put<ST>(min(e, dm), flag);
           }
@@ -884,7 +899,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 
     // ---- backtrack (ViennaRNA's deterministic order); warp 0, lanes scan candidates in that order
     if (warp == 0 && !misc[3]) {
-      const int failc = backtrack_warp<ST, true>(n, S, f5, CB, F, rs, bt, db, gp, lane);
+      const int failc = backtrack_warp<ST, true>(n, S, f5, CB, F, rs, bt, db, gp, lane, mlf);
       if (lane == 0 && failc) misc[1] = failc;
     }
     __syncthreads();
