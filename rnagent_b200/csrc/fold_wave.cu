@@ -26,6 +26,7 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <cstring>
 
 #include "energy.cuh"
 #include "fold_kernels.h"
@@ -38,6 +39,9 @@ struct WaveConst {
   int GB[32];      // bulges (0,L) and (L,0): bulge[L]
   int G1[32];      // 1xn loops (1,L-1) and (L-1,1): interior[L] + asymmetry penalty
   int MLbase, MLclosing, MLintern, TerminalAU;
+  // mismatch tables of the fill's finalisation items: constant-cache copies (lane-divergent index, but only a
+  // handful of distinct entries per warp) instead of global loads that miss the small L1 left beside 225 KB of smem
+  int mmH[8][5][5], mmI[8][5][5], mm1nI[8][5][5], mmM[8][5][5], mmExt[8][5][5];
 };
 __constant__ WaveConst cW;
 
@@ -48,8 +52,12 @@ __device__ unsigned long long g_phase_clk[640];
 #endif
 #define PHASE_CLK_BEGIN() long long clk_t0 = (tid == 0) ? clock64() : 0
 #define PHASE_CLK_END(slot) do { if (tid == 0) { const long long t1 = clock64(); atomicAdd(&g_phase_clk[slot], (unsigned long long)(t1 - clk_t0)); clk_t0 = t1; } } while (0)
+#define ITEM_CLK_BEGIN() const long long item_t0 = clock64()
+#define ITEM_CLK_END(kind, late) do { if (lane == 0) { atomicAdd(&g_phase_clk[610 + 8 * (late) + (kind)], (unsigned long long)(clock64() - item_t0)); atomicAdd(&g_phase_clk[626 + 8 * (late) + (kind)], 1ull); } } while (0)
 #else
 #define WAVE_SKIP 0
+#define ITEM_CLK_BEGIN() do { } while (0)
+#define ITEM_CLK_END(kind, late) do { } while (0)
 #define PHASE_CLK_BEGIN() do { } while (0)
 #define PHASE_CLK_END(slot) do { } while (0)
 #endif
@@ -62,6 +70,9 @@ constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are r
 #endif
 #ifndef WAVE_FINE
 #define WAVE_FINE 0
+#endif
+#ifndef WAVE_CMM
+#define WAVE_CMM 0  // 1: the fill reads the mismatch tables from constant memory
 #endif
 #ifndef WAVE_DYN
 #define WAVE_DYN 0  // 1: work items of a phase are claimed dynamically (shared-memory counter) instead of round-robin
@@ -560,7 +571,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
   unsigned short *plo = reinterpret_cast<unsigned short *>(smem + Ls.plo_off);
   unsigned *mlf = reinterpret_cast<unsigned *>(smem + Ls.mlf_off);
   const int np = wave_np(nmax), rs = Ls.rs, mlparts = Ls.mlparts;
-  const int tid = threadIdx.x, lane = tid & 31, NW = blockDim.x >> 5, NT = blockDim.x;
+  const int tid = threadIdx.x, lane = tid & 31;
+  constexpr int NW = MAXT / 32, NT = MAXT;  // the kernel is always launched with MAXT threads
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
   const SmallParams &sp = gp->s;
   constexpr int kInfS = Store<ST>::kInfS;
@@ -579,6 +591,15 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
   __syncthreads();
   auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
   auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
+#if WAVE_CMM
+  auto MMI = [&](int t, int a, int b) -> int { return cW.mmI[t][a][b]; };
+  auto MM1 = [&](int t, int a, int b) -> int { return cW.mm1nI[t][a][b]; };
+  auto MLSTEM = [&](int t, int s5, int s3) -> int { return cW.mmM[t][s5][s3] + (t > 2 ? tau : 0) + cW.MLintern; };
+#else
+  auto MMI = [&](int t, int a, int b) -> int { return __ldg(&sp.mmI[t][a][b]); };
+  auto MM1 = [&](int t, int a, int b) -> int { return __ldg(&sp.mm1nI[t][a][b]); };
+  auto MLSTEM = [&](int t, int s5, int s3) -> int { return e_mlstem(sp, t, s5, s3); };
+#endif
 
   for (;;) {
     __syncthreads();
@@ -708,6 +729,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       // ---------------- G(cell): generic interior shapes, lanes across shapes, one pairable cell at a time
       const int nvalid = (d < n && !(WAVE_SKIP & 1)) ? gen_valid(d) : 0;
 #if !WAVE_DYN
+      ITEM_CLK_BEGIN();
       if (nvalid == kGenSlots) {
 #pragma unroll 1
         for (int c = warp; c < npair; c += NW) {
@@ -725,6 +747,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
         }
       }
+      ITEM_CLK_END(5, d >= 68 ? 1 : 0);
 #endif
       // the block items start with the warp after the last one that took a cell, to even out the phase
       const int nG = nvalid > 0 ? npair : 0;
@@ -756,6 +779,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       if (k0 < 0) k0 += NW;
       for (int k = k0; k < total; k += NW) {
 #endif
+        ITEM_CLK_BEGIN();
+        const int item_kind = k < nI ? 0 : k < nI + nT ? 1 : k < nI + nT + nM ? 2 : k < nI + nT + nM + nF ? 3 : 4;
         if (k < nI) {
           // ---------------- E(b,r): bulges and 1xn loops of the loop sizes in part r, lanes across pairable cells
           const int r = div_small(k, nbI, kEParts), blk = k - r * nbI;
@@ -768,7 +793,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           if (idx < npair) {
             const int i = x + 1, j = i + d;
             const int type = PT(S[i], S[j]);
-            const int e = min(a1 + __ldg(&sp.mm1nI[type][S[i + 1]][S[j - 1]]), aB + (type > 2 ? tau : 0));
+            const int e = min(a1 + MM1(type, S[i + 1], S[j - 1]), aB + (type > 2 ? tau : 0));
             part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
           }
         } else if (k < nI + nT) {
@@ -822,15 +847,20 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
             const int wrow1 = (d1 & (kWin - 1)) * rs + x;
             const int wrow = kFullW ? tri(n, d1) + x : wrow1;
             if (type) {
+#if WAVE_CMM
+              if (d1 == 4 || d1 == 5 || d1 == 7) cij = e_hairpin(sp, gp, S, i, j, type);  // sizes with special loops
+              else cij = ((d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1])) + cW.mmH[type][si1][sj1];
+#else
               cij = e_hairpin(sp, gp, S, i, j, type);
+#endif
               const ST *src = part + (par1 * kWSlots) * np + x;
-              if (d1 >= 12) cij = min(cij, (int)src[0] + __ldg(&sp.mmI[type][si1][sj1]));  // generic shapes (L >= 6)
+              if (d1 >= 12) cij = min(cij, (int)src[0] + MMI(type, si1, sj1));  // generic shapes (L >= 6)
               if (d1 >= 6) cij = min(cij, (int)src[np]);                                    // tabulated shapes
 #pragma unroll
               for (int r = 0; r < kEParts; ++r)                                             // bulges, 1xn of loop sizes >= epart_beg(r)
                 if (d1 - 6 >= epart_beg(r)) cij = min(cij, (int)src[(2 + r) * np]);
               if (d1 >= 2 * kTurn + 4) {
-                const int eml = dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing;
+                const int eml = dml[((d1 - 2) % 3) * np + x + 1] + MLSTEM(rtype_of(type), sj1, si1) + cW.MLclosing;
                 if (eml < cij) {
                   // strictly better than the hairpin and every interior loop: the backtrack may skip its
                   // search for an interior loop here (the long search that would end empty-handed)
@@ -841,8 +871,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
               }
               const int rt = rtype_of(type);
               CB[tri(n, d1) + x] = put<ST>(cij + (type > 2 ? tau : 0), flag);
-              wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
-              w1[wrow1] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
+              wI[wrow] = put<ST>(cij + MMI(rt, sjp1, sim1), flag);
+              w1[wrow1] = put<ST>(cij + MM1(rt, sjp1, sim1), flag);
             } else {
               CB[tri(n, d1) + x] = (ST)kInfS;
               wI[wrow] = (ST)kInfS;
@@ -853,7 +883,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
               const int pb = fold_idx(rs, d1 - 1, x);
               e = min((int)F[pb + 1], (int)F[pb]) + cW.MLbase;
             }
-            if (type) e = min(e, cij + e_mlstem(sp, type, sim1, sjp1));
+            if (type) e = min(e, cij + MLSTEM(type, sim1, sjp1));
             int dm = kInf;
             const int mp1 = mlparts_of(d1, n);
             for (int m = 0; m < mp1; ++m) dm = min(dm, (int)mlp[(par1 * mlparts + m) * np + x]);
@@ -875,6 +905,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
           if (lane == 0) f5[j] = min(f5[j - 1], best);
         }
+        ITEM_CLK_END(item_kind, d >= 68 ? 1 : 0);
       }
       // next diagonal: every slot moves one row down its table (row d-2-L has n-d+2+L cells)
       {
@@ -974,6 +1005,11 @@ cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
       for (int n1 = 0; n1 < 32; ++n1)
         w.GI[L][n1] = (n1 <= L && shape_class(n1, L - n1) == kGen) ? s.interior[L] + asym(L - 2 * n1) : kBig;
   }
+  memcpy(w.mmH, s.mmH, sizeof(w.mmH));
+  memcpy(w.mmI, s.mmI, sizeof(w.mmI));
+  memcpy(w.mm1nI, s.mm1nI, sizeof(w.mm1nI));
+  memcpy(w.mmM, s.mmM, sizeof(w.mmM));
+  memcpy(w.mmExt, s.mmExt, sizeof(w.mmExt));
   w.MLbase = s.MLbase;
   w.MLclosing = s.MLclosing;
   w.MLintern = s.MLintern;

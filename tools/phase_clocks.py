@@ -30,3 +30,8 @@ print(f"cycles per fold (CTA wall): {tot:.0f}; prologue {v[600]:.0f} backtrack {
 for d0 in range(4, n + 2, 8):
     seg = v[d0:d0 + 8]
     print(f"d {d0:3d}..{d0 + 7:3d}: " + " ".join(f"{x:6.0f}" for x in seg) + f"   sum {seg.sum():7.0f} ({100 * seg.sum() / tot:4.1f}%)")
+raw = np.array(list(out), dtype=np.float64)
+names = ["E", "T", "M", "F", "X", "G-loop"]
+for late in (0, 1):
+    print("items, d %s 68: " % (">=" if late else "<") + "  ".join(
+        f"{nm} {raw[610 + 8 * late + k] / max(raw[626 + 8 * late + k], 1):6.0f}cyc x{raw[626 + 8 * late + k] / count:5.1f}" for k, nm in enumerate(names)))
