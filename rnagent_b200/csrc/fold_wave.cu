@@ -837,57 +837,63 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           if (x < cells_d) mlp[(par * mlparts + m) * np + x] = put<ST>(best, flag);
         } else if (k < nI + nT + nM + nF) {
           // ---------------- F(b): finalise diagonal d1
+          // Every table lookup is issued up front and unconditionally (safe indices; unpairable cells and
+          // lanes beyond the diagonal are masked afterwards): the parameter loads of a cell are independent of
+          // each other, but behind branches they would be fetched one L2 round trip after the other.
           const int blk = k - nI - nT - nM;
           const int x = blk * 32 + lane;
-          if (x < cells_1) {
-            const int i = x + 1, j = i + d1;
-            const int type = PT(S[i], S[j]);
-            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
-            int cij = kInf;
+          const bool live = x < cells_1;
+          const int xs = live ? x : 0;
+          const int i = xs + 1, j = i + d1;
+          const int type = PT(S[i], S[j]);
+          const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+          const int rt = rtype_of(type);
+          const int v_mmh = __ldg(&sp.mmH[type][si1][sj1]);
+          const int v_mmio = MMI(type, si1, sj1);
+          const int v_mlc = MLSTEM(rt, sj1, si1);
+          const int v_mmii = MMI(rt, sjp1, sim1);
+          const int v_mm1i = MM1(rt, sjp1, sim1);
+          const int v_mls = MLSTEM(type, sim1, sjp1);
+          const int hbase = (d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1]);  // warp-uniform
+          const ST *src = part + (par1 * kWSlots) * np + xs;
+          const int s_g = (int)src[0], s_t = (int)src[np];
+          int s_e = kInfS;
+#pragma unroll
+          for (int r = 0; r < kEParts; ++r) s_e = (d1 - 6 >= epart_beg(r)) ? min(s_e, (int)src[(2 + r) * np]) : s_e;
+          const int v_dml = dml[((d1 - 2) % 3) * np + xs + 1];
+          const int pb = fold_idx(rs, max(d1 - 1, kTurn + 1), xs);
+          const int f_a = (int)F[pb + 1], f_b = (int)F[pb];
+          int dm = kInf;
+          const int mp1 = mlparts_of(d1, n);
+          for (int m = 0; m < mp1; ++m) dm = min(dm, (int)mlp[(par1 * mlparts + m) * np + xs]);
+          if (dm >= Store<ST>::kThr) dm = kInf;
+
+          int cij = hbase + v_mmh;
+          if (d1 == 4 || d1 == 5 || d1 == 7) cij = type ? e_hairpin(sp, gp, S, i, j, type) : cij;  // sizes with special loops
+          cij = (d1 >= 12) ? min(cij, s_g + v_mmio) : cij;  // generic shapes (L >= 6)
+          cij = (d1 >= 6) ? min(cij, s_t) : cij;            // tabulated shapes
+          cij = (d1 >= 8) ? min(cij, s_e) : cij;            // bulges, 1xn
+          const int eml = v_dml + v_mlc + cW.MLclosing;
+          // strictly better than the hairpin and every interior loop: the backtrack may skip its search for an
+          // interior loop at this cell (the long search that would end empty-handed)
+          const bool ml_only = d1 >= 2 * kTurn + 4 && eml < cij;
+          cij = ml_only ? eml : cij;
+          int e = (d1 > kTurn + 1) ? min(f_a, f_b) + cW.MLbase : kInf;
+          e = type ? min(e, cij + v_mls) : e;
+          if (live) {
             const int wrow1 = (d1 & (kWin - 1)) * rs + x;
             const int wrow = kFullW ? tri(n, d1) + x : wrow1;
+            const int cidx = tri(n, d1) + x;
             if (type) {
-#if WAVE_CMM
-              if (d1 == 4 || d1 == 5 || d1 == 7) cij = e_hairpin(sp, gp, S, i, j, type);  // sizes with special loops
-              else cij = ((d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1])) + cW.mmH[type][si1][sj1];
-#else
-              cij = e_hairpin(sp, gp, S, i, j, type);
-#endif
-              const ST *src = part + (par1 * kWSlots) * np + x;
-              if (d1 >= 12) cij = min(cij, (int)src[0] + MMI(type, si1, sj1));  // generic shapes (L >= 6)
-              if (d1 >= 6) cij = min(cij, (int)src[np]);                                    // tabulated shapes
-#pragma unroll
-              for (int r = 0; r < kEParts; ++r)                                             // bulges, 1xn of loop sizes >= epart_beg(r)
-                if (d1 - 6 >= epart_beg(r)) cij = min(cij, (int)src[(2 + r) * np]);
-              if (d1 >= 2 * kTurn + 4) {
-                const int eml = dml[((d1 - 2) % 3) * np + x + 1] + MLSTEM(rtype_of(type), sj1, si1) + cW.MLclosing;
-                if (eml < cij) {
-                  // strictly better than the hairpin and every interior loop: the backtrack may skip its
-                  // search for an interior loop here (the long search that would end empty-handed)
-                  cij = eml;
-                  const int cidx = tri(n, d1) + x;
-                  atomicOr(&mlf[cidx >> 5], 1u << (cidx & 31));
-                }
-              }
-              const int rt = rtype_of(type);
-              CB[tri(n, d1) + x] = put<ST>(cij + (type > 2 ? tau : 0), flag);
-              wI[wrow] = put<ST>(cij + MMI(rt, sjp1, sim1), flag);
-              w1[wrow1] = put<ST>(cij + MM1(rt, sjp1, sim1), flag);
+              if (ml_only) atomicOr(&mlf[cidx >> 5], 1u << (cidx & 31));
+              CB[cidx] = put<ST>(cij + (type > 2 ? tau : 0), flag);
+              wI[wrow] = put<ST>(cij + v_mmii, flag);
+              w1[wrow1] = put<ST>(cij + v_mm1i, flag);
             } else {
-              CB[tri(n, d1) + x] = (ST)kInfS;
+              CB[cidx] = (ST)kInfS;
               wI[wrow] = (ST)kInfS;
               w1[wrow1] = (ST)kInfS;
             }
-            int e = kInf;
-            if (d1 > kTurn + 1) {
-              const int pb = fold_idx(rs, d1 - 1, x);
-              e = min((int)F[pb + 1], (int)F[pb]) + cW.MLbase;
-            }
-            if (type) e = min(e, cij + MLSTEM(type, sim1, sjp1));
-            int dm = kInf;
-            const int mp1 = mlparts_of(d1, n);
-            for (int m = 0; m < mp1; ++m) dm = min(dm, (int)mlp[(par1 * mlparts + m) * np + x]);
-            if (dm >= Store<ST>::kThr) dm = kInf;
             dml[(d1 % 3) * np + x] = dm;
             F[fold_idx(rs, d1, x)] = put<ST>(min(e, dm), flag);
           }
