@@ -56,7 +56,7 @@ struct ClusterSmem {
 };
 
 template <typename ST>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads, 1)
 fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *__restrict__ queue,
                     ST *__restrict__ CBg, ST *__restrict__ Fg, long long gstride) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -140,14 +140,16 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
             const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
             const int idx = blk * 32 + lane;
             const int x = pld[min(idx, npair - 1)];
+            // the outer pair's terms are fetched before the scan, not after it (their latency hides behind it)
+            const int oi = x + 1, oj = oi + d;
+            const int type = PT(S[oi], S[oj]);
+            const int v_mmi = __ldg(&sp.mmI[type][S[oi + 1]][S[oj - 1]]);
+            const int v_mm1 = __ldg(&sp.mm1nI[type][S[oi + 1]][S[oj - 1]]);
             int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
             interior_item<ST, false, true>(wI + x + 1, w1 + x + 1, wB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
             if (idx < npair) {
-              const int i = x + 1, j = i + d;
-              const int type = PT(S[i], S[j]);
-              const int si1 = S[i + 1], sj1 = S[j - 1];
-              int e = min(min(aI[0], aI[1]), min(aI[2], aI[3])) + __ldg(&sp.mmI[type][si1][sj1]);
-              e = min(e, a1 + __ldg(&sp.mm1nI[type][si1][sj1]));
+              int e = min(min(aI[0], aI[1]), min(aI[2], aI[3])) + v_mmi;
+              e = min(e, a1 + v_mm1);
               e = min(e, aB + (type > 2 ? tau : 0));
               part[(par * kSlots + r) * np + x] = (ST)min(e, kInfS);
             }
@@ -166,43 +168,53 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
                 sj[u] = S[j - u];
               }
 #pragma unroll
-              for (int s = 0; s < 9; ++s) {
+              for (int s = 0; s < 9; ++s) {  // branch-free: the nine lookup chains overlap (see fold_wave_kernel)
                 constexpr int kN1[9] = {0, 0, 1, 1, 1, 2, 2, 2, 3};
                 constexpr int kN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
                 const int n1 = kN1[s], n2 = kN2[s];
-                if (n1 + n2 <= d - 6) {
-                  const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
-                  if (t2) {
-                    const int cpq = craw((int)wB[((d - 2 - n1 - n2) & (kWin - 1)) * rs + x + 1 + n1], t2);
-                    best = min(best, cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]));
-                  }
-                }
+                const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
+                const int cpq = craw((int)wB[((d - 2 - n1 - n2) & (kWin - 1)) * rs + x + 1 + n1], t2);
+                const int e = cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]);
+                best = (n1 + n2 <= d - 6 && t2 != 0) ? min(best, e) : best;
               }
               part[(par * kSlots + kParts) * np + x] = (ST)min(best, kInfS);
             }
           } else if (k < nI + nT + nF) {
             // ---- Fp(b): finalise c of diagonal d1, push c + E_MLstem to the multiloop CTA
+            // all lookups up front and unconditional, masked afterwards (see fold_wave_kernel's F item)
             const int x = (k - nI - nT) * 32 + lane;
-            if (x < cells_1) {
-              const int i = x + 1, j = i + d1;
-              const int type = PT(S[i], S[j]);
-              const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+            const bool live = x < cells_1;
+            const int xs = live ? x : 0;
+            const int i = xs + 1, j = i + d1;
+            const int type = PT(S[i], S[j]);
+            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+            const int rt = rtype_of(type);
+            const int v_mmh = __ldg(&sp.mmH[type][si1][sj1]);
+            const int v_mlc = e_mlstem(sp, rt, sj1, si1);
+            const int v_mmii = __ldg(&sp.mmI[rt][sjp1][sim1]);
+            const int v_mm1i = __ldg(&sp.mm1nI[rt][sjp1][sim1]);
+            const int v_mls = e_mlstem(sp, type, sim1, sjp1);
+            const int hbase = (d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1]);
+            const ST *src = part + (par1 * kSlots) * np + xs;
+            int sp_min = kInfS;
+#pragma unroll
+            for (int r = 0; r < kParts; ++r) sp_min = (part_beg(r) <= d1 - 6) ? min(sp_min, (int)src[r * np]) : sp_min;
+            const int s_t = (int)src[kParts * np];
+            const int v_dml = dml[((d1 - 2) % 3) * np + xs + 1];
+            int cij = hbase + v_mmh;
+            if (d1 == 4 || d1 == 5 || d1 == 7) cij = type ? e_hairpin(sp, gp, S, i, j, type) : cij;
+            cij = (d1 >= 8) ? min(cij, sp_min) : cij;
+            cij = (d1 >= 6) ? min(cij, s_t) : cij;
+            cij = (d1 >= 2 * kTurn + 4) ? min(cij, v_dml + v_mlc + cW.MLclosing) : cij;
+            if (live) {
               const int wrow = (d1 & (kWin - 1)) * rs + x;
               int stem = kInf;
               ST cb = (ST)kInfS;
               if (type) {
-                int cij = e_hairpin(sp, gp, S, i, j, type);
-                const int np1 = nparts_of(d1, n);
-                const ST *src = part + (par1 * kSlots) * np + x;
-                for (int r = 0; r < np1; ++r) cij = min(cij, (int)src[r * np]);
-                if (d1 >= 6) cij = min(cij, (int)src[kParts * np]);
-                if (d1 >= 2 * kTurn + 4)
-                  cij = min(cij, dml[((d1 - 2) % 3) * np + x + 1] + e_mlstem(sp, rtype_of(type), sj1, si1) + cW.MLclosing);
-                const int rt = rtype_of(type);
                 cb = put<ST>(cij + (type > 2 ? tau : 0), flag);
-                wI[wrow] = put<ST>(cij + __ldg(&sp.mmI[rt][sjp1][sim1]), flag);
-                w1[wrow] = put<ST>(cij + __ldg(&sp.mm1nI[rt][sjp1][sim1]), flag);
-                stem = cij + e_mlstem(sp, type, sim1, sjp1);
+                wI[wrow] = put<ST>(cij + v_mmii, flag);
+                w1[wrow] = put<ST>(cij + v_mm1i, flag);
+                stem = cij + v_mls;
               } else {
                 wI[wrow] = (ST)kInfS;
                 w1[wrow] = (ST)kInfS;

@@ -788,12 +788,14 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           const int l1 = min((r == 0 ? epart_beg(1) : r == 1 ? epart_beg(2) : epart_beg(3)) - 1, lmax);
           const int idx = blk * 32 + lane;
           const int x = pl[pl0 + min(idx, npair - 1)];
+          // the outer pair's term is fetched before the scan, not after it (its latency hides behind the scan)
+          const int oi = x + 1, oj = oi + d;
+          const int type = PT(S[oi], S[oj]);
+          const int v_mm1 = MM1(type, S[oi + 1], S[oj - 1]);
           int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
           interior_item<ST, kFullW, false, false>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
           if (idx < npair) {
-            const int i = x + 1, j = i + d;
-            const int type = PT(S[i], S[j]);
-            const int e = min(a1 + MM1(type, S[i + 1], S[j - 1]), aB + (type > 2 ? tau : 0));
+            const int e = min(a1 + v_mm1, aB + (type > 2 ? tau : 0));
             part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
           }
         } else if (k < nI + nT) {
