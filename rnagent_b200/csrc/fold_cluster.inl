@@ -23,7 +23,7 @@ struct ClusterSmem {
   // common
   int misc_off, ptab_off, S_off;
   // rank 0
-  int wB_off, wI_off, w1_off, part_off, dml_off, pl_off, plc_off;
+  int wB_off, wI_off, w1_off, part_off, dml_off, pl_off, plc_off, gd_off;
   // rank 1 (overlays rank 0's region)
   int F_off, mlp_off, cst_off;
   int total, rs, mlparts, np;
@@ -41,10 +41,11 @@ struct ClusterSmem {
     L.wB_off = take((kWin * L.rs + 64) * esz);
     L.wI_off = take((kWin * L.rs + 64) * esz);
     L.w1_off = take((kWin * L.rs + 64) * esz);
-    L.part_off = take(2 * kSlots * L.np * esz);
+    L.part_off = take(2 * kWSlots * L.np * esz);  // slot 0 generic shapes, 1 tabulated, 2.. bulge/1xn parts
     L.dml_off = take(3 * L.np * 4);
     L.pl_off = take(2 * L.np * 2);
     L.plc_off = take(16);
+    L.gd_off = take(kGenSlots * 2);
     const int end0 = o;
     o = base;
     L.F_off = take((fold_rows(L.rs) * L.rs + 64) * esz);  // folded layout, pitch rs
@@ -90,6 +91,15 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
   if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
   auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
   auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
+  // lane slots of the shape-parallel generic interior item (see fold_wave_kernel): slot -> L | n1 << 8
+  unsigned short *gdesc = reinterpret_cast<unsigned short *>(smem + Ls.gd_off);
+  if (rank == 0)
+    for (int sidx = tid; sidx < kGenSlots; sidx += NT) {
+      const int sc = min(sidx, kGenShapes - 1);
+      int L = 6;
+      while (gen_before(L + 1) <= sc) ++L;
+      gdesc[sidx] = (unsigned short)(L | ((2 + sc - gen_before(L)) << 8));
+    }
 
   for (;;) {
     cluster.sync();
@@ -109,6 +119,8 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
     int flag = 0;
 
     for (int k = tid; k < n; k += NT) S[k + 1] = (unsigned char)enc_base(a.seq[beg + k]);
+    if (rank == 1)
+      for (int k = tid; k < 3 * mlparts * np; k += NT) mlp[k] = kInf;
     __syncthreads();
     if (tid == 0 && n > 0) {
       S[0] = S[n];
@@ -116,14 +128,33 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
     }
     cluster.sync();
 
+    // pair CTA: window offsets of the generic-shape slots at d = 4 (one row down per diagonal, wrapping)
+    int gterm[kGenIters], goff[kGenIters];
+    unsigned gpack[kGenIters / 4] = {};
+    if (rank == 0) {
+#pragma unroll
+      for (int k = 0; k < kGenIters; ++k) {
+        const int ds = gdesc[32 * k + lane];
+        const int L = ds & 255, n1 = ds >> 8;
+        gterm[k] = (32 * k + lane < kGenShapes) ? cW.GI[L][n1] : kBig;
+        goff[k] = (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);
+        gpack[k >> 2] |= (unsigned)((1 + n1) * (int)sizeof(ST)) << (8 * (k & 3));
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < kGenIters; ++k) gterm[k] = goff[k] = 0;
+    }
+
     for (int d = kTurn + 1; d <= n + 1; ++d) {
+#ifdef WAVE_PHASE_CLK
+      const long long clk_p0 = clock64();
+#endif
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
       const int nb_d = (cells_d + 31) >> 5;
       const int lmax = min(kMaxLoop, d - 6);
       if (rank == 0) {
         // ================= pair CTA
-        const int npd = nparts_of(d, n);
         const int d1 = d - 1;
         const int cells_1 = (d1 >= kTurn + 1 && d1 < n) ? n - d1 : 0;
         const int nb_1 = (cells_1 + 31) >> 5;
@@ -131,27 +162,27 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         const unsigned short *pld = pl + par * np;
         const int nbI = (npair + 31) >> 5;
         const int nP = (d + 1 < n && d + 1 >= 6) ? 1 : 0;
-        const int nI = nbI * npd, nT = (lmax >= 0) ? nbI : 0, nF = nb_1;
+        int neparts = 0;
+#pragma unroll
+        for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
+        const int nI = nbI * neparts, nT = (lmax >= 0) ? nbI : 0, nF = nb_1;
         const int total = nI + nT + nF + nP;
         for (int k = warp; k < total; k += NW) {
           if (k < nI) {
-            // ---- I(b,r)
-            const int r = div_small(k, nbI, kParts), blk = k - r * nbI;
-            const int l0 = part_beg_rt(r), l1 = min(part_beg_rt(r + 1) - 1, lmax);
+            // ---- E(b,r): bulges and 1xn loops of the loop sizes in part r, lanes across pairable cells
+            const int r = div_small(k, nbI, kEParts), blk = k - r * nbI;
+            const int l0 = r == 0 ? epart_beg(0) : r == 1 ? epart_beg(1) : epart_beg(2);
+            const int l1 = min((r == 0 ? epart_beg(1) : r == 1 ? epart_beg(2) : epart_beg(3)) - 1, lmax);
             const int idx = blk * 32 + lane;
             const int x = pld[min(idx, npair - 1)];
-            // the outer pair's terms are fetched before the scan, not after it (their latency hides behind it)
             const int oi = x + 1, oj = oi + d;
             const int type = PT(S[oi], S[oj]);
-            const int v_mmi = __ldg(&sp.mmI[type][S[oi + 1]][S[oj - 1]]);
             const int v_mm1 = __ldg(&sp.mm1nI[type][S[oi + 1]][S[oj - 1]]);
             int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
-            interior_item<ST, false, true>(wI + x + 1, w1 + x + 1, wB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
+            interior_item<ST, false, true, false>(wI + x + 1, w1 + x + 1, wB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
             if (idx < npair) {
-              int e = min(min(aI[0], aI[1]), min(aI[2], aI[3])) + v_mmi;
-              e = min(e, a1 + v_mm1);
-              e = min(e, aB + (type > 2 ? tau : 0));
-              part[(par * kSlots + r) * np + x] = (ST)min(e, kInfS);
+              const int e = min(a1 + v_mm1, aB + (type > 2 ? tau : 0));
+              part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
             }
           } else if (k < nI + nT) {
             // ---- T(b): tabulated shapes, inner pairs from the cB window
@@ -177,7 +208,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
                 const int e = cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]);
                 best = (n1 + n2 <= d - 6 && t2 != 0) ? min(best, e) : best;
               }
-              part[(par * kSlots + kParts) * np + x] = (ST)min(best, kInfS);
+              part[(par * kWSlots + 1) * np + x] = (ST)min(best, kInfS);
             }
           } else if (k < nI + nT + nF) {
             // ---- Fp(b): finalise c of diagonal d1, push c + E_MLstem to the multiloop CTA
@@ -195,16 +226,18 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
             const int v_mm1i = __ldg(&sp.mm1nI[rt][sjp1][sim1]);
             const int v_mls = e_mlstem(sp, type, sim1, sjp1);
             const int hbase = (d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1]);
-            const ST *src = part + (par1 * kSlots) * np + xs;
-            int sp_min = kInfS;
+            const int v_mmio = __ldg(&sp.mmI[type][si1][sj1]);
+            const ST *src = part + (par1 * kWSlots) * np + xs;
+            const int s_g = (int)src[0], s_t = (int)src[np];
+            int s_e = kInfS;
 #pragma unroll
-            for (int r = 0; r < kParts; ++r) sp_min = (part_beg(r) <= d1 - 6) ? min(sp_min, (int)src[r * np]) : sp_min;
-            const int s_t = (int)src[kParts * np];
+            for (int r = 0; r < kEParts; ++r) s_e = (d1 - 6 >= epart_beg(r)) ? min(s_e, (int)src[(2 + r) * np]) : s_e;
             const int v_dml = dml[((d1 - 2) % 3) * np + xs + 1];
             int cij = hbase + v_mmh;
             if (d1 == 4 || d1 == 5 || d1 == 7) cij = type ? e_hairpin(sp, gp, S, i, j, type) : cij;
-            cij = (d1 >= 8) ? min(cij, sp_min) : cij;
+            cij = (d1 >= 12) ? min(cij, s_g + v_mmio) : cij;
             cij = (d1 >= 6) ? min(cij, s_t) : cij;
+            cij = (d1 >= 8) ? min(cij, s_e) : cij;
             cij = (d1 >= 2 * kTurn + 4) ? min(cij, v_dml + v_mlc + cW.MLclosing) : cij;
             if (live) {
               const int wrow = (d1 & (kWin - 1)) * rs + x;
@@ -238,22 +271,56 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
             if (lane == 0) plc[par1] = pos;
           }
         }
+        // ---- G(cell): generic interior shapes, lanes across shapes, one pairable cell at a time
+        const int nvalid = (d < n) ? gen_valid(d) : 0;
+        int cg0 = warp - (total % NW);
+        if (cg0 < 0) cg0 += NW;
+        if (nvalid == kGenSlots) {
+#pragma unroll 1
+          for (int c = cg0; c < npair; c += NW) {
+            const int xv = pld[c];
+            const int r = gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xv * (int)sizeof(ST), goff, gterm, nvalid, lane);
+            if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
+          }
+        } else if (nvalid > 0) {
+#pragma unroll 1
+          for (int c = cg0; c < npair; c += NW) {
+            const int xv = pld[c];
+            const int r = gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xv * (int)sizeof(ST), goff, gterm, nvalid, lane);
+            if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kGenIters; ++k) {
+          const int bb = (int)((gpack[k >> 2] >> (8 * (k & 3))) & 0xffu);
+          const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
+          goff[k] = (u >= bb) ? u : t;
+        }
       } else {
         // ================= multiloop CTA
-        const int mpd = mlparts_of(d, n);
+        // split range t = 4 .. d-5 cut into enough chunks that every warp of this CTA gets work even on the
+        // late diagonals (few cells, many split points); chunk minima are merged with shared-memory atomicMin
+        const int nsplit = d - 2 * kTurn - 2;
+        int nch = 0, chunk = 8;
+        if (d < n && nsplit > 0) {
+          const int want = (2 * NW + nb_d - 1) / nb_d;
+          nch = max(1, min(want, (nsplit + 15) >> 4));
+          chunk = ((nsplit + nch - 1) / nch + 7) & ~7;
+          nch = (nsplit + chunk - 1) / chunk;
+        }
         const int d2 = d - 2;
         const int cells_2 = (d2 >= kTurn + 1 && d2 < n) ? n - d2 : 0;
         const int nb_2 = (cells_2 + 31) >> 5;
-        const int nM = nb_d * mpd;
+        const int nM = nb_d * nch;
         const int total = nM + nb_2;
         for (int k = warp; k < total; k += NW) {
           if (k < nM) {
             // ---- M(b,m)
-            const int m = (mpd == 1) ? 0 : div_small(k, nb_d, kMaxMlParts), blk = k - m * nb_d;
+            const int m = k / nb_d, blk = k - m * nb_d;
             const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
-            const int t0 = kTurn + 1 + m * kMlChunk, t1 = min(d - kTurn - 1, t0 + kMlChunk);
+            const int t0 = kTurn + 1 + m * chunk, t1 = min(d - kTurn - 1, t0 + chunk);
             const int best = split_scan<ST>(F, rs, d, xc, t0, t1);
-            if (x < cells_d) mlp[((d % 3) * mlparts + m) * np + x] = best;
+            if (x < cells_d) atomicMin(&mlp[(d % 3) * mlparts * np + x], best);
           } else {
             // ---- Fm(b): finalise fML of diagonal d2, push DML to the pair CTA
             const int x = (k - nM) * 32 + lane;
@@ -264,9 +331,8 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
                 e = min((int)F[pb + 1], (int)F[pb]) + cW.MLbase;
               }
               e = min(e, cst[(d2 & 1) * np + x]);
-              int dm = kInf;
-              const int mp2 = mlparts_of(d2, n);
-              for (int m = 0; m < mp2; ++m) dm = min(dm, mlp[((d2 % 3) * mlparts + m) * np + x]);
+              const int dm = mlp[(d2 % 3) * mlparts * np + x];
+              mlp[(d2 % 3) * mlparts * np + x] = kInf;  // ready for diagonal d2 + 3
               peer_dml[(d2 % 3) * np + x] = dm;
               const ST f = put<ST>(min(e, dm), flag);
               F[fold_idx(rs, d2, x)] = f;
@@ -275,7 +341,14 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
           }
         }
       }
+#ifdef WAVE_PHASE_CLK
+      __syncthreads();
+      if (tid == 0) atomicAdd(&g_phase_clk[(rank ? 64 : 0) + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
+#endif
       cluster.sync();
+#ifdef WAVE_PHASE_CLK
+      if (tid == 0 && rank == 0) atomicAdd(&g_phase_clk[128 + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
+#endif
     }
     if (Store<ST>::kChecked && flag && a.redo) a.redo[b] = 1;
   }
