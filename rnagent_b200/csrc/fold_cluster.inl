@@ -276,8 +276,19 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         int cg0 = warp - (total % NW);
         if (cg0 < 0) cg0 += NW;
         if (nvalid == kGenSlots) {
+          int c = cg0;
 #pragma unroll 1
-          for (int c = cg0; c < npair; c += NW) {
+          for (; c + NW < npair; c += 2 * NW) {
+            const int xv0 = pld[c], xv1 = pld[c + NW];
+            int r0, r1;
+            gen_cell2<ST>(reinterpret_cast<const unsigned char *>(wI), xv0 * (int)sizeof(ST), xv1 * (int)sizeof(ST), goff, gterm, r0, r1);
+            if (lane == 0) {
+              part[(par * kWSlots + 0) * np + xv0] = (ST)min(r0, kInfS);
+              part[(par * kWSlots + 0) * np + xv1] = (ST)min(r1, kInfS);
+            }
+          }
+#pragma unroll 1
+          for (; c < npair; c += NW) {
             const int xv = pld[c];
             const int r = gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xv * (int)sizeof(ST), goff, gterm, nvalid, lane);
             if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
@@ -303,7 +314,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         const int nsplit = d - 2 * kTurn - 2;
         int nch = 0, chunk = 8;
         if (d < n && nsplit > 0) {
-          const int want = (2 * NW + nb_d - 1) / nb_d;
+          const int want = (WAVE_MLWANT * NW + nb_d - 1) / nb_d;
           nch = max(1, min(want, (nsplit + 15) >> 4));
           chunk = ((nsplit + nch - 1) / nch + 7) & ~7;
           nch = (nsplit + chunk - 1) / chunk;

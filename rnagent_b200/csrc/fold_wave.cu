@@ -74,6 +74,9 @@ constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are r
 #ifndef WAVE_CMM
 #define WAVE_CMM 0  // 1: the fill reads the mismatch tables from constant memory
 #endif
+#ifndef WAVE_MLWANT
+#define WAVE_MLWANT 1  // cluster kernel: multiloop work items per warp the split chunks aim for
+#endif
 #ifndef WAVE_DYN
 #define WAVE_DYN 0  // 1: work items of a phase are claimed dynamically (shared-memory counter) instead of round-robin
 #endif
@@ -325,6 +328,28 @@ __device__ __forceinline__ int gen_cell(const unsigned char *__restrict__ tab, i
     }
   }
   return __reduce_min_sync(0xffffffffu, min(min(a0, a1), min(a2, a3)));
+}
+
+// two cells at once (kernels with registers to spare): twice the loads in flight per warp
+template <typename ST>
+__device__ __forceinline__ void gen_cell2(const unsigned char *__restrict__ tab, int xb0, int xb1,
+                                          const int (&goff)[kGenIters], const int (&g)[kGenIters], int &r0, int &r1) {
+  const unsigned char *b0 = tab + xb0, *b1 = tab + xb1;
+  int a0 = Store<ST>::kInfS, a1 = Store<ST>::kInfS, c0 = Store<ST>::kInfS, c1 = Store<ST>::kInfS;
+#pragma unroll
+  for (int k = 0; k < kGenIters; ++k) {
+    const int v = (int)*reinterpret_cast<const ST *>(b0 + goff[k]);
+    const int w = (int)*reinterpret_cast<const ST *>(b1 + goff[k]);
+    if (k & 1) {
+      a1 = __viaddmin_s32(v, g[k], a1);
+      c1 = __viaddmin_s32(w, g[k], c1);
+    } else {
+      a0 = __viaddmin_s32(v, g[k], a0);
+      c0 = __viaddmin_s32(w, g[k], c0);
+    }
+  }
+  r0 = __reduce_min_sync(0xffffffffu, min(a0, a1));
+  r1 = __reduce_min_sync(0xffffffffu, min(c0, c1));
 }
 
 template <typename ST>
