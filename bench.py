@@ -276,12 +276,15 @@ def run_ours(args):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_bytes = float(sum(synth.algorithmic_hbm_bytes(int(n)) for n in np.diff(off)))
+    # dram__bytes_read.sum + dram__bytes_write.sum of the fold kernel from the committed `ncu --set full` capture
+    # (profiles/r1_v13_wave16_full.txt: 5.12 MB read, 0 written for 23,680 folds of n = 100), scaled to this launch
+    traffic = (5122304.0 / 23680.0) * B if args.workload == "c2" else None
     roofline = {
         "bound": "smem-load/int32-alu (on-chip; neither hbm nor tensor binds this integer min-plus DP)",
         "achieved": cand_per_s / 1e9, "peak": lds_peak / 1e9, "unit": "G min-plus candidates/s (1 shared load each)",
         "frac": cand_per_s / lds_peak, "peak_source": "conflict-free ld.shared.b32 stream measured on this device by bench.py",
         "alu_peak": alu_peak / 1e9, "alu_frac": cand_per_s / alu_peak,
-        "work_per_launch": W, "kernel_ms": k_ms, "traffic": None,
+        "work_per_launch": W, "kernel_ms": k_ms, "traffic": traffic,
         "hbm": {"bound": "hbm", "achieved": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650 GB/s"},
