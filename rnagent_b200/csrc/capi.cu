@@ -225,6 +225,12 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
       for (int s0 = k; s0 < e; s0 += chunk) launches.push_back(Launch{s0, std::min(e, s0 + chunk), kClusterClasses[q], kKindCluster});
       k = e;
     }
+    if (k < B && B - k <= c->num_sms && !getenv("RNAFOLD_NO_MERGE")) {
+      // fewer sequences than SMs: one launch of the longest sequence's class (every CTA has an SM to itself,
+      // so the step costs one fold latency instead of one per length class)
+      launches.push_back(Launch{k, B, std::max(len_at(k), 8), kKindWave});
+      k = B;
+    }
     for (int cls = ncls - 1; cls >= 0 && k < B; --cls) {
       if (kWaveClasses[cls] > wave_limit) continue;
       const int lo = cls > 0 ? kWaveClasses[cls - 1] : -1;
@@ -340,7 +346,13 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     a.redo = (int32_t *)c->d_redo.p;
     a.redo_filter = 0;
     if (L.kind == kKindWave) {
-      const int threads = wave_threads(L.nmax);
+      // A launch that cannot even fill the SMs is latency-bound per fold: give each sequence a wider CTA
+      // (the per-diagonal items spread over more warps).  RNAFOLD_SMALL_THREADS overrides for experiments.
+      int threads = wave_threads(L.nmax);
+      if (count <= c->num_sms) {
+        static const int forced = getenv("RNAFOLD_SMALL_THREADS") ? atoi(getenv("RNAFOLD_SMALL_THREADS")) : 512;
+        if (forced == 256 || forced == 512) threads = std::max(threads, forced);
+      }
       const int occ = std::max(1, wave_occupancy(L.nmax, wave_esz, threads));
       const int grid = std::min(count, c->num_sms * occ);
       CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, wave_esz, grid, threads, d_ctl + 2 * li, st));

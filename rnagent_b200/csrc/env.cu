@@ -8,6 +8,9 @@
 // auto-reset of the reference's VecEnv), and one kernel emits the [N, 10, 2k] observation windows.
 // Nothing here runs on the CPU except target parsing (once per data set) and launch bookkeeping.
 #include <cuda_runtime.h>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <stdint.h>
 
 #include <cstdio>
@@ -435,10 +438,12 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
 }
 
 static int env_emit_obs(Env *e, uint8_t *obs_out) {
+  // a device destination is written by the kernel itself (no 2 MB device-to-device copy per step)
+  const bool direct = obs_out && env_is_device_ptr(obs_out);
   env_obs_kernel<<<e->n_envs, 128, 0, e->stream>>>(e->n_envs, e->lmax, e->k, e->d_cur, e->d_idx, e->d_toff, e->d_mot,
-                                                    e->d_mask, e->d_obs);
+                                                    e->d_mask, direct ? obs_out : e->d_obs);
   ENV_TRY(cudaGetLastError());
-  ENV_TRY(copy_out(obs_out, e->d_obs, (size_t)e->n_envs * kRows * 2 * e->k, e->stream));
+  if (!direct) ENV_TRY(copy_out(obs_out, e->d_obs, (size_t)e->n_envs * kRows * 2 * e->k, e->stream));
   return RNAFOLD_OK;
 }
 
@@ -458,8 +463,15 @@ int rnafold_env_reset(int32_t h, uint8_t *obs_out) {
 }
 
 // RnaDesign.step for every environment (RLIFenv.py:59-81) + the VecEnv auto-reset when enabled
+static double g_env_t[6];
+static long g_env_calls;
+static inline double env_now() {
+  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8_t *obs_out, double *reward_out,
                      uint8_t *done_out) {
+  const double t_a = env_now();
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e || !e->n_targets || !actions) return set_error(RNAFOLD_EINVAL, "bad env handle, no targets set or null actions");
@@ -476,10 +488,15 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   env_compact_kernel<<<1, 1024, 0, st>>>(N, e->lmax, e->d_done, e->d_cur, e->d_toff, e->d_tgt, e->d_seq, e->d_list, e->d_off,
                                          e->d_bseq, e->d_btgt);
   ENV_TRY(cudaGetLastError());
-  ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t) * ((size_t)N + 2), cudaMemcpyDeviceToHost, st));
+  // only the number of finished environments crosses on most steps (4 bytes); their offsets follow when there are any
+  const double t_b = env_now();
+  ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   ENV_TRY(cudaStreamSynchronize(st));
+  const double t_c = env_now();
   const int count = e->h_off[0];
   if (count > 0) {
+    ENV_TRY(cudaMemcpyAsync(e->h_off + 1, e->d_off + 1, sizeof(int32_t) * ((size_t)count + 1), cudaMemcpyDeviceToHost, st));
+    ENV_TRY(cudaStreamSynchronize(st));
     int rc = rnafold_fold_hamming_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
                                         nullptr, reward_exp, (void *)st);
     if (rc) return rc;
@@ -493,11 +510,20 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
       ENV_TRY(cudaGetLastError());
     }
   }
+  const double t_d = env_now();
   int rc = env_emit_obs(e, obs_out);
   if (rc) return rc;
   ENV_TRY(copy_out(reward_out, e->d_reward, sizeof(double) * (size_t)N, st));
   ENV_TRY(copy_out(done_out, e->d_done, (size_t)N, st));
+  const double t_e = env_now();
   ENV_TRY(cudaStreamSynchronize(st));
+  const double t_f = env_now();
+  g_env_t[0] += t_b - t_a; g_env_t[1] += t_c - t_b; g_env_t[2] += t_d - t_c; g_env_t[3] += t_e - t_d; g_env_t[4] += t_f - t_e;
+  if (++g_env_calls % 200 == 0 && getenv("RNAFOLD_ENV_TIMING")) {
+    fprintf(stderr, "[env] per step us: launch step+compact %.1f | count D2H+sync %.1f | fold+scatter+reset %.1f | obs+copies enqueue %.1f | final sync %.1f\n",
+            g_env_t[0] / 200, g_env_t[1] / 200, g_env_t[2] / 200, g_env_t[3] / 200, g_env_t[4] / 200);
+    for (double &v : g_env_t) v = 0;
+  }
   return RNAFOLD_OK;
 }
 

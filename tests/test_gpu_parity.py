@@ -132,6 +132,20 @@ def test_every_length_up_to_70(engine, oracle_params):
     _check(engine, oracle_params("turner2004"), seqs)
 
 
+def test_small_mixed_batches_take_one_launch(engine, oracle_params):
+    """Fewer sequences than SMs are folded by ONE launch of the longest sequence's class (the RL step's case):
+    short sequences then run in the wide-CTA, windowed instances as well."""
+    from rnagent_b200 import _lib
+    engine.set_vienna_params(1)
+    rng = np.random.default_rng(4242)
+    P = oracle_params("turner2004")
+    for hi in (256, 224, 128, 100, 40):
+        lens = [hi] + [int(v) for v in rng.integers(0, hi + 1, 90)]
+        seqs = ["".join(rng.choice(list("ACGU"), n)) for n in lens]
+        _check(engine, P, seqs)
+        assert _lib.last_launch_info()[0] <= 2  # fold launch + (empty) int32 re-run
+
+
 def test_fold_signature_and_edge_cases(engine):
     engine.set_vienna_params(1)
     s, e = engine.fold("GCAAAAAAAAAUUUGC")
