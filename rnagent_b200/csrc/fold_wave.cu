@@ -215,7 +215,8 @@ struct WaveSmem {
     const int cells = table_cells(nmax) + 64;
     L.C_off = take(cells * esz);
     L.F_off = take((fold_rows(L.rs) * L.rs + 64) * esz);  // folded layout, pitch rs
-    const int wcells = nmax <= kFullWinMax ? cells : kWin * L.rs + 64;
+    // short classes may also run in a windowed (wide-CTA) instance: room for whichever layout is larger
+    const int wcells = nmax <= kFullWinMax ? (cells > kWin * L.rs + 64 ? cells : kWin * L.rs + 64) : kWin * L.rs + 64;
     L.wI_off = take(wcells * esz);
     L.w1_off = take((kWin * L.rs + 64) * esz);  // c1 is only read at the two ends of a row: always a window
     L.pl_off = take(nmax * nmax / 4 + 64);          // cells whose ends can pair, diagonal by diagonal (uint8 index)
