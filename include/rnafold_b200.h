@@ -125,6 +125,27 @@ int rnafold_env_snapshot(int32_t handle, uint8_t *seq, int32_t *idx, int32_t *cu
 /* Host-only: base-pair partners (opener -> closer, -1 elsewhere) and motif codes 0..5 of one target. */
 int rnafold_parse_target(const uint8_t *dotbracket, int32_t n, int16_t *pair_out, uint8_t *motif_out);
 
+/* ---- Batched local search: Solution.permute (rlif/rna/solution.py:157-219) as reached from
+ * Solution.evaluate(permute=True) (rlif/rna/solution.py:133-141).  Every sequence is folded; those with
+ * 0 < HD <= threshold run up to `budget` rounds of mutate-around-the-mismatches / refold / keep-if-HD-improves
+ * (config keys permutation_budget, permutation_radius, permutation_threshold, mutation_probability,
+ * allow_gu_permutations of rlif/config/RnaDesign.yml:34-38, Testing.yml:4-8); all candidates of a round are
+ * folded by one batched fold.  `seq` is updated in place with the best sequence found.  Outputs (any may be NULL):
+ * structure / MFE / HD / reward of the best sequence, rounds used per sequence, total folds performed.
+ * seq/target/outputs may be host or device pointers; `off` must be a host array.  Random draws are the
+ * counter-based function rnafold_permute_draw(seed, sequence number, round, position, kind). */
+int rnafold_permute_batch(uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, int32_t budget,
+                          int32_t radius, int32_t threshold, double mutation_probability, int32_t allow_gu,
+                          uint64_t seed, double reward_exp, uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
+                          double *reward_out, int32_t *rounds_out, int32_t *folds_out);
+/* Host-only: the draw behind random.random() (kind 0: (v >> 11) * 2^-53), random.randint(0,3) (kind 1: (v >> 33) % 4)
+ * and random.randint(0,5) (kind 2: (v >> 33) % 6) of round `step` at position `pos` of sequence `index`. */
+uint64_t rnafold_permute_draw(uint64_t seed, int32_t index, int32_t step, int32_t pos, int32_t kind);
+/* RnaDesign.permute for the batched environment (RLIFenv.py:13,69-73; set through env.set_attr('permute', ...),
+ * rlif/learning/tester.py:65): terminal evaluations run rnafold_permute_batch instead of a plain fold. */
+int rnafold_env_config_permute(int32_t handle, int32_t enabled, int32_t budget, int32_t radius, int32_t threshold,
+                               double mutation_probability, int32_t allow_gu);
+
 /* Measurement helper (bench.py): on-box peaks of the two on-chip resources that bound the fold DP,
  * whole device: conflict-free 4-byte shared-memory loads per second and integer add+min
  * (min-plus candidate) updates per second. */

@@ -6,10 +6,11 @@ signatures.  Import is cheap and GPU-free; the first fold binds the CUDA library
 """
 from .dotbracket import DotBracket
 from .environments import RnaDesignBatch, RolloutStats, create_env, rollout, shard_targets
+from .permute import PermuteResult, permute_batch
 from .utils import hamming_distance
 from .vienna import (PARAM_FILES, PARAMETERS, config_vienna, cvar, fold, fold_batch, fold_hamming_batch,
                      read_parameter_file, set_vienna_params)
 
 __all__ = ["fold", "fold_batch", "fold_hamming_batch", "read_parameter_file", "set_vienna_params",
            "config_vienna", "cvar", "hamming_distance", "PARAMETERS", "PARAM_FILES", "DotBracket", "RnaDesignBatch",
-           "RolloutStats", "create_env", "rollout", "shard_targets"]
+           "RolloutStats", "create_env", "rollout", "shard_targets", "permute_batch", "PermuteResult"]

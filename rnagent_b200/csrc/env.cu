@@ -42,6 +42,11 @@ struct Env {
   int n_envs = 0, k = 25, n_targets = 0, lmax = 0;
   bool auto_reset = true, randomize = false;
   uint64_t seed = 0;
+  // Solution.permute at the terminal evaluation (RLIFenv.py:13,69-73)
+  bool permute = false;
+  int pm_budget = 50, pm_radius = 1, pm_threshold = 5, pm_allow_gu = 0;
+  double pm_p = 0.5;
+  uint64_t pm_calls = 0;
   cudaStream_t stream = nullptr;
   // data set (device, CSR over targets)
   uint8_t *d_tgt = nullptr, *d_mot = nullptr;
@@ -383,6 +388,24 @@ int rnafold_env_config(int32_t h, int32_t auto_reset, int32_t randomize, uint64_
   return RNAFOLD_OK;
 }
 
+int rnafold_env_config_permute(int32_t h, int32_t enabled, int32_t budget, int32_t radius, int32_t threshold,
+                               double mutation_probability, int32_t allow_gu) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  if (enabled && (budget < 0 || radius < 1 || radius > 64 || threshold < 0 || !(mutation_probability >= 0.0 && mutation_probability <= 1.0)))
+    return set_error(RNAFOLD_EINVAL, "bad permutation settings");
+  e->permute = enabled != 0;
+  if (enabled) {
+    e->pm_budget = budget;
+    e->pm_radius = radius;
+    e->pm_threshold = threshold;
+    e->pm_p = mutation_probability;
+    e->pm_allow_gu = allow_gu ? 1 : 0;
+  }
+  return RNAFOLD_OK;
+}
+
 // RnaDesign.set_data (RLIFenv.py:106-109): install a data set of dot-bracket targets; every environment
 // starts over at current_sequence = -1 and takes its first target.
 int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off, int32_t n_targets) {
@@ -497,8 +520,16 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   if (count > 0) {
     ENV_TRY(cudaMemcpyAsync(e->h_off + 1, e->d_off + 1, sizeof(int32_t) * ((size_t)count + 1), cudaMemcpyDeviceToHost, st));
     ENV_TRY(cudaStreamSynchronize(st));
-    int rc = rnafold_fold_hamming_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
-                                        nullptr, reward_exp, (void *)st);
+    int rc;
+    if (e->permute) {
+      // evaluate(permute=True): fold, local search on the near misses, results of the best sequence (solution.py:133-141)
+      rc = rnafold_permute_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
+                                 e->pm_allow_gu, e->seed + 0x632be59bd9b4e019ull * ++e->pm_calls, reward_exp, e->d_bdb, e->d_mfe,
+                                 e->d_hd, e->d_brw, nullptr, nullptr);
+    } else {
+      rc = rnafold_fold_hamming_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
+                                      nullptr, reward_exp, (void *)st);
+    }
     if (rc) return rc;
     env_scatter_kernel<<<count, 64, 0, st>>>(count, e->lmax, e->d_list, e->d_off, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb,
                                              e->d_bseq, e->d_cur, e->d_reward, e->d_last_db, e->d_last_seq, e->d_last_hd,

@@ -1,0 +1,341 @@
+// permute.cu -- batched local search of Solution.permute (reference: rlif/rna/solution.py:157-219) as it is
+// reached from Solution.evaluate(permute=True) (rlif/rna/solution.py:133-141): fold, and for every sequence
+// with 0 < HD <= permutation_threshold run up to permutation_budget rounds of
+//     mutate the positions around the mismatches -> refold -> keep the candidate iff its HD improves.
+// All candidates of a round are folded by ONE call of the library's batched fold (fold + Hamming + mismatch
+// flags), so a round costs one fold latency for the whole batch instead of one RNA.fold per solution.
+//
+// What is kept from the reference, quirks included:
+//   * get_surrounding (solution.py:166-181): the candidate set holds only the NEIGHBOURS (distance 1..radius)
+//     of the mismatches; the probability table is written in the reference's order (mismatches ascending,
+//     distance ascending, `probs[index] = p` first, then index-i with linspace(0.01, p, radius+1)[i-1], then
+//     index+i with linspace(...)[:-1][-i]) and later writes override earlier ones;
+//   * the mutation (solution.py:188-201): action in 0..3, or 0..5 on paired positions when
+//     allow_gu_permutations; the partner of a paired position receives the complementary letter;
+//   * acceptance (solution.py:206-212): strictly smaller HD only; the search stops at HD 0.
+// Python's `random` stream cannot be reproduced, so the draws are a counter-based hash of
+// (seed + sequence number, round, position, kind) -- the SAME function the golden-vector generator
+// (tools/make_permute_golden.py) patches into the reference's `random`, which makes the whole search
+// bit-comparable with the reference's own permute() code.  Candidate positions are visited in ascending
+// order (the reference iterates a Python set; the order only matters when two mutated positions write the
+// same nucleotide, the generator records which of its cases are order-sensitive).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../../include/rnafold_b200.h"
+#include "fold_kernels.h"
+
+namespace {
+
+using rnafold::set_error;
+
+#define PM_TRY(expr)                                                                    \
+  do {                                                                                  \
+    cudaError_t e_ = (expr);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      char buf_[256];                                                                   \
+      std::snprintf(buf_, sizeof(buf_), "%s: %s", #expr, cudaGetErrorString(e_));       \
+      return set_error(RNAFOLD_ECUDA, buf_);                                            \
+    }                                                                                   \
+  } while (0)
+
+__host__ __device__ __forceinline__ unsigned long long pm_mix64(unsigned long long x) {
+  x += 0x9e3779b97f4a7c15ull;
+  x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+  x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+  return x ^ (x >> 31);
+}
+// kind 0: random.random(); 1: random.randint(0, 3); 2: random.randint(0, 5)
+__host__ __device__ __forceinline__ unsigned long long pm_draw(unsigned long long key, int step, int pos, int kind) {
+  return pm_mix64(key ^ (((unsigned long long)(unsigned)step << 32) | ((unsigned long long)(unsigned)pos << 4) | (unsigned long long)kind));
+}
+
+struct PermuteCfg {
+  int budget, radius, threshold, allow_gu;
+  double p;
+  unsigned long long seed;
+};
+
+// partner of every paired position, both directions (DotBracket.find_base_pairs, rlif/rna/dotbracket.py:94-111:
+// unbalanced closers are skipped, unmatched openers have no partner); one thread per sequence, the stack lives
+// in the partner array's own slots of a scratch buffer
+__global__ void pm_pairs_kernel(int B, const int32_t *__restrict__ off, const uint8_t *__restrict__ tgt, int32_t *partner,
+                                int32_t *stack) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int o = off[b], n = off[b + 1] - o;
+  int top = 0;
+  for (int i = 0; i < n; ++i) partner[o + i] = -1;
+  for (int i = 0; i < n; ++i) {
+    const uint8_t c = tgt[o + i];
+    if (c == '(') stack[o + top++] = i;
+    else if (c == ')' && top > 0) {
+      const int a = stack[o + --top];
+      partner[o + a] = i;
+      partner[o + i] = a;
+    }
+  }
+}
+
+// get_surrounding (solution.py:166-181) for one sequence: prob[] >= 0 marks membership of the candidate set
+__device__ void pm_surround(int n, const uint8_t *__restrict__ mm, float *inset, double *prob, int radius, double p) {
+  for (int i = 0; i < n; ++i) inset[i] = 0.f;
+  const double stepw = (p - 0.01) / (double)radius;  // numpy.linspace(0.01, p, radius + 1): start + k * step
+  for (int index = 0; index < n; ++index) {
+    if (!mm[index]) continue;
+    for (int i = 1; i <= radius; ++i) {
+      prob[index] = p;
+      if (index - i >= 0) {
+        inset[index - i] = 1.f;
+        prob[index - i] = 0.01 + (double)(i - 1) * stepw;
+      }
+      if (index + i <= n - 1) {
+        inset[index + i] = 1.f;
+        prob[index + i] = 0.01 + (double)(radius - i) * stepw;
+      }
+    }
+  }
+}
+
+// after the first fold: which sequences enter the search (0 < HD <= threshold), their first candidate sets
+__global__ void pm_init_kernel(int B, const int32_t *__restrict__ off, const int32_t *__restrict__ hd, const uint8_t *__restrict__ mm,
+                               float *inset, double *prob, uint8_t *active, int32_t *rounds, PermuteCfg cfg) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int o = off[b], n = off[b + 1] - o;
+  const int act = (hd[b] > 0 && hd[b] <= cfg.threshold && cfg.budget > 0) ? 1 : 0;
+  active[b] = (uint8_t)act;
+  rounds[b] = 0;
+  if (act) pm_surround(n, mm + o, inset + o, prob + o, cfg.radius, cfg.p);
+}
+
+// one round's candidates: gather the best sequence (and its target) of every searching solution into the
+// compacted batch, then apply the mutations of this round in ascending position order
+__global__ void pm_mutate_kernel(int count, int step, const int32_t *__restrict__ list, const int32_t *__restrict__ boff,
+                                 const int32_t *__restrict__ off, const uint8_t *__restrict__ best, const uint8_t *__restrict__ tgt,
+                                 const int32_t *__restrict__ partner, const float *__restrict__ inset,
+                                 const double *__restrict__ prob, uint8_t *bseq, uint8_t *btgt, PermuteCfg cfg) {
+  const int s = blockIdx.x;
+  if (s >= count) return;
+  const int b = list[s], o = off[b], n = off[b + 1] - o, bo = boff[s];
+  for (int q = threadIdx.x; q < n; q += blockDim.x) {
+    bseq[bo + q] = best[o + q];
+    btgt[bo + q] = tgt[o + q];
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const unsigned long long key = pm_mix64(cfg.seed + (unsigned long long)b);
+  for (int m = 0; m < n; ++m) {
+    if (inset[o + m] == 0.f) continue;
+    const double u = (double)(pm_draw(key, step, m, 0) >> 11) * (1.0 / 9007199254740992.0);
+    if (!(u < prob[o + m])) continue;
+    int action = (int)((pm_draw(key, step, m, 1) >> 33) % 4ull);
+    const bool paired = tgt[o + m] != '.';
+    if (cfg.allow_gu && paired) action = (int)((pm_draw(key, step, m, 2) >> 33) % 6ull);
+    bseq[bo + m] = "ACGUGU"[action];          // mapping {0:'AU', 1:'CG', 2:'GC', 3:'UA', 4:'GU', 5:'UG'} (solution.py:20)
+    if (paired) {
+      const int pr = partner[o + m];
+      if (pr >= 0) bseq[bo + pr] = "UGCAUG"[action];
+    }
+  }
+}
+
+// keep a candidate iff its HD is strictly smaller (solution.py:206-212); new candidate set from its mismatches
+__global__ void pm_accept_kernel(int count, int step, const int32_t *__restrict__ list, const int32_t *__restrict__ boff,
+                                 const int32_t *__restrict__ off, const uint8_t *__restrict__ bseq, const uint8_t *__restrict__ bdb,
+                                 const uint8_t *__restrict__ bmm, const int32_t *__restrict__ bhd, const int32_t *__restrict__ bmfe,
+                                 uint8_t *best, uint8_t *best_db, int32_t *min_hd, int32_t *best_mfe, float *inset, double *prob,
+                                 uint8_t *active, int32_t *rounds, PermuteCfg cfg) {
+  const int s = blockIdx.x;
+  if (s >= count) return;
+  const int b = list[s], o = off[b], n = off[b + 1] - o, bo = boff[s];
+  const int hd = bhd[s];
+  const bool better = hd < min_hd[b];  // uniform over the block (read before anyone writes)
+  __syncthreads();
+  if (better) {
+    for (int q = threadIdx.x; q < n; q += blockDim.x) {
+      best[o + q] = bseq[bo + q];
+      best_db[o + q] = bdb[bo + q];
+    }
+  }
+  if (threadIdx.x == 0) {
+    rounds[b] = step + 1;
+    if (better) {
+      min_hd[b] = hd;
+      best_mfe[b] = bmfe[s];
+      pm_surround(n, bmm + bo, inset + o, prob + o, cfg.radius, cfg.p);
+    }
+    const int cur = better ? hd : min_hd[b];
+    active[b] = (uint8_t)((cur != 0 && step + 1 < cfg.budget) ? 1 : 0);
+  }
+}
+
+__global__ void pm_reward_kernel(int B, const int32_t *__restrict__ off, const int32_t *__restrict__ hd, double reward_exp,
+                                 double *reward) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int n = off[b + 1] - off[b];
+  double r = (n > 0) ? pow(1.0 - (double)hd[b] / (double)n, reward_exp) : 0.0;  // solution.py:145-148
+  if (hd[b] == 0) r += 0.25;
+  reward[b] = r;
+}
+
+bool pm_is_device_ptr(const void *p) {
+  if (!p) return false;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+// grow-only device scratch shared by all calls (the environment calls this once per terminal step)
+struct Scratch {
+  std::vector<void *> ptrs;
+  cudaStream_t st = nullptr;
+  size_t cap_total = 0, cap_b = 0;
+  void release() {
+    for (void *p : ptrs) cudaFree(p);
+    ptrs.clear();
+    cap_total = cap_b = 0;
+  }
+  template <typename T>
+  cudaError_t get(T **p, size_t n) {
+    cudaError_t e = cudaMalloc((void **)p, sizeof(T) * (n ? n : 1));
+    if (e == cudaSuccess) ptrs.push_back(*p);
+    return e;
+  }
+  uint8_t *d_best, *d_tgt, *d_bestdb, *d_mm, *d_bseq, *d_btgt, *d_bdb, *d_bmm, *d_active;
+  int32_t *d_off, *d_partner, *d_stack, *d_minhd, *d_mfe, *d_rounds, *d_list, *d_boff, *d_bhd, *d_bmfe;
+  float *d_inset;
+  double *d_prob, *d_reward;
+  cudaError_t reserve(size_t total, size_t NB) {
+    cudaError_t e;
+    if (!st && (e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if (total <= cap_total && NB <= cap_b) return cudaSuccess;
+    release();
+    total += total / 4 + 64;
+    NB += NB / 4 + 16;
+#define PM_GET(p, n) if ((e = get(&p, n)) != cudaSuccess) { release(); return e; }
+    PM_GET(d_best, total) PM_GET(d_tgt, total) PM_GET(d_bestdb, total) PM_GET(d_mm, total) PM_GET(d_bseq, total)
+    PM_GET(d_btgt, total) PM_GET(d_bdb, total) PM_GET(d_bmm, total) PM_GET(d_active, NB) PM_GET(d_off, NB + 1)
+    PM_GET(d_partner, total) PM_GET(d_stack, total) PM_GET(d_minhd, NB) PM_GET(d_mfe, NB) PM_GET(d_rounds, NB)
+    PM_GET(d_list, NB) PM_GET(d_boff, NB + 1) PM_GET(d_bhd, NB) PM_GET(d_bmfe, NB) PM_GET(d_inset, total)
+    PM_GET(d_prob, total) PM_GET(d_reward, NB)
+#undef PM_GET
+    cap_total = total;
+    cap_b = NB;
+    return cudaSuccess;
+  }
+};
+Scratch g_scratch;
+
+std::mutex g_pm_mu;
+
+}  // namespace
+
+extern "C" {
+
+uint64_t rnafold_permute_draw(uint64_t seed, int32_t index, int32_t step, int32_t pos, int32_t kind) {
+  return pm_draw(pm_mix64(seed + (uint64_t)(uint32_t)index), step, pos, kind);
+}
+
+int rnafold_permute_batch(uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, int32_t budget,
+                          int32_t radius, int32_t threshold, double mutation_probability, int32_t allow_gu,
+                          uint64_t seed, double reward_exp, uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
+                          double *reward_out, int32_t *rounds_out, int32_t *folds_out) {
+  std::lock_guard<std::mutex> lk(g_pm_mu);
+  if (B < 0 || !off || (B > 0 && (!seq || !target))) return set_error(RNAFOLD_EINVAL, "null seq/off/target or negative batch size");
+  if (pm_is_device_ptr(off)) return set_error(RNAFOLD_EINVAL, "permute: the CSR offsets must be a host array");
+  if (budget < 0 || radius < 1 || radius > 64 || threshold < 0 || !(mutation_probability >= 0.0 && mutation_probability <= 1.0))
+    return set_error(RNAFOLD_EINVAL, "permute: budget >= 0, 1 <= radius <= 64, threshold >= 0, 0 <= mutation_probability <= 1");
+  if (folds_out) *folds_out = 0;
+  if (B == 0) return RNAFOLD_OK;
+  const int dev = rnafold_current_device();
+  if (dev < 0) return set_error(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  PM_TRY(cudaSetDevice(dev));
+  if (off[0] != 0) return set_error(RNAFOLD_EINVAL, "off[0] must be 0");
+  for (int b = 0; b < B; ++b)
+    if (off[b + 1] < off[b] || off[b + 1] - off[b] > RNAFOLD_MAX_LEN) return set_error(RNAFOLD_EINVAL, "bad sequence length");
+  const size_t total = (size_t)off[B], NB = (size_t)B;
+  const PermuteCfg cfg{budget, radius, threshold, allow_gu ? 1 : 0, mutation_probability, (unsigned long long)seed};
+
+  Scratch &S = g_scratch;
+  PM_TRY(S.reserve(total, NB));
+  cudaStream_t st = S.st;
+  uint8_t *d_best = S.d_best, *d_tgt = S.d_tgt, *d_bestdb = S.d_bestdb, *d_mm = S.d_mm, *d_bseq = S.d_bseq, *d_btgt = S.d_btgt,
+          *d_bdb = S.d_bdb, *d_bmm = S.d_bmm, *d_active = S.d_active;
+  int32_t *d_off = S.d_off, *d_partner = S.d_partner, *d_stack = S.d_stack, *d_minhd = S.d_minhd, *d_mfe = S.d_mfe,
+          *d_rounds = S.d_rounds, *d_list = S.d_list, *d_boff = S.d_boff, *d_bhd = S.d_bhd, *d_bmfe = S.d_bmfe;
+  float *d_inset = S.d_inset;
+  double *d_prob = S.d_prob, *d_reward = S.d_reward;
+
+  const cudaMemcpyKind k_seq = pm_is_device_ptr(seq) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  const cudaMemcpyKind k_tgt = pm_is_device_ptr(target) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  PM_TRY(cudaMemcpyAsync(d_best, seq, total, k_seq, st));
+  PM_TRY(cudaMemcpyAsync(d_tgt, target, total, k_tgt, st));
+  PM_TRY(cudaMemcpyAsync(d_off, off, sizeof(int32_t) * (NB + 1), cudaMemcpyHostToDevice, st));
+  PM_TRY(cudaStreamSynchronize(st));
+
+  // the evaluation every solution gets (solution.py:133-134): fold + HD + mismatch flags
+  int folds = 0;
+  int rc = rnafold_fold_hamming_batch(d_best, off, B, d_tgt, d_bestdb, d_mfe, d_minhd, nullptr, d_mm, reward_exp, (void *)st);
+  if (rc) return rc;
+  folds += B;
+  const int tpb = 128, nblk = (B + tpb - 1) / tpb;
+  pm_pairs_kernel<<<nblk, tpb, 0, st>>>(B, d_off, d_tgt, d_partner, d_stack);
+  pm_init_kernel<<<nblk, tpb, 0, st>>>(B, d_off, d_minhd, d_mm, d_inset, d_prob, d_active, d_rounds, cfg);
+  PM_TRY(cudaGetLastError());
+
+  std::vector<uint8_t> h_active(NB);
+  std::vector<int32_t> h_list(NB), h_boff(NB + 1);
+  for (int step = 0; step < budget; ++step) {
+    PM_TRY(cudaMemcpyAsync(h_active.data(), d_active, NB, cudaMemcpyDeviceToHost, st));
+    PM_TRY(cudaStreamSynchronize(st));
+    int count = 0;
+    h_boff[0] = 0;
+    for (int b = 0; b < B; ++b)
+      if (h_active[b]) {
+        h_list[count] = b;
+        h_boff[count + 1] = h_boff[count] + (off[b + 1] - off[b]);
+        ++count;
+      }
+    if (count == 0) break;
+    PM_TRY(cudaMemcpyAsync(d_list, h_list.data(), sizeof(int32_t) * (size_t)count, cudaMemcpyHostToDevice, st));
+    PM_TRY(cudaMemcpyAsync(d_boff, h_boff.data(), sizeof(int32_t) * ((size_t)count + 1), cudaMemcpyHostToDevice, st));
+    pm_mutate_kernel<<<count, 64, 0, st>>>(count, step, d_list, d_boff, d_off, d_best, d_tgt, d_partner, d_inset, d_prob,
+                                           d_bseq, d_btgt, cfg);
+    PM_TRY(cudaGetLastError());
+    // h_list / h_boff stay untouched until the next round's synchronize, so the async copies above are safe
+    rc = rnafold_fold_hamming_batch(d_bseq, h_boff.data(), count, d_btgt, d_bdb, d_bmfe, d_bhd, nullptr, d_bmm, reward_exp, (void *)st);
+    if (rc) return rc;
+    folds += count;
+    pm_accept_kernel<<<count, 64, 0, st>>>(count, step, d_list, d_boff, d_off, d_bseq, d_bdb, d_bmm, d_bhd, d_bmfe, d_best,
+                                           d_bestdb, d_minhd, d_mfe, d_inset, d_prob, d_active, d_rounds, cfg);
+    PM_TRY(cudaGetLastError());
+  }
+  pm_reward_kernel<<<nblk, tpb, 0, st>>>(B, d_off, d_minhd, reward_exp, d_reward);
+  PM_TRY(cudaGetLastError());
+
+  auto out = [&](void *user, const void *devp, size_t bytes) -> cudaError_t {
+    if (!user || !bytes) return cudaSuccess;
+    return cudaMemcpyAsync(user, devp, bytes, pm_is_device_ptr(user) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st);
+  };
+  PM_TRY(out(seq, d_best, total));
+  PM_TRY(out(db_out, d_bestdb, total));
+  PM_TRY(out(mfe_dcal_out, d_mfe, 4 * NB));
+  PM_TRY(out(hd_out, d_minhd, 4 * NB));
+  PM_TRY(out(reward_out, d_reward, 8 * NB));
+  PM_TRY(out(rounds_out, d_rounds, 4 * NB));
+  PM_TRY(cudaStreamSynchronize(st));
+  if (folds_out) *folds_out = folds;
+  return RNAFOLD_OK;
+}
+
+}  // extern "C"

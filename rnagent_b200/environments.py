@@ -29,7 +29,7 @@ class _PrevSolution(object):
         self.target, self.string, self.folded_structure, self.hd, self.fe = target, string, folded, hd, fe
         n = max(1, len(string))
         self.r = (1 - float(hd) / float(n)) ** reward_exp + (0.25 if hd == 0 else 0.0)
-        self.source = 'rlif'
+        self.source = 'rlif'  # the local search's 'rlif*' tag (solution.py:215) is not tracked per environment
 
     def __repr__(self):
         return f"<solution hd={self.hd} fe={self.fe:.2f} {self.string}>"
@@ -39,14 +39,14 @@ class RnaDesignBatch(object):
     """N RnaDesign environments stepped in lock-step on one GPU.
 
     config keys read (same names as rlif/config/RnaDesign.yml `environment`): kernel_size, reward_exp, permute,
-    encoding_type, use_nucleotides.  permute=True / boosting / testing-mode statistics are not part of this
-    path and raise NotImplementedError instead of silently returning something else.
+    permutation_budget / _radius / _threshold, mutation_probability, allow_gu_permutations, encoding_type,
+    use_nucleotides.  With permute=True the terminal evaluation runs the batched local search
+    (Solution.permute, rlif/rna/solution.py:157-219 -> rnafold_permute_batch).  boosting / testing-mode
+    statistics are not part of this path and raise NotImplementedError instead of silently returning something else.
     """
 
     def __init__(self, config, n_envs, targets=None, rank=0, auto_reset=True, randomize=False, seed=0):
         self.config = dict(config)
-        if self.config.get('permute'):
-            raise NotImplementedError("permute=True (Solution.permute local search) is not on the batched path")
         if self.config.get('encoding_type', 2) != 2 or not self.config.get('use_nucleotides', True):
             raise NotImplementedError("only encoding_type=2 with use_nucleotides=True is implemented")
         self.n_envs = int(n_envs)
@@ -55,7 +55,7 @@ class RnaDesignBatch(object):
         self.reward_exp = float(self.config.get('reward_exp', 9))
         self.randomize = bool(randomize)
         self.meta_learning = True
-        self.permute = False
+        self.permute = bool(self.config.get('permute', False))
         self.testing_mode = False
         self.verbose = False
         self.seed = int(seed) + 7919 * int(rank)
@@ -75,7 +75,12 @@ class RnaDesignBatch(object):
             self.set_data(targets)
 
     def _configure(self):
+        from .permute import DEFAULTS
         _lib.check(self.L.rnafold_env_config(self._h, int(self.auto_reset), int(self.randomize), self.seed))
+        c = {k: self.config.get(k, v) for k, v in DEFAULTS.items()}
+        _lib.check(self.L.rnafold_env_config_permute(
+            self._h, int(bool(self.permute)), int(c['permutation_budget']), int(c['permutation_radius']),
+            int(c['permutation_threshold']), float(c['mutation_probability']), int(bool(c['allow_gu_permutations']))))
 
     # ---- RnaDesign.set_data / set_sequence (RLIFenv.py:106-113)
     def set_data(self, data):
@@ -153,12 +158,12 @@ class RnaDesignBatch(object):
     def set_attr(self, name, value):
         if name == 'dataset':
             return self.set_data(value)
-        if name in ('permute', 'boosting') and value:
-            raise NotImplementedError(f"{name}=True is not on the batched path")
+        if name == 'boosting' and value:
+            raise NotImplementedError("boosting=True is not on the batched path")
         if name == 'testing_mode' and value:
             raise NotImplementedError("testing_mode=True (partition-function statistics) is not on the batched path")
         setattr(self, name, value)
-        if name in ('randomize', 'auto_reset', 'seed'):
+        if name in ('randomize', 'auto_reset', 'seed', 'permute', 'config'):
             self._configure()
 
     def close(self):

@@ -86,5 +86,5 @@ def test_auto_reset_statistics_and_device_step():
     env.step_device(a, d_obs, d_r, d_done)
     assert int(d_obs.sum()) > 0 and env.stats().steps == 201 * N
     with pytest.raises(NotImplementedError):
-        env.set_attr("permute", True)
+        env.set_attr("boosting", True)
     env.close()

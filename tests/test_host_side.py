@@ -54,6 +54,30 @@ def test_target_parser_matches_reference_dotbracket():
     assert t.rev_base_pair_indices[25] == 2
 
 
+def test_permute_draws_mirror_the_library_and_golden_cases_are_consistent(oracle_params):
+    """The Python mirror of the local search's counter-based draws equals the library's (host-callable) function,
+    and the golden cases recorded from the reference's permute() agree with the oracle on what they claim."""
+    import ctypes
+    from rnagent_b200 import _lib, permute as pm
+    L = _lib.load_library()
+    rng = np.random.default_rng(1)
+    for _ in range(2000):
+        seed, idx, step, pos, kind = (int(rng.integers(0, 2**62)), int(rng.integers(0, 70000)), int(rng.integers(0, 60)),
+                                      int(rng.integers(0, 4000)), int(rng.integers(0, 3)))
+        assert L.rnafold_permute_draw(ctypes.c_uint64(seed), idx, step, pos, kind) == pm.draw(seed, idx, step, pos, kind)
+    u = [pm.draw_random(5, 0, s, p) for s in range(40) for p in range(50)]
+    assert 0.0 <= min(u) and max(u) < 1.0 and 0.45 < float(np.mean(u)) < 0.55
+    g = json.load(open(os.path.join(GOLDEN, "permute_cases.json")))
+    P = oracle_params("turner2004")
+    assert len(g["cases"]) >= 60 and sum(c["out_hd"] < c["hd0"] for c in g["cases"]) >= 20
+    for c in g["cases"]:
+        s, e = P.fold(c["out_seq"])
+        assert s == c["out_folded"] and sum(a != b for a, b in zip(s, c["target"])) == c["out_hd"] <= c["hd0"]
+        thr = g["configs"][c["config"]]["permutation_threshold"]
+        if not 0 < c["hd0"] <= thr:
+            assert c["out_seq"] == c["seq"] and c["folds"] == 1
+
+
 def test_hamming_distance_signature():
     from rnagent_b200 import hamming_distance
     hd, idx = hamming_distance("((..))", "(....)")
