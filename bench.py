@@ -349,6 +349,51 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
     out["n400"] = {"metric": "mfe_folds_per_sec_n400", "value": world * 2 * B / (ms * 1e-3), "unit": "folds/s",
                    "workload": desc, "ms_per_pass": ms / 2, "candidates_per_s": world * 2 * W / (ms * 1e-3),
                    "routed": _lib.last_launch_info()[1]}
+    # C5: Turner 1999, Eterna100-shaped length mix 12..400 (wave, cluster and re-run kernels in one call)
+    seq5, off5, tgt5, setno5, desc5 = make_workload("c5", rank)
+    vienna.set_vienna_params(setno5)
+    B5 = len(off5) - 1
+    d5 = [torch.from_numpy(x).to(dev) for x in (seq5, off5, tgt5)]
+    o5 = (torch.empty_like(d5[0]), torch.empty(B5, dtype=torch.int32, device=dev), torch.empty(B5, dtype=torch.int32, device=dev))
+
+    def run5():
+        _lib.fold_hamming_raw(d5[0], d5[1], B5, target=d5[2], db=o5[0], mfe=o5[1], hd=o5[2], reward_exp=9.0, stream=st.cuda_stream)
+    with torch.cuda.stream(st):
+        run5()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        run5()
+        e1.record(st)
+        e1.synchronize()
+    ms5 = max_over_ranks(e0.elapsed_time(e1))
+    out["mixed"] = {"metric": "mfe_folds_per_sec_mixed_12_400", "value": world * B5 / (ms5 * 1e-3), "unit": "folds/s",
+                    "workload": desc5, "ms_per_pass": ms5, "candidates_per_s": world * total_work(off5) / (ms5 * 1e-3),
+                    "routed": _lib.last_launch_info()[1]}
+    # A8 / N1: batched local search (Solution.permute) over 4096 near misses of n=100, the reference's Testing.yml settings
+    vienna.set_vienna_params(1)
+    rngp = np.random.default_rng(515 + rank)
+    pseq, poff = synth.random_sequences(4096, 100, 5100 + rank)
+    base = [pseq[poff[k]:poff[k + 1]].tobytes().decode() for k in range(4096)]
+    ptargets, _ = rnagent_b200.fold_batch(base)
+    near = []
+    for s_ in base:
+        s_ = list(s_)
+        for _ in range(int(rngp.integers(1, 4))):
+            s_[int(rngp.integers(0, 100))] = "ACGU"[int(rngp.integers(0, 4))]
+        near.append("".join(s_))
+    rnagent_b200.permute_batch(near[:256], ptargets[:256], rnagent_b200.permute.TESTING, seed=1)   # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    res = rnagent_b200.permute_batch(near, ptargets, rnagent_b200.permute.TESTING, seed=rank)
+    psecs = max_over_ranks(time.perf_counter() - t0)
+    searched = int((res.rounds > 0).sum())
+    out["permute"] = {"metric": "local_search_solutions_per_sec", "value": world * 4096 / psecs, "unit": "solutions/s",
+                      "folds_per_s": world * res.folds / psecs, "folds": res.folds, "searched": searched,
+                      "solved_by_search": int(((res.hd == 0) & (res.rounds > 0)).sum()),
+                      "workload": "4096 near misses (1-3 point mutations of a solving sequence) of n=100 per GPU, "
+                                  "permutation_budget 15, radius 5, threshold 15, GU allowed (rlif/config/Testing.yml:3-8); "
+                                  "host strings in, host strings out"}
     # C4: 4096 environments per GPU, n=100 targets (folds of random sequences), random actions, auto-reset
     vienna.set_vienna_params(1)
     sseq, soff = synth.random_sequences(256, 100, 4100 + rank)
