@@ -181,3 +181,50 @@ def test_device_buffers_async(engine, oracle_params):
     want, wmfe, _ = _oracle_batch(oracle_params("turner2004"), seqs)
     assert unpack(d_db.cpu().numpy(), off) == want
     assert np.array_equal(d_mfe.cpu().numpy(), wmfe)
+
+
+def _full_size_checks(engine, P, name, count, n, seed, subset, rng_seed):
+    """BASELINE.json full-size workload through the C ABI: size-independent properties on every sequence
+    (energy of the returned structure re-evaluated by the oracle's independent loop-decomposition evaluator ==
+    returned MFE; Hamming distance == byte comparison; idempotence) + bit-equality with the oracle on a subset."""
+    from rnagent_b200 import _lib, synth
+    seq, off = synth.random_sequences(count, n, seed)
+    tgt = synth.random_targets(off, seed + 1)
+    out = []
+    for _ in range(2):
+        db = np.zeros_like(seq)
+        mfe = np.zeros(count, dtype=np.int32)
+        hd = np.zeros(count, dtype=np.int32)
+        _lib.fold_hamming_raw(seq, off, count, target=tgt, db=db, mfe=mfe, hd=hd, reward_exp=9.0)
+        out.append((db, mfe, hd))
+    (db, mfe, hd), (db2, mfe2, hd2) = out
+    assert np.array_equal(db, db2) and np.array_equal(mfe, mfe2) and np.array_equal(hd, hd2)   # idempotent
+    assert set(np.unique(db).tolist()) <= {ord("("), ord(")"), ord(".")}
+    assert np.array_equal(hd, (db.reshape(count, n) != tgt.reshape(count, n)).sum(axis=1))
+    sraw, draw = seq.tobytes().decode(), db.tobytes().decode()
+    bad = 0
+    for k in range(count):
+        s, d = sraw[k * n:(k + 1) * n], draw[k * n:(k + 1) * n]
+        bad += P.eval_structure(s, d) != int(mfe[k])
+    assert bad == 0, bad
+    assert (mfe <= 0).all() and mfe.min() < -1000
+    pick = np.sort(np.random.default_rng(rng_seed).choice(count, subset, replace=False))
+    sub = np.concatenate([seq[off[k]:off[k + 1]] for k in pick])
+    soff = (np.arange(subset + 1) * n).astype(np.int32)
+    wdb, wmfe, _ = P.fold_batch(sub, soff, nthreads=0)
+    assert np.array_equal(wmfe, mfe[pick])
+    assert np.array_equal(wdb.reshape(subset, n), db.reshape(count, n)[pick])
+    return int(mfe.astype(np.int64).sum())
+
+
+def test_full_size_c2_65536_x_n100(engine, oracle_params):
+    engine.set_vienna_params(1)
+    chk = _full_size_checks(engine, oracle_params("turner2004"), "c2", 65536, 100, 100, 4096, 1)
+    assert chk == -151306730   # bench.py's checksum_mfe_dcal of the same workload
+
+
+def test_full_size_c3_8192_x_n400(engine, oracle_params):
+    from rnagent_b200 import _lib
+    engine.set_vienna_params(1)
+    _full_size_checks(engine, oracle_params("turner2004"), "c3", 8192, 400, 400, 192, 2)
+    assert _lib.last_launch_info()[1][1] == 8192   # all through the cluster kernel
