@@ -228,3 +228,15 @@ def test_full_size_c3_8192_x_n400(engine, oracle_params):
     engine.set_vienna_params(1)
     _full_size_checks(engine, oracle_params("turner2004"), "c3", 8192, 400, 400, 192, 2)
     assert _lib.last_launch_info()[1][1] == 8192   # all through the cluster kernel
+
+
+def test_load_fasta_folds_all_records_in_one_batch(engine, tmp_path):
+    engine.set_vienna_params(1)
+    fa = tmp_path / "x.fasta"
+    fa.write_text(">a\nGGGGAAAA\nCCCC\n>b\nGCAAAAAAAAATTTGC\n>c\nACGT\n")
+    sols = engine.load_fasta(str(fa))
+    assert [(s["name"], s["folded_structure"], s["fe"]) for s in sols] == [
+        ("a", "((((....))))", float(np.float32(-5.4))), ("b", "(((((......)))))", float(np.float32(-2.2))), ("c", "....", 0.0)]
+    assert sols[1]["string"] == "GCAAAAAAAAAUUUGC" and sols[1]["target"].base_pair_indices[0] == 15
+    quirk = engine.load_fasta(str(fa), reference_quirks=True)   # the reference's loop: next header's name, last record dropped
+    assert [(s["name"], s["string"]) for s in quirk] == [("b", "GGGGAAAACCCC"), ("c", "GCAAAAAAAAAUUUGC")]

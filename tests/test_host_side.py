@@ -78,6 +78,27 @@ def test_permute_draws_mirror_the_library_and_golden_cases_are_consistent(oracle
             assert c["out_seq"] == c["seq"] and c["folds"] == 1
 
 
+def test_rna_and_fasta_formats(tmp_path):
+    """.rna targets (rlif/rna/utils.py:115-129) and FASTA records (utils.py:9-63): host-side parsing only."""
+    import rnagent_b200 as rb
+    d = tmp_path / "eterna"
+    d.mkdir()
+    (d / "1.rna").write_text("((((....))))\n")
+    (d / "2.rna").write_text("..((...))..\nsecond line ignored\n")
+    t = rb.load_sequence(1, dataset="eterna", data_dir=str(tmp_path))
+    assert t.seq == "((((....))))" and t.file_nr == 1 and t.base_pair_indices[0] == 11
+    assert rb.load_sequence(7, dataset="eterna", data_dir=str(tmp_path)) == []
+    ds = rb.load_dataset("eterna", start=1, n_seqs=5, data_dir=str(tmp_path))
+    assert [x.seq for x in ds] == ["((((....))))", "..((...)).."]
+    fa = tmp_path / "x.fasta"
+    fa.write_text(">a\nGGGGAAAA\nCCCC\n>b desc\nACGT\n")
+    assert rb.read_fasta_records(str(fa)) == [("a", "GGGGAAAACCCC"), ("b desc", "ACGU")]
+    out = tmp_path / "o.fa"
+    rb.write_fasta(str(out), [dict(string="GGGGAAAACCCC", target="((((....))))", name="s1")], write_dot_brackets=True, linebreak=8)
+    assert out.read_text() == ">s1\nGGGGAAAA\nCCCC\n((((....\n))))\n"
+    assert rb.read_fasta_records(str(out))[0] == ("s1", "GGGGAAAACCCC((((....))))")
+
+
 def test_hamming_distance_signature():
     from rnagent_b200 import hamming_distance
     hd, idx = hamming_distance("((..))", "(....)")
