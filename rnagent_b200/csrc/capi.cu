@@ -588,11 +588,11 @@ int rnafold_workspace_bytes(int32_t B, int32_t nmax, size_t *bytes) {
   size_t ws = 0;
   const int sms = g_ctx ? g_ctx->num_sms : 148;
   if (nmax > kWaveClasses[sizeof(kWaveClasses) / sizeof(int) - 1]) {
-    if (nmax <= 432) {  // 2-CTA cluster kernel: int16 c and fML triangles per sequence, capped per launch
+    if (nmax <= 464) {  // 2-CTA cluster kernel: int16 c and fML triangles per sequence, capped per launch
       const size_t per_seq = 2 * cluster_table_stride(nmax) * sizeof(int16_t);
       ws = std::min(kClusterWorkspaceCap, per_seq * (size_t)B);
     }
-    // int32 kernel with tables in global memory (n > 432, and re-runs of range-check flags): 8 CTAs per SM
+    // int32 kernel with tables in global memory (n > 464, and re-runs of range-check flags): 8 CTAs per SM
     ws += sizeof(int32_t) * 2 * (size_t)table_cells(nmax) * (size_t)std::min<long long>(B, 8LL * sms);
   }
   *bytes = ws + (size_t)B * (size_t)nmax * 3 + (size_t)B * 32;

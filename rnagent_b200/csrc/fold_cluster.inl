@@ -33,7 +33,7 @@ struct ClusterSmem {
     auto take = [&](int bytes) { int r = o; o += (bytes + 15) / 16 * 16; return r; };
     L.np = wave_np(nmax);
     L.rs = (nmax + 7) / 8 * 8;
-    L.mlparts = (nmax + kMlChunk - 1) / kMlChunk;
+    L.mlparts = 1;  // split chunks are merged by atomicMin into ONE row per diagonal (three diagonals in flight)
     L.misc_off = take(64);
     L.ptab_off = take(64);
     L.S_off = take(L.np);

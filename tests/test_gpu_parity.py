@@ -76,13 +76,15 @@ def test_random_n100_block(engine, oracle_params):
 
 
 def test_random_long_cluster_kernel(engine, oracle_params):
-    """257..432 nt: 2-CTA cluster kernel (DSMEM row exchange) + warp-per-sequence f5/backtrack kernel."""
+    """257..464 nt: 2-CTA cluster kernel (DSMEM row exchange) + warp-per-sequence f5/backtrack kernel."""
     from rnagent_b200 import _lib
     engine.set_vienna_params(1)
     rng = np.random.default_rng(400)
     _check(engine, oracle_params("turner2004"), _rand_batch(rng, 160, 257, 432))
     assert _lib.last_launch_info()[1][1] == 160
     _check(engine, oracle_params("turner2004"), _rand_batch(rng, 64, 400, 400))
+    _check(engine, oracle_params("turner2004"), _rand_batch(rng, 48, 433, 464) + _rand_batch(rng, 8, 464, 464))
+    assert _lib.last_launch_info()[1][1] == 56   # the longest reference targets (451 nt) stay on the cluster path
     engine.set_vienna_params(2)
     _check(engine, oracle_params("turner1999"), _rand_batch(rng, 64, 300, 420, alphabet="GGCCAU"))
     engine.set_vienna_params(1)
