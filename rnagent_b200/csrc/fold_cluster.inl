@@ -422,7 +422,7 @@ f5_backtrack_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, co
     if (lane == 0) f5[j] = min(f5[j - 1], best);
     __syncwarp();
   }
-  const int failc = backtrack_warp<ST, false>(n, S, f5, CB, F, 0, bt, db, gp, lane);
+  const int failc = backtrack_warp<ST, false, true>(n, S, f5, CB, F, 0, bt, db, gp, lane);
   __syncwarp();
 
   int hd = 0;

@@ -44,6 +44,17 @@ struct WaveConst {
   int mmH[8][5][5], mmI[8][5][5], mm1nI[8][5][5], mmM[8][5][5], mmExt[8][5][5];
 };
 __constant__ WaveConst cW;
+// The small tables once more in the constant bank, for the backtrack of the latency-bound instances (one CTA per
+// SM: the wide-CTA kernel of small batches / long sequences and the cluster path's f5_backtrack_kernel): the
+// backtrack's lookups are warp-uniform (one pair at a time), so they become constant-cache broadcasts instead of
+// dependent global loads.  The throughput instance (128 threads, 5 CTAs/SM) keeps the global path: its register
+// allocation is at the edge and must not change.
+__constant__ SmallParams cSP;
+template <bool CP>
+__device__ __forceinline__ const SmallParams &small_params(const FoldParams *__restrict__ gp) {
+  if constexpr (CP) return cSP;
+  else return gp->s;
+}
 
 #ifdef WAVE_PHASE_CLK  // debug builds only: cycles per phase, summed over all folds (tools/phase_clocks.py)
 __device__ unsigned long long g_phase_clk[640];
@@ -386,11 +397,11 @@ __device__ __forceinline__ int div_small(int k, int nb, int qmax) {
 // order, the first hit (ballot + ffs) wins.  Tables may live in shared or global memory.
 // Returns 0 or a failure code (no decomposition found -- would mean a fill error).
 // ---------------------------------------------------------------------------------------------
-template <typename ST, bool FOLDED>
+template <typename ST, bool FOLDED, bool CP = false>
 __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, const ST *CB, const ST *F, int rp, int *bt,
                               unsigned char *db, const FoldParams *__restrict__ gp, int lane,
                               const unsigned *mlf = nullptr) {
-  const SmallParams &sp = gp->s;
+  const SmallParams &sp = small_params<CP>(gp);
   auto fx = [&](int t, int x) -> int { return FOLDED ? fold_idx(rp, t, x) : tri(n, t) + x; };
   const int tau = cW.TerminalAU;
   auto craw = [&](int cb, int type) -> int { return cb - (type > 2 ? tau : 0); };
@@ -964,7 +975,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 
     // ---- backtrack (ViennaRNA's deterministic order); warp 0, lanes scan candidates in that order
     if (warp == 0 && !misc[3]) {
-      const int failc = backtrack_warp<ST, true>(n, S, f5, CB, F, rs, bt, db, gp, lane, mlf);
+      const int failc = backtrack_warp<ST, true, (MAXT == 512)>(n, S, f5, CB, F, rs, bt, db, gp, lane, mlf);
       if (lane == 0 && failc) misc[1] = failc;
     }
     __syncthreads();
@@ -1049,6 +1060,10 @@ cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
   w.MLintern = s.MLintern;
   w.TerminalAU = s.TerminalAU;
   cudaError_t e = cudaMemcpyToSymbolAsync(cW, &w, sizeof(w), 0, cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return e;
+  static SmallParams sps;
+  sps = s;
+  e = cudaMemcpyToSymbolAsync(cSP, &sps, sizeof(sps), 0, cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) return e;
   return cudaStreamSynchronize(st);
 }
