@@ -62,7 +62,7 @@ def test_golden_rows_both_parameter_sets(engine, golden_rows, golden_folds):
     engine.set_vienna_params(1)
 
 
-@pytest.mark.parametrize("setno,name", [(1, "turner2004"), (2, "turner1999"), (3, "andronescu2007")])
+@pytest.mark.parametrize("setno,name", [(1, "turner2004"), (2, "turner1999"), (3, "andronescu2007"), (4, "langdon2018")])
 def test_random_short(engine, oracle_params, setno, name):
     engine.set_vienna_params(setno)
     rng = np.random.default_rng(100 + setno)
@@ -242,3 +242,39 @@ def test_load_fasta_folds_all_records_in_one_batch(engine, tmp_path):
     assert sols[1]["string"] == "GCAAAAAAAAAUUUGC" and sols[1]["target"].base_pair_indices[0] == 15
     quirk = engine.load_fasta(str(fa), reference_quirks=True)   # the reference's loop: next header's name, last record dropped
     assert [(s["name"], s["string"]) for s in quirk] == [("b", "GGGGAAAACCCC"), ("c", "GCAAAAAAAAAUUUGC")]
+
+
+@pytest.mark.parametrize("setno,name", [(2, "turner1999"), (3, "andronescu2007"), (4, "langdon2018")])
+def test_other_parameter_sets_on_every_kernel_family(engine, oracle_params, setno, name):
+    """Wide-CTA wave instances (129..256 nt), cluster kernel (257..464) and the global-table kernel under the
+    reference's other parameter files (rlif/rna/vienna.py:11-15)."""
+    engine.set_vienna_params(setno)
+    rng = np.random.default_rng(900 + setno)
+    seqs = _rand_batch(rng, 200, 129, 256) + _rand_batch(rng, 40, 257, 464) + _rand_batch(rng, 4, 470, 520)
+    _check(engine, oracle_params(name), seqs)
+    engine.set_vienna_params(1)
+
+
+def test_int32_tables_when_a_parameter_set_exceeds_the_int16_margin(engine, tmp_path):
+    """A parameter file whose loop terms are too large for the int16 fast path (wave_int16_ok) routes every
+    sequence through the int32 instances of the wave kernel / the int32 CTA kernels; results stay bit-exact."""
+    import oracle
+    from conftest import param_file
+    from rnagent_b200 import _lib
+    text = open(param_file("turner2004")).read()
+    head, rest = text.split("# bulge\n", 1)
+    body, tail = rest.split("\n\n", 1)
+    vals = body.split()
+    vals[-1] = "2950"          # bulge[30]: beyond the 2700 dcal margin of the int16 tables
+    big = tmp_path / "big_bulge.par"
+    big.write_text(head + "# bulge\n" + " ".join(vals) + "\n\n" + tail)
+    engine.read_parameter_file(str(big))
+    P = oracle.Params(str(big))
+    assert P.export().max() >= 2950
+    rng = np.random.default_rng(3232)
+    try:
+        _check(engine, P, _rand_batch(rng, 1500, 0, 128))
+        _check(engine, P, _rand_batch(rng, 120, 129, 256) + _rand_batch(rng, 6, 257, 330))
+        assert _lib.last_launch_info()[1][1] == 0    # no int16 cluster kernel under this parameter set
+    finally:
+        engine.set_vienna_params(1)
