@@ -211,6 +211,22 @@ def shard_targets(targets, rank, world):
     return list(targets[rank::world]) or list(targets)
 
 
+def shard_sequences(lengths, rank, world):
+    """Fold-batch shard of one rank: contiguous index ranges balanced on the work
+    sum W(n_i) (cubic in the length), not on the count -- lengths of 12..400 nt differ 3e4-fold in cost.
+    -> (begin, end) into the batch; the ranges of all ranks tile [0, len(lengths))."""
+    from .synth import work_candidates
+    import numpy as np
+    lengths = np.asarray(lengths, dtype=np.int64)
+    if world <= 1 or len(lengths) == 0:
+        return (0, len(lengths)) if rank == 0 else (len(lengths), len(lengths))
+    uniq = {int(n): float(work_candidates(int(n))) + 1.0 for n in np.unique(lengths)}
+    cum = np.cumsum([uniq[int(n)] for n in lengths])
+    cuts = [int(np.searchsorted(cum, cum[-1] * r / world, side='left')) for r in range(world + 1)]
+    cuts[0], cuts[-1] = 0, len(lengths)
+    return cuts[rank], cuts[rank + 1]
+
+
 def create_env(env_name, config, n_workers=1, targets=None, **kw):
     """rlif/learning/trainer.py:523-565 shaped factory: one batched environment replaces the n_workers processes."""
     if env_name != 'RnaDesign':

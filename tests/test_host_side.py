@@ -127,7 +127,8 @@ _GLOO_WORKER = r"""
 import os, sys
 sys.path.insert(0, {root!r})
 import torch.distributed as dist
-from rnagent_b200 import RolloutStats, shard_targets
+from rnagent_b200 import RolloutStats, shard_sequences, shard_targets
+from rnagent_b200.synth import eterna_mixed_lengths, work_candidates
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=rank, world_size=world)
 targets = ["t%d" % k for k in range(7)]
@@ -137,6 +138,16 @@ tot = local.all_reduce()
 assert tot.episodes == 7 and tot.solved == 1 and tot.sum_hd == 30 and tot.steps == 201, vars(tot)
 assert abs(tot.sum_reward - 1.5) < 1e-12 and abs(tot.sum_mfe + 4.5) < 1e-12
 assert sorted(mine + shard_targets(targets, 1 - rank, world)) == sorted(targets)
+# fold batches: contiguous shards balanced on the work sum, tiling the batch exactly
+lens = eterna_mixed_lengths(600, 5)
+b, e = shard_sequences(lens, rank, world)
+ob, oe = shard_sequences(lens, 1 - rank, world)
+assert (b, oe) == (0, 600) and e == ob if rank == 0 else (ob, e) == (0, 600) and oe == b
+t = torch_t = __import__("torch").tensor([float(sum(work_candidates(int(n)) for n in lens[b:e]))], dtype=__import__("torch").float64)
+parts = [t.clone(), t.clone()]
+dist.all_gather(parts, t)
+w = [float(p.item()) for p in parts]
+assert max(w) / sum(w) < 0.56, w     # within one long sequence of an even split
 dist.destroy_process_group()
 print("ok", rank)
 """
