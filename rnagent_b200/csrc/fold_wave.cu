@@ -750,6 +750,10 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       }
     }
 
+    // carried across phases instead of being re-derived from d by every warp in every phase: the first cells of
+    // the six rows the tabulated shapes read (diagonals max(d-2-k, 4), k = 0..5) and d mod 3 for the dml rows
+    int trow[6] = {0, 0, 0, 0, 0, 0};
+    int dm3 = (kTurn + 1) % 3;
     for (int d = kTurn + 1; d <= n + 1; ++d) {
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
@@ -858,8 +862,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
                 constexpr int kN2[9] = {0, 1, 0, 1, 2, 1, 2, 3, 2};
                 const int n1 = kN1[s], n2 = kN2[s];
                 const int t2 = PT(si[n1 + 1], sj[n2 + 1]);
-                const int row = max(d - 2 - n1 - n2, kTurn + 1);
-                const int cpq = craw((int)CB[tri(n, row) + x + 1 + n1], t2);
+                const int cpq = craw((int)CB[trow[n1 + n2] + x + 1 + n1], t2);
                 const int e = cpq + e_intloop(sp, gp, n1, n2, type, rtype_of(t2), si[1], sj[1], si[n1], sj[n2]);
                 best = (n1 + n2 <= d - 6 && t2 != 0) ? min(best, e) : best;
               }
@@ -899,7 +902,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           int s_e = kInfS;
 #pragma unroll
           for (int r = 0; r < kEParts; ++r) s_e = (d1 - 6 >= epart_beg(r)) ? min(s_e, (int)src[(2 + r) * np]) : s_e;
-          const int v_dml = dml[((d1 - 2) % 3) * np + xs + 1];
+          const int v_dml = dml[dm3 * np + xs + 1];  // row (d1 - 2) mod 3 = d mod 3
           const int pb = fold_idx(rs, max(d1 - 1, kTurn + 1), xs);
           const int f_a = (int)F[pb + 1], f_b = (int)F[pb];
           int dm = kInf;
@@ -933,7 +936,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
               wI[wrow] = (ST)kInfS;
               w1[wrow1] = (ST)kInfS;
             }
-            dml[(d1 % 3) * np + x] = dm;
+            dml[(dm3 == 0 ? 2 : dm3 - 1) * np + x] = dm;  // row d1 mod 3
             F[fold_idx(rs, d1, x)] = put<ST>(min(e, dm), flag);
           }
         } else {
@@ -952,7 +955,12 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
         }
         ITEM_CLK_END(item_kind, d >= 68 ? 1 : 0);
       }
-      // next diagonal: every slot moves one row down its table (row d-2-L has n-d+2+L cells)
+      // next diagonal: the tabulated shapes' rows shift by one (row r+1 starts n-r cells after row r)
+#pragma unroll
+      for (int k = 5; k >= 1; --k) trow[k] = trow[k - 1];
+      if (d - 2 >= kTurn + 1) trow[0] += n - (d - 2);
+      dm3 = (dm3 == 2) ? 0 : dm3 + 1;
+      // ... and every generic-shape slot moves one row down its table (row d-2-L has n-d+2+L cells)
       {
         const int ustep = (n - d + 2) * (int)sizeof(ST);
 #pragma unroll
