@@ -282,7 +282,7 @@ def run_ours(args):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_bytes = float(sum(synth.algorithmic_hbm_bytes(int(n)) for n in np.diff(off)))
     # dram__bytes_read.sum + dram__bytes_write.sum of the fold kernel from the committed `ncu --set full` capture
-    # (profiles/r1_v13_wave16_full.txt: 5.12 MB read, 0 written for 23,680 folds of n = 100), scaled to this launch
+    # (profiles/r1_v16_wave16_full.txt: 5.12 MB read, 0 written for 23,680 folds of n = 100), scaled to this launch
     traffic = (5122304.0 / 23680.0) * B if args.workload == "c2" else None
     roofline = {
         "bound": "smem-load/int32-alu (on-chip; neither hbm nor tensor binds this integer min-plus DP)",
