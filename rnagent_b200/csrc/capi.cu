@@ -157,7 +157,7 @@ struct Launch {
 
 int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target,
               uint8_t *db_out, int32_t *mfe_out, int32_t *hd_out, double *reward_out,
-              uint8_t *mismatch_out, double reward_exp, void *stream_v) {
+              uint8_t *mismatch_out, double reward_exp, void *stream_v, bool defer_sync = false) {
   if (B < 0 || !off || (B > 0 && !seq)) return fail(RNAFOLD_EINVAL, "null seq/off or negative batch size");
   c->last_launches = 0;
   c->last_routed[0] = c->last_routed[1] = c->last_routed[2] = 0;
@@ -421,7 +421,7 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     fin(target ? reward_out : nullptr, o_rw, 8 * (size_t)B);
     fin(target ? mismatch_out : nullptr, o_mm, total);
     if (status) return fail(RNAFOLD_ECUDA, "backtrack found no decomposition (code %d)", status);
-  } else if (!seq_dev || (target && !tgt_dev) || !off_dev) {
+  } else if ((!seq_dev || (target && !tgt_dev) || !off_dev) && !defer_sync) {
     // pinned staging buffers are reused by the next call
     CUDA_TRY(cudaStreamSynchronize(st));
   }
@@ -431,6 +431,15 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
 }  // namespace
 
 namespace rnafold {
+// env.cu: fold the compacted terminal batch (device buffers, host offsets) WITHOUT the trailing stream
+// synchronisation -- the environment step enqueues its scatter / reset / observation kernels behind the fold and
+// synchronises once at its end, before anything can reuse the staging buffers.
+int fold_hamming_batch_enqueue(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, uint8_t *db_out,
+                               int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  return run_batch(g_ctx, seq, off, B, target, db_out, mfe_out, hd_out, reward_out, nullptr, reward_exp, stream, true);
+}
 // error channel shared with env.cu
 int set_error(int code, const char *msg) {
   g_err = msg ? msg : "";

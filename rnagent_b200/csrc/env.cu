@@ -513,13 +513,18 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   ENV_TRY(cudaGetLastError());
   // only the number of finished environments crosses on most steps (4 bytes); their offsets follow when there are any
   const double t_b = env_now();
-  ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  // the count and the first offsets travel together (1 KB): a second round trip only for large terminal batches
+  const int prefetch = N + 2 < 258 ? N + 2 : 258;
+  ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t) * (size_t)prefetch, cudaMemcpyDeviceToHost, st));
   ENV_TRY(cudaStreamSynchronize(st));
   const double t_c = env_now();
   const int count = e->h_off[0];
   if (count > 0) {
-    ENV_TRY(cudaMemcpyAsync(e->h_off + 1, e->d_off + 1, sizeof(int32_t) * ((size_t)count + 1), cudaMemcpyDeviceToHost, st));
-    ENV_TRY(cudaStreamSynchronize(st));
+    if (count + 2 > prefetch) {
+      ENV_TRY(cudaMemcpyAsync(e->h_off + prefetch, e->d_off + prefetch, sizeof(int32_t) * (size_t)(count + 2 - prefetch),
+                              cudaMemcpyDeviceToHost, st));
+      ENV_TRY(cudaStreamSynchronize(st));
+    }
     int rc;
     if (e->permute) {
       // evaluate(permute=True): fold, local search on the near misses, results of the best sequence (solution.py:133-141)
@@ -527,8 +532,8 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
                                  e->pm_allow_gu, e->seed + 0x632be59bd9b4e019ull * ++e->pm_calls, reward_exp, e->d_bdb, e->d_mfe,
                                  e->d_hd, e->d_brw, nullptr, nullptr);
     } else {
-      rc = rnafold_fold_hamming_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
-                                      nullptr, reward_exp, (void *)st);
+      rc = rnafold::fold_hamming_batch_enqueue(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd,
+                                               e->d_brw, reward_exp, (void *)st);
     }
     if (rc) return rc;
     env_scatter_kernel<<<count, 64, 0, st>>>(count, e->lmax, e->d_list, e->d_off, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb,

@@ -81,13 +81,6 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
   int *peer_cst = cluster.map_shared_rank(cst, 1);
   int *peer_dml = cluster.map_shared_rank(dml, 0);
   int *peer_misc = cluster.map_shared_rank(misc, 1);
-  // Role rebalancing: while the pair CTA is the longer role (early diagonals: many cells, few split points) the
-  // multiloop CTA takes over its bulge / 1xn items, reading the pair CTA's windows and pair list and writing the
-  // partial minima back through distributed shared memory.
-  const ST *r0_wB = cluster.map_shared_rank(wB, 0), *r0_w1 = cluster.map_shared_rank(w1, 0);
-  const unsigned short *r0_pl = cluster.map_shared_rank(pl, 0);
-  const int *r0_plc = cluster.map_shared_rank(plc, 0);
-  ST *r0_part = cluster.map_shared_rank(part, 0);
   const int np = Ls.np, rs = Ls.rs, mlparts = Ls.mlparts;
   const int tid = threadIdx.x, lane = tid & 31, NW = kClusterThreads >> 5, NT = kClusterThreads;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -160,7 +153,6 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
       const int cells_d = (d < n) ? n - d : 0;
       const int nb_d = (cells_d + 31) >> 5;
       const int lmax = min(kMaxLoop, d - 6);
-      const bool e_remote = 16 * d < WAVE_ESPLIT * n;  // both CTAs agree on who runs the E items of this diagonal
       if (rank == 0) {
         // ================= pair CTA
         const int d1 = d - 1;
@@ -173,7 +165,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         int neparts = 0;
 #pragma unroll
         for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
-        const int nI = e_remote ? 0 : nbI * neparts, nT = (lmax >= 0) ? nbI : 0, nF = nb_1;
+        const int nI = nbI * neparts, nT = (lmax >= 0) ? nbI : 0, nF = nb_1;
         const int total = nI + nT + nF + nP;
         for (int k = warp; k < total; k += NW) {
           if (k < nI) {
@@ -331,33 +323,9 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         const int cells_2 = (d2 >= kTurn + 1 && d2 < n) ? n - d2 : 0;
         const int nb_2 = (cells_2 + 31) >> 5;
         const int nM = nb_d * nch;
-        // E items taken over from the pair CTA (its pair list of diagonal d was finished in the previous phase)
-        const int npair = (e_remote && lmax >= 0 && d < n) ? r0_plc[par] : 0;
-        const int nbI = (npair + 31) >> 5;
-        int neparts = 0;
-#pragma unroll
-        for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
-        const int nE = nbI * neparts;
-        const int total = nM + nb_2 + nE;
+        const int total = nM + nb_2;
         for (int k = warp; k < total; k += NW) {
-          if (k >= nM + nb_2) {
-            // ---- E(b,r) on behalf of the pair CTA: windows, pair list and result rows live in ITS shared memory
-            const int kk = k - nM - nb_2;
-            const int r = div_small(kk, nbI, kEParts), blk = kk - r * nbI;
-            const int l0 = r == 0 ? epart_beg(0) : r == 1 ? epart_beg(1) : epart_beg(2);
-            const int l1 = min((r == 0 ? epart_beg(1) : r == 1 ? epart_beg(2) : epart_beg(3)) - 1, lmax);
-            const int idx = blk * 32 + lane;
-            const int x = r0_pl[par * np + min(idx, npair - 1)];
-            const int oi = x + 1, oj = oi + d;
-            const int type = PT(S[oi], S[oj]);
-            const int v_mm1 = __ldg(&sp.mm1nI[type][S[oi + 1]][S[oj - 1]]);
-            int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
-            interior_item<ST, false, true, false>(r0_w1 + x + 1, r0_w1 + x + 1, r0_wB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
-            if (idx < npair) {
-              const int e = min(a1 + v_mm1, aB + (type > 2 ? tau : 0));
-              r0_part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
-            }
-          } else if (k < nM) {
+          if (k < nM) {
             // ---- M(b,m)
             const int m = k / nb_d, blk = k - m * nb_d;
             const int x = blk * 32 + lane, xc = min(x, cells_d - 1);

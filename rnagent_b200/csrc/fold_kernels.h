@@ -54,6 +54,11 @@ cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nm
 cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
                                 cudaStream_t st);
 
+// capi.cu: fold + Hamming of a device-resident batch with host offsets, enqueued on `stream` without a trailing
+// synchronisation (the caller synchronises before the next fold call)
+int fold_hamming_batch_enqueue(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, uint8_t *db_out,
+                               int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream);
+
 // capi.cu: records the message returned by rnafold_last_error() and passes `code` through
 int set_error(int code, const char *msg);
 

@@ -88,9 +88,6 @@ constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are r
 #ifndef WAVE_MLWANT
 #define WAVE_MLWANT 1  // cluster kernel: multiloop work items per warp the split chunks aim for
 #endif
-#ifndef WAVE_ESPLIT
-#define WAVE_ESPLIT 7  // cluster kernel: the multiloop CTA runs the bulge / 1xn items on diagonals d < n * WAVE_ESPLIT / 16
-#endif
 #ifndef WAVE_DYN
 #define WAVE_DYN 0  // 1: work items of a phase are claimed dynamically (shared-memory counter) instead of round-robin
 #endif
