@@ -2,7 +2,7 @@
 // rlif/rna/solution.py:84-155, rlif/rna/dotbracket.py:94-211).
 //
 // N environments advance in lock-step: one kernel applies the N actions (insert_nucleotide +
-// find_next_unfilled), the environments that reached their last position are compacted into a CSR
+// find_next_unfilled), the environments that reached their last position claim slots of a CSR
 // batch and folded by the library's own fold kernels (fold + Hamming + reward), the results are
 // scattered back, finished environments are optionally re-armed with their next target (the
 // auto-reset of the reference's VecEnv), and one kernel emits the [N, 10, 2k] observation windows.
@@ -60,7 +60,7 @@ struct Env {
   int32_t *d_list = nullptr, *d_off = nullptr, *d_hd = nullptr, *d_mfe = nullptr;
   uint8_t *d_bseq = nullptr, *d_btgt = nullptr, *d_bdb = nullptr;
   double *d_brw = nullptr;
-  int32_t *h_off = nullptr;  // pinned: [0] = count, [1..] offsets
+  int32_t *h_off = nullptr;  // pinned: [0] = total length, [1] = count, [2..] offsets
   // statistics: episodes, solved, sum_hd, steps (int64) ; sum_reward, sum_mfe_kcal (double)
   unsigned long long *d_istat = nullptr;
   double *d_fstat = nullptr;
@@ -124,11 +124,11 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
 
 // (re)arm environments: next target (round-robin per env, or hashed random), empty sequence
 __global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int randomize, unsigned long long seed,
-                                 const uint8_t *__restrict__ only_done, int32_t *cur, int32_t *idx, int32_t *ep,
+                                 const int32_t *__restrict__ list, int32_t *cur, int32_t *idx, int32_t *ep,
                                  uint8_t *seq, uint8_t *mask) {
-  const int e = blockIdx.x;
+  // list: the finished environments of this step (one block each); nullptr: every environment
+  const int e = list ? list[blockIdx.x] : (int)blockIdx.x;
   if (e >= n_envs) return;
-  if (only_done && !only_done[e]) return;
   __shared__ int t_next;
   if (threadIdx.x == 0) {
     const int epn = ep[e] + 1;
@@ -151,7 +151,8 @@ __global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int random
 __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict__ act, const int32_t *__restrict__ cur,
                                 const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
                                 const int16_t *__restrict__ pair, int32_t *idx, uint8_t *seq, uint8_t *mask,
-                                uint8_t *done, double *reward, unsigned long long *istat) {
+                                uint8_t *done, double *reward, unsigned long long *istat, unsigned long long *packed,
+                                int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_envs) return;
   const int t = cur[e];
@@ -176,82 +177,32 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
     done[e] = 0;
   } else {
     done[e] = 1;
+    // terminal: claim the next slot of the CSR batch that goes to the fold.  Count and total length advance in ONE
+    // 64-bit atomic, so slot order and offset order agree and the offsets form a proper CSR whatever the arrival order.
+    const unsigned long long old = atomicAdd(packed, (1ull << 32) | (unsigned long long)n);
+    const int slot = (int)(old >> 32), o0 = (int)(old & 0xffffffffull);
+    list[slot] = e;
+    boff[slot] = o0;
+    for (int q = 0; q < n; ++q) {
+      bseq[o0 + q] = s[q];
+      btgt[o0 + q] = tgt[base + q];
+    }
   }
   atomicAdd(&istat[3], 1ull);
-}
-
-// compact the terminal environments into a CSR batch (single CTA; N is a few thousand)
-__global__ void env_compact_kernel(int n_envs, int lmax, const uint8_t *__restrict__ done, const int32_t *__restrict__ cur,
-                                   const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
-                                   const uint8_t *__restrict__ seq, int32_t *list, int32_t *off, uint8_t *bseq,
-                                   uint8_t *btgt) {
-  __shared__ int s_cnt[32], s_len[32];
-  __shared__ int base_cnt, base_len;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
-  if (tid == 0) {
-    base_cnt = 0;
-    base_len = 0;
-  }
-  __syncthreads();
-  for (int e0 = 0; e0 < n_envs; e0 += blockDim.x) {
-    const int e = e0 + tid;
-    const int is = (e < n_envs && done[e]) ? 1 : 0;
-    int len = 0;
-    if (is) len = toff[cur[e] + 1] - toff[cur[e]];
-    int c = is, l = len;
-    for (int o = 1; o < 32; o <<= 1) {
-      const int tc = __shfl_up_sync(0xffffffffu, c, o), tl = __shfl_up_sync(0xffffffffu, l, o);
-      if (lane >= o) {
-        c += tc;
-        l += tl;
-      }
-    }
-    if (lane == 31) {
-      s_cnt[warp] = c;
-      s_len[warp] = l;
-    }
-    __syncthreads();
-    int pc = base_cnt, plen = base_len;
-    for (int w = 0; w < warp; ++w) {
-      pc += s_cnt[w];
-      plen += s_len[w];
-    }
-    if (is) {
-      const int slot = pc + c - 1, o0 = plen + l - len;
-      list[slot] = e;
-      off[1 + slot] = o0;  // off[0] holds the count; offsets start at off[1]
-      const int tb = toff[cur[e]];
-      for (int q = 0; q < len; ++q) {
-        bseq[o0 + q] = seq[(size_t)e * lmax + q];
-        btgt[o0 + q] = tgt[tb + q];
-      }
-    }
-    __syncthreads();
-    if (tid == 0) {
-      for (int w = 0; w < nw; ++w) {
-        base_cnt += s_cnt[w];
-        base_len += s_len[w];
-      }
-    }
-    __syncthreads();
-  }
-  if (tid == 0) {
-    off[0] = base_cnt;
-    off[1 + base_cnt] = base_len;
-  }
 }
 
 // scatter fold results back to their environments and update the rollout statistics
 __global__ void env_scatter_kernel(int count, int lmax, const int32_t *__restrict__ list, const int32_t *__restrict__ off,
                                    const double *__restrict__ brw, const int32_t *__restrict__ bhd,
                                    const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb,
-                                   const uint8_t *__restrict__ bseq, const int32_t *__restrict__ cur, double *reward,
+                                   const uint8_t *__restrict__ bseq, const int32_t *__restrict__ cur,
+                                   const int32_t *__restrict__ toff, double *reward,
                                    uint8_t *last_db, uint8_t *last_seq, int32_t *last_hd, int32_t *last_mfe,
                                    int32_t *last_t, unsigned long long *istat, double *fstat) {
   const int s = blockIdx.x;
   if (s >= count) return;
   const int e = list[s];
-  const int o0 = off[1 + s], len = off[2 + s] - o0;
+  const int o0 = off[s], len = toff[cur[e] + 1] - toff[cur[e]];
   for (int q = threadIdx.x; q < len; q += blockDim.x) {
     last_db[(size_t)e * lmax + q] = bdb[o0 + q];
     last_seq[(size_t)e * lmax + q] = bseq[o0 + q];
@@ -272,17 +223,27 @@ __global__ void env_scatter_kernel(int count, int lmax, const int32_t *__restric
 // observation window encoding[:, i:i+2k] of the zero-padded [10, len+2k] encoding (solution.py:62-75,116-123)
 __global__ void env_obs_kernel(int n_envs, int lmax, int k, const int32_t *__restrict__ cur, const int32_t *__restrict__ idx,
                                const int32_t *__restrict__ toff, const uint8_t *__restrict__ mot,
-                               const uint8_t *__restrict__ mask, uint8_t *obs) {
+                               const uint8_t *__restrict__ mask, uint8_t *obs, unsigned long long *packed) {
   const int e = blockIdx.x;
   if (e >= n_envs) return;
+  if (e == 0 && threadIdx.x == 0) *packed = 0ull;  // last kernel of every step: the next step's terminal batch starts empty
   const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
   const int w = 2 * k;
-  for (int q = threadIdx.x; q < kRows * w; q += blockDim.x) {
+  auto cell = [&](int q) -> unsigned {
     const int row = q / w, col = q - row * w;
     const int pos = i - k + col;
-    uint8_t v = 0;
+    unsigned v = 0;
     if (pos >= 0 && pos < n) v = row < 6 ? (mot[base + pos] == row) : ((mask[(size_t)e * lmax + pos] >> (row - 6)) & 1);
-    obs[(size_t)e * kRows * w + q] = v;
+    return v;
+  };
+  // kRows * w = 20 k bytes per environment: a multiple of 4, so every thread emits one 32-bit word when the
+  // destination is word-aligned
+  uint8_t *dst = obs + (size_t)e * kRows * w;
+  if ((reinterpret_cast<uintptr_t>(obs) & 3u) == 0) {
+    for (int q = 4 * threadIdx.x; q < kRows * w; q += 4 * blockDim.x)
+      *reinterpret_cast<unsigned *>(dst + q) = cell(q) | (cell(q + 1) << 8) | (cell(q + 2) << 16) | (cell(q + 3) << 24);
+  } else {
+    for (int q = threadIdx.x; q < kRows * w; q += blockDim.x) dst[q] = (uint8_t)cell(q);
   }
 }
 
@@ -344,7 +305,8 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_done, N));
   ENV_TRY(dalloc(&e->d_reward, N));
   ENV_TRY(dalloc(&e->d_list, N));
-  ENV_TRY(dalloc(&e->d_off, N + 2));
+  ENV_TRY(dalloc(&e->d_off, N + 4));
+  ENV_TRY(cudaMemset(e->d_off, 0, (N + 4) * sizeof(int32_t)));
   ENV_TRY(dalloc(&e->d_hd, N));
   ENV_TRY(dalloc(&e->d_mfe, N));
   ENV_TRY(dalloc(&e->d_brw, N));
@@ -354,7 +316,7 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_istat, 4));
   ENV_TRY(dalloc(&e->d_fstat, 2));
   ENV_TRY(dalloc(&e->d_obs, N * kRows * 2 * (size_t)kernel_size));
-  ENV_TRY(cudaMallocHost((void **)&e->h_off, sizeof(int32_t) * (N + 2)));
+  ENV_TRY(cudaMallocHost((void **)&e->h_off, sizeof(int32_t) * (N + 4)));
   ENV_TRY(cudaMemset(e->d_istat, 0, 4 * sizeof(unsigned long long)));
   ENV_TRY(cudaMemset(e->d_fstat, 0, 2 * sizeof(double)));
   ENV_TRY(cudaMemset(e->d_cur, 0xff, N * sizeof(int32_t)));  // current_sequence = -1 (RLIFenv.py:25)
@@ -464,7 +426,8 @@ static int env_emit_obs(Env *e, uint8_t *obs_out) {
   // a device destination is written by the kernel itself (no 2 MB device-to-device copy per step)
   const bool direct = obs_out && env_is_device_ptr(obs_out);
   env_obs_kernel<<<e->n_envs, 128, 0, e->stream>>>(e->n_envs, e->lmax, e->k, e->d_cur, e->d_idx, e->d_toff, e->d_mot,
-                                                    e->d_mask, direct ? obs_out : e->d_obs);
+                                                    e->d_mask, direct ? obs_out : e->d_obs,
+                                                    reinterpret_cast<unsigned long long *>(e->d_off));
   ENV_TRY(cudaGetLastError());
   if (!direct) ENV_TRY(copy_out(obs_out, e->d_obs, (size_t)e->n_envs * kRows * 2 * e->k, e->stream));
   return RNAFOLD_OK;
@@ -506,43 +469,45 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
     ENV_TRY(cudaMemcpyAsync(e->d_act, actions, sizeof(int32_t) * (size_t)N, cudaMemcpyHostToDevice, st));
     d_act = e->d_act;
   }
+  // d_off: [0] total length, [1] count (one 64-bit word advanced atomically by the terminal environments), [2..] offsets
   env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
-                                                   e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat);
-  env_compact_kernel<<<1, 1024, 0, st>>>(N, e->lmax, e->d_done, e->d_cur, e->d_toff, e->d_tgt, e->d_seq, e->d_list, e->d_off,
-                                         e->d_bseq, e->d_btgt);
+                                                   e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
+                                                   reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
+                                                   e->d_bseq, e->d_btgt);
   ENV_TRY(cudaGetLastError());
-  // only the number of finished environments crosses on most steps (4 bytes); their offsets follow when there are any
   const double t_b = env_now();
   // the count and the first offsets travel together (1 KB): a second round trip only for large terminal batches
-  const int prefetch = N + 2 < 258 ? N + 2 : 258;
+  const int prefetch = N + 3 < 259 ? N + 3 : 259;
   ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t) * (size_t)prefetch, cudaMemcpyDeviceToHost, st));
   ENV_TRY(cudaStreamSynchronize(st));
   const double t_c = env_now();
-  const int count = e->h_off[0];
+  const int count = e->h_off[1];
   if (count > 0) {
     if (count + 2 > prefetch) {
       ENV_TRY(cudaMemcpyAsync(e->h_off + prefetch, e->d_off + prefetch, sizeof(int32_t) * (size_t)(count + 2 - prefetch),
                               cudaMemcpyDeviceToHost, st));
       ENV_TRY(cudaStreamSynchronize(st));
     }
+    int32_t *boff = e->h_off + 2;   // CSR offsets of the terminal batch (slot order = arrival order)
+    boff[count] = e->h_off[0];
     int rc;
     if (e->permute) {
       // evaluate(permute=True): fold, local search on the near misses, results of the best sequence (solution.py:133-141)
-      rc = rnafold_permute_batch(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
+      rc = rnafold_permute_batch(e->d_bseq, boff, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
                                  e->pm_allow_gu, e->seed + 0x632be59bd9b4e019ull * ++e->pm_calls, reward_exp, e->d_bdb, e->d_mfe,
                                  e->d_hd, e->d_brw, nullptr, nullptr);
     } else {
-      rc = rnafold::fold_hamming_batch_enqueue(e->d_bseq, e->h_off + 1, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd,
+      rc = rnafold::fold_hamming_batch_enqueue(e->d_bseq, boff, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd,
                                                e->d_brw, reward_exp, (void *)st);
     }
     if (rc) return rc;
-    env_scatter_kernel<<<count, 64, 0, st>>>(count, e->lmax, e->d_list, e->d_off, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb,
-                                             e->d_bseq, e->d_cur, e->d_reward, e->d_last_db, e->d_last_seq, e->d_last_hd,
+    env_scatter_kernel<<<count, 64, 0, st>>>(count, e->lmax, e->d_list, e->d_off + 2, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb,
+                                             e->d_bseq, e->d_cur, e->d_toff, e->d_reward, e->d_last_db, e->d_last_seq, e->d_last_hd,
                                              e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat);
     ENV_TRY(cudaGetLastError());
     if (e->auto_reset) {
-      env_reset_kernel<<<N, 64, 0, st>>>(N, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, e->d_done, e->d_cur, e->d_idx,
-                                         e->d_ep, e->d_seq, e->d_mask);
+      env_reset_kernel<<<count, 64, 0, st>>>(N, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, e->d_list, e->d_cur,
+                                             e->d_idx, e->d_ep, e->d_seq, e->d_mask);
       ENV_TRY(cudaGetLastError());
     }
   }
@@ -556,7 +521,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   const double t_f = env_now();
   g_env_t[0] += t_b - t_a; g_env_t[1] += t_c - t_b; g_env_t[2] += t_d - t_c; g_env_t[3] += t_e - t_d; g_env_t[4] += t_f - t_e;
   if (++g_env_calls % 200 == 0 && getenv("RNAFOLD_ENV_TIMING")) {
-    fprintf(stderr, "[env] per step us: launch step+compact %.1f | count D2H+sync %.1f | fold+scatter+reset %.1f | obs+copies enqueue %.1f | final sync %.1f\n",
+    fprintf(stderr, "[env] per step us: launch step %.1f | count D2H+sync %.1f | fold+scatter+reset %.1f | obs+copies enqueue %.1f | final sync %.1f\n",
             g_env_t[0] / 200, g_env_t[1] / 200, g_env_t[2] / 200, g_env_t[3] / 200, g_env_t[4] / 200);
     for (double &v : g_env_t) v = 0;
   }
