@@ -311,6 +311,46 @@ __device__ __forceinline__ int gen_valid(int d) {
   return lmax < 6 ? 0 : (lmax == kMaxLoop ? kGenIters * 32 : gen_before(lmax + 1));
 }
 
+// shared-memory load at a 32-bit shared-space address (lane part + warp-uniform part: ptxas folds a uniform
+// register into the LDS address, which the generic-pointer form does not get)
+template <typename ST>
+__device__ __forceinline__ int lds_sa(unsigned addr) {
+  int v;
+  if (sizeof(ST) == 2) asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(addr));
+  else asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+
+template <typename ST, bool ALL>
+__device__ __forceinline__ int gen_cell_sa(unsigned xb, const int (&goff)[kGenIters], const int (&g)[kGenIters],
+                                           int nvalid, int lane) {
+  // goff[] are shared-space byte ADDRESSES of the lane's slots for cell 0, xb the warp-uniform byte offset of the cell
+  int a0 = Store<ST>::kInfS, a1 = Store<ST>::kInfS, a2 = Store<ST>::kInfS, a3 = Store<ST>::kInfS;
+  if (ALL) {
+#pragma unroll
+    for (int k = 0; k < kGenIters; ++k) {
+      const int v = lds_sa<ST>((unsigned)goff[k] + xb);
+      if ((k & 3) == 0) a0 = __viaddmin_s32(v, g[k], a0);
+      else if ((k & 3) == 1) a1 = __viaddmin_s32(v, g[k], a1);
+      else if ((k & 3) == 2) a2 = __viaddmin_s32(v, g[k], a2);
+      else a3 = __viaddmin_s32(v, g[k], a3);
+    }
+  } else {
+    const int nv = nvalid - lane;
+#pragma unroll
+    for (int k = 0; k < kGenIters; ++k) {
+      if (32 * k < nvalid) {           // warp-uniform early out
+        if (32 * k < nv) {             // this lane's slot is a valid shape on this diagonal
+          const int v = lds_sa<ST>((unsigned)goff[k] + xb);
+          if (k & 1) a1 = __viaddmin_s32(v, g[k], a1);
+          else a0 = __viaddmin_s32(v, g[k], a0);
+        }
+      }
+    }
+  }
+  return __reduce_min_sync(0xffffffffu, min(min(a0, a1), min(a2, a3)));
+}
+
 template <typename ST, bool ALL>
 __device__ __forceinline__ int gen_cell(const unsigned char *__restrict__ tab, int xb, const int (&goff)[kGenIters],
                                         const int (&g)[kGenIters], int nvalid, int lane) {
@@ -735,6 +775,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
     // generic-shape slots at d = 4: element offset of (row d-2-L, column 1+n1), its per-diagonal step and
     // the shape's size + asymmetry term (nothing of this is live across the backtrack)
     int gterm[kGenIters], goff[kGenIters];
+    const unsigned wI_sa = (unsigned)__cvta_generic_to_shared(wI);
     unsigned gpack[kGenIters / 4] = {};  // one byte per slot: L * esz (full tables) or (1 + n1) * esz (windows)
 #pragma unroll
     for (int k = 0; k < kGenIters; ++k) {
@@ -742,10 +783,10 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       const int L = ds & 255, n1 = ds >> 8;
       gterm[k] = (32 * k + lane < kGenShapes) ? cW.GI[L][n1] : kBig;
       if (kFullW) {
-        goff[k] = (tri(n, kTurn + 1 - 2 - L) + 1 + n1) * (int)sizeof(ST);
+        goff[k] = (int)wI_sa + (tri(n, kTurn + 1 - 2 - L) + 1 + n1) * (int)sizeof(ST);  // shared-space addresses
         gpack[k >> 2] |= (unsigned)(L * (int)sizeof(ST)) << (8 * (k & 3));
       } else {
-        goff[k] = (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);
+        goff[k] = (int)wI_sa + (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);
         gpack[k >> 2] |= (unsigned)((1 + n1) * (int)sizeof(ST)) << (8 * (k & 3));
       }
     }
@@ -775,16 +816,18 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 #pragma unroll 1
         for (int c = warp; c < npair; c += NW) {
           const int xv = pl[pl0 + c];
-          const int xb = xv * (int)sizeof(ST);
-          const int r = gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
+          // the cell is the same for every lane: through REDUX its byte offset lands in a uniform register and
+          // the twelve table loads address [lane offset + uniform base] without an add each
+          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int r = gen_cell_sa<ST, true>((unsigned)xb, goff, gterm, nvalid, lane);
           if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
         }
       } else if (nvalid > 0) {
 #pragma unroll 1
         for (int c = warp; c < npair; c += NW) {
           const int xv = pl[pl0 + c];
-          const int xb = xv * (int)sizeof(ST);
-          const int r = gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
+          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
+          const int r = gen_cell_sa<ST, false>((unsigned)xb, goff, gterm, nvalid, lane);
           if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
         }
       }
@@ -810,8 +853,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           const int xv = pl[pl0 + k - total];
           const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
           const int r = (nvalid == kGenSlots)
-                            ? gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane)
-                            : gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xb, goff, gterm, nvalid, lane);
+                            ? gen_cell_sa<ST, true>((unsigned)xb, goff, gterm, nvalid, lane)
+                            : gen_cell_sa<ST, false>((unsigned)xb, goff, gterm, nvalid, lane);
           if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
           continue;
         }
@@ -970,7 +1013,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
             goff[k] += ustep + b;
           } else {
             const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
-            goff[k] = (u >= b) ? u : t;
+            goff[k] = (u >= b + (int)wI_sa) ? u : t;
           }
         }
       }
