@@ -87,6 +87,8 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
   const SmallParams &sp = gp->s;
   constexpr int kInfS = Store<ST>::kInfS;
   const int tau = cW.TerminalAU;
+  const unsigned wI_sa = (unsigned)__cvta_generic_to_shared(wI), w1_sa = (unsigned)__cvta_generic_to_shared(w1),
+                 wB_sa = (unsigned)__cvta_generic_to_shared(wB);
 
   if (tid < 64) ptab[tid] = (unsigned char)(((tid >> 3) < 5 && (tid & 7) < 5) ? pair_type(tid >> 3, tid & 7) : 0);
   auto PT = [&](int x, int y) -> int { return ptab[x * 8 + y]; };
@@ -137,7 +139,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         const int ds = gdesc[32 * k + lane];
         const int L = ds & 255, n1 = ds >> 8;
         gterm[k] = (32 * k + lane < kGenShapes) ? cW.GI[L][n1] : kBig;
-        goff[k] = (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);
+        goff[k] = (int)wI_sa + (((kTurn + 1 - 2 - L) & (kWin - 1)) * rs + 1 + n1) * (int)sizeof(ST);  // shared-space addresses
         gpack[k >> 2] |= (unsigned)((1 + n1) * (int)sizeof(ST)) << (8 * (k & 3));
       }
     } else {
@@ -178,8 +180,9 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
             const int oi = x + 1, oj = oi + d;
             const int type = PT(S[oi], S[oj]);
             const int v_mm1 = __ldg(&sp.mm1nI[type][S[oi + 1]][S[oj - 1]]);
-            int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
-            interior_item<ST, false, true, false>(wI + x + 1, w1 + x + 1, wB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
+            int a1 = kInfS, aB = kInfS;
+            e_item_sa<ST, true>(w1_sa + (unsigned)((x + 1) * (int)sizeof(ST)), wB_sa + (unsigned)((x + 1) * (int)sizeof(ST)), d, n,
+                                rs, l0, l1, a1, aB);
             if (idx < npair) {
               const int e = min(a1 + v_mm1, aB + (type > 2 ? tau : 0));
               part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
@@ -281,7 +284,8 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
           for (; c + NW < npair; c += 2 * NW) {
             const int xv0 = pld[c], xv1 = pld[c + NW];
             int r0, r1;
-            gen_cell2<ST>(reinterpret_cast<const unsigned char *>(wI), xv0 * (int)sizeof(ST), xv1 * (int)sizeof(ST), goff, gterm, r0, r1);
+            gen_cell2_sa<ST>(__reduce_max_sync(0xffffffffu, (unsigned)xv0 * (unsigned)sizeof(ST)),
+                             __reduce_max_sync(0xffffffffu, (unsigned)xv1 * (unsigned)sizeof(ST)), goff, gterm, r0, r1);
             if (lane == 0) {
               part[(par * kWSlots + 0) * np + xv0] = (ST)min(r0, kInfS);
               part[(par * kWSlots + 0) * np + xv1] = (ST)min(r1, kInfS);
@@ -290,14 +294,14 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
 #pragma unroll 1
           for (; c < npair; c += NW) {
             const int xv = pld[c];
-            const int r = gen_cell<ST, true>(reinterpret_cast<const unsigned char *>(wI), xv * (int)sizeof(ST), goff, gterm, nvalid, lane);
+            const int r = gen_cell_sa<ST, true>(__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST)), goff, gterm, nvalid, lane);
             if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
           }
         } else if (nvalid > 0) {
 #pragma unroll 1
           for (int c = cg0; c < npair; c += NW) {
             const int xv = pld[c];
-            const int r = gen_cell<ST, false>(reinterpret_cast<const unsigned char *>(wI), xv * (int)sizeof(ST), goff, gterm, nvalid, lane);
+            const int r = gen_cell_sa<ST, false>(__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST)), goff, gterm, nvalid, lane);
             if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
           }
         }
@@ -305,7 +309,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         for (int k = 0; k < kGenIters; ++k) {
           const int bb = (int)((gpack[k >> 2] >> (8 * (k & 3))) & 0xffu);
           const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
-          goff[k] = (u >= bb) ? u : t;
+          goff[k] = (u >= bb + (int)wI_sa) ? u : t;
         }
       } else {
         // ================= multiloop CTA

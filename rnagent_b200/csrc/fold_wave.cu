@@ -321,6 +321,27 @@ __device__ __forceinline__ int lds_sa(unsigned addr) {
   return v;
 }
 
+// E item body (bulges and 1xn loops of loop sizes l0..l1 for the lane's cell) on shared-space addresses: p1 / pB are
+// the lane's addresses of element (row 0, its cell + 1) in the c1 window / the cB table; every row and column offset
+// is warp-uniform, so each candidate is one LDS [lane + uniform] and one VIADDMNMX with a constant-bank term.
+template <typename ST, bool BWIN>
+__device__ __forceinline__ void e_item_sa(unsigned p1, unsigned pB, int d, int n, int rs, int l0, int l1, int &a1, int &aB) {
+  constexpr int esz = (int)sizeof(ST);
+  int off = tri(n, d - 2 - l0);      // first cell of diagonal d-2-L in the full triangle
+  int step = n - d + 3 + l0;         // off(L+1) = off(L) - step(L)
+  for (int L = l0; L <= l1; ++L) {
+    const int offw = ((d - 2 - L) & (kWin - 1)) * rs;
+    const int gb = cW.GB[L], g1 = cW.G1[L];
+    const int offb = BWIN ? offw : off;
+    aB = __viaddmin_s32(lds_sa<ST>(pB + (unsigned)(offb * esz)), gb, aB);
+    aB = __viaddmin_s32(lds_sa<ST>(pB + (unsigned)((offb + L) * esz)), gb, aB);
+    a1 = __viaddmin_s32(lds_sa<ST>(p1 + (unsigned)((offw + 1) * esz)), g1, a1);
+    a1 = __viaddmin_s32(lds_sa<ST>(p1 + (unsigned)((offw + L - 1) * esz)), g1, a1);
+    off -= step;
+    ++step;
+  }
+}
+
 template <typename ST, bool ALL>
 __device__ __forceinline__ int gen_cell_sa(unsigned xb, const int (&goff)[kGenIters], const int (&g)[kGenIters],
                                            int nvalid, int lane) {
@@ -392,6 +413,26 @@ __device__ __forceinline__ void gen_cell2(const unsigned char *__restrict__ tab,
   for (int k = 0; k < kGenIters; ++k) {
     const int v = (int)*reinterpret_cast<const ST *>(b0 + goff[k]);
     const int w = (int)*reinterpret_cast<const ST *>(b1 + goff[k]);
+    if (k & 1) {
+      a1 = __viaddmin_s32(v, g[k], a1);
+      c1 = __viaddmin_s32(w, g[k], c1);
+    } else {
+      a0 = __viaddmin_s32(v, g[k], a0);
+      c0 = __viaddmin_s32(w, g[k], c0);
+    }
+  }
+  r0 = __reduce_min_sync(0xffffffffu, min(a0, a1));
+  r1 = __reduce_min_sync(0xffffffffu, min(c0, c1));
+}
+
+template <typename ST>
+__device__ __forceinline__ void gen_cell2_sa(unsigned xb0, unsigned xb1, const int (&goff)[kGenIters], const int (&g)[kGenIters],
+                                             int &r0, int &r1) {
+  int a0 = Store<ST>::kInfS, a1 = Store<ST>::kInfS, c0 = Store<ST>::kInfS, c1 = Store<ST>::kInfS;
+#pragma unroll
+  for (int k = 0; k < kGenIters; ++k) {
+    const int v = lds_sa<ST>((unsigned)goff[k] + xb0);
+    const int w = lds_sa<ST>((unsigned)goff[k] + xb1);
     if (k & 1) {
       a1 = __viaddmin_s32(v, g[k], a1);
       c1 = __viaddmin_s32(w, g[k], c1);
@@ -776,6 +817,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
     // the shape's size + asymmetry term (nothing of this is live across the backtrack)
     int gterm[kGenIters], goff[kGenIters];
     const unsigned wI_sa = (unsigned)__cvta_generic_to_shared(wI);
+    const unsigned w1_sa = (unsigned)__cvta_generic_to_shared(w1), CB_sa = (unsigned)__cvta_generic_to_shared(CB);
     unsigned gpack[kGenIters / 4] = {};  // one byte per slot: L * esz (full tables) or (1 + n1) * esz (windows)
 #pragma unroll
     for (int k = 0; k < kGenIters; ++k) {
@@ -876,8 +918,9 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           const int oi = x + 1, oj = oi + d;
           const int type = PT(S[oi], S[oj]);
           const int v_mm1 = MM1(type, S[oi + 1], S[oj - 1]);
-          int aI[4] = {kInfS, kInfS, kInfS, kInfS}, a1 = kInfS, aB = kInfS;
-          interior_item<ST, kFullW, false, false>(wI + x + 1, w1 + x + 1, CB + x + 1, d, n, rs, l0, l1, aI, a1, aB);
+          int a1 = kInfS, aB = kInfS;
+          e_item_sa<ST, false>(w1_sa + (unsigned)((x + 1) * (int)sizeof(ST)), CB_sa + (unsigned)((x + 1) * (int)sizeof(ST)), d, n,
+                               rs, l0, l1, a1, aB);
           if (idx < npair) {
             const int e = min(a1 + v_mm1, aB + (type > 2 ? tau : 0));
             part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
