@@ -103,13 +103,30 @@ __host__ __device__ constexpr int part_beg(int r) {
 #endif
 }
 __device__ __forceinline__ int part_beg_rt(int r) { return part_beg(r); }
-constexpr int kEParts = 3;            // loop-size ranges of the bulge / 1xn work items of the wave kernel
+#ifndef WAVE_EPARTS
+#define WAVE_EPARTS 2
+#endif
+#ifndef WAVE_EMID
+#define WAVE_EMID 16  // first loop size of the second bulge / 1xn part
+#endif
+constexpr int kEParts = WAVE_EPARTS;  // loop-size ranges of the bulge / 1xn work items of the wave kernel
 constexpr int kWSlots = 2 + kEParts;  // wave kernel scratch rows: generic shapes, tabulated shapes, one per E part
-__host__ __device__ constexpr int epart_beg(int r) { return r == 0 ? 2 : r == 1 ? 12 : r == 2 ? 22 : 31; }
+__host__ __device__ constexpr int epart_beg(int r) {
+#if WAVE_EPARTS == 2
+  return r == 0 ? 2 : r == 1 ? WAVE_EMID : 31;
+#elif WAVE_EPARTS == 1
+  return r == 0 ? 2 : 31;
+#else
+  return r == 0 ? 2 : r == 1 ? 12 : r == 2 ? 22 : 31;
+#endif
+}
 constexpr int kMaxMlParts = 4;
 constexpr int kBig = 10000000;  // additive term that can never win a minimum
 constexpr int kFullWinMax = 128;  // up to this length the cI / c1 tables are full triangles (cheaper row offsets)
-constexpr int kMlChunk = 128;  // split points per multiloop work item
+#ifndef WAVE_MLCHUNK
+#define WAVE_MLCHUNK 128
+#endif
+constexpr int kMlChunk = WAVE_MLCHUNK;  // split points per multiloop work item
 constexpr int kGenSlots = 12 * 32;  // lane slots of the shape-parallel generic interior item (375 shapes + padding)
 
 template <typename ST> struct Store;
