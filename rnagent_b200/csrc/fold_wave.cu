@@ -854,6 +854,10 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
     // the six rows the tabulated shapes read (diagonals max(d-2-k, 4), k = 0..5) and d mod 3 for the dml rows
     int trow[6] = {0, 0, 0, 0, 0, 0};
     int dm3 = (kTurn + 1) % 3;
+    // ... and what the finalisation of diagonal d1 = d - 1 indexes: first cell of d1 in the triangle (tri1) and in
+    // the folded fML layout (fi1), and the latter for d1 - 1 (fi0); the folded layout turns around after row T0
+    int tri1 = 0, fi1 = 0, fi0 = 0;
+    const int foldT0 = rs / 2 + 2, fold_jump = fold_idx(rs, foldT0 + 1, 0) - fold_idx(rs, foldT0, 0);
     for (int d = kTurn + 1; d <= n + 1; ++d) {
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
@@ -1006,7 +1010,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 #pragma unroll
           for (int r = 0; r < kEParts; ++r) s_e = (d1 - 6 >= epart_beg(r)) ? min(s_e, (int)src[(2 + r) * np]) : s_e;
           const int v_dml = dml[dm3 * np + xs + 1];  // row (d1 - 2) mod 3 = d mod 3
-          const int pb = fold_idx(rs, max(d1 - 1, kTurn + 1), xs);
+          const int pb = fi0 + xs;
           const int f_a = (int)F[pb + 1], f_b = (int)F[pb];
           int dm = kInf;
           const int mp1 = mlparts_of(d1, n);
@@ -1027,8 +1031,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           e = type ? min(e, cij + v_mls) : e;
           if (live) {
             const int wrow1 = (d1 & (kWin - 1)) * rs + x;
-            const int wrow = kFullW ? tri(n, d1) + x : wrow1;
-            const int cidx = tri(n, d1) + x;
+            const int wrow = kFullW ? tri1 + x : wrow1;
+            const int cidx = tri1 + x;
             if (type) {
               if (ml_only) atomicOr(&mlf[cidx >> 5], 1u << (cidx & 31));
               CB[cidx] = put<ST>(cij + (type > 2 ? tau : 0), flag);
@@ -1040,7 +1044,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
               w1[wrow1] = (ST)kInfS;
             }
             dml[(dm3 == 0 ? 2 : dm3 - 1) * np + x] = dm;  // row d1 mod 3
-            F[fold_idx(rs, d1, x)] = put<ST>(min(e, dm), flag);
+            F[fi1 + x] = put<ST>(min(e, dm), flag);
           }
         } else {
           // ---------------- X: f5[d1]
@@ -1063,6 +1067,11 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       for (int k = 5; k >= 1; --k) trow[k] = trow[k - 1];
       if (d - 2 >= kTurn + 1) trow[0] += n - (d - 2);
       dm3 = (dm3 == 2) ? 0 : dm3 + 1;
+      if (d1 >= kTurn + 1) {
+        tri1 += n - d1;
+        fi0 = fi1;
+        fi1 += (d1 < foldT0) ? rs : (d1 == foldT0 ? fold_jump : 1 - rs);
+      }
       // ... and every generic-shape slot moves one row down its table (row d-2-L has n-d+2+L cells)
       {
         const int ustep = (n - d + 2) * (int)sizeof(ST);
