@@ -7,11 +7,12 @@ signatures.  Import is cheap and GPU-free; the first fold binds the CUDA library
 from .dotbracket import DotBracket
 from .environments import RnaDesignBatch, RolloutStats, create_env, rollout, shard_sequences, shard_targets
 from .permute import PermuteResult, permute_batch
+from .solution import Solution
 from .utils import hamming_distance, load_dataset, load_fasta, load_sequence, read_fasta_records, write_fasta
 from .vienna import (PARAM_FILES, PARAMETERS, config_vienna, cvar, fold, fold_batch, fold_hamming_batch,
                      read_parameter_file, set_vienna_params)
 
 __all__ = ["fold", "fold_batch", "fold_hamming_batch", "read_parameter_file", "set_vienna_params",
            "config_vienna", "cvar", "hamming_distance", "PARAMETERS", "PARAM_FILES", "DotBracket", "RnaDesignBatch",
-           "RolloutStats", "create_env", "rollout", "shard_targets", "shard_sequences", "permute_batch", "PermuteResult",
+           "RolloutStats", "create_env", "rollout", "shard_targets", "shard_sequences", "permute_batch", "PermuteResult", "Solution",
            "load_sequence", "load_dataset", "load_fasta", "write_fasta", "read_fasta_records"]

@@ -88,3 +88,22 @@ def test_auto_reset_statistics_and_device_step():
     with pytest.raises(NotImplementedError):
         env.set_attr("boosting", True)
     env.close()
+
+
+def test_solution_object_evaluates_like_the_reference(golden):
+    """Per-object drop-in (`Solution.evaluate`, rlif/rna/solution.py:125-155) on the recorded episodes' final
+    sequences: folded structure, HD, mismatch indices, MFE and reward; with permute=True never worse."""
+    import rnagent_b200 as rb
+    rb.set_vienna_params(1)
+    cfg = dict(golden["config"], permutation_budget=15, permutation_radius=5, permutation_threshold=15,
+               allow_gu_permutations=True)
+    for ep in golden["episodes"][:16]:
+        sol = rb.Solution(target=ep["target"], config=cfg)
+        sol.str = list(ep["sequence"])
+        r, hd, mism = sol.evaluate(reward=True)
+        assert (sol.folded_structure, hd, [int(v) for v in mism]) == (ep["folded"], ep["hd"], ep["mismatch"])
+        assert sol.fe == float(np.float32(ep["fe"])) and abs(r - ep["rewards"][-1]) < 1e-12
+        better = rb.Solution(target=ep["target"], config=cfg, string=ep["sequence"])
+        assert (better.hd, better.folded_structure) == (ep["hd"], ep["folded"])
+        r2, hd2, _ = better.evaluate(permute=True, reward=True)
+        assert hd2 <= hd and rb.fold(better.string)[0] == better.folded_structure

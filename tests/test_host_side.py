@@ -99,6 +99,31 @@ def test_rna_and_fasta_formats(tmp_path):
     assert rb.read_fasta_records(str(out))[0] == ("s1", "GGGGAAAACCCC((((....))))")
 
 
+def test_solution_state_machine_replays_reference_episodes():
+    """Host-side `Solution` (insert_nucleotide / find_next_unfilled / get_state, rlif/rna/solution.py:84-123) and the
+    RnaDesign.step control flow (RLIFenv.py:59-81) against the episodes recorded from the reference's own code:
+    every observation up to the terminal step, bit for bit, without a GPU."""
+    from rnagent_b200 import DotBracket, Solution
+    g = json.load(open(os.path.join(GOLDEN, "env_episodes.json")))
+    cfg = g["config"]
+    steps = 0
+    for ep in g["episodes"]:
+        tgt = DotBracket(ep["target"])
+        sol = Solution(target=tgt, config=cfg)
+        unpack = lambda hx: np.unpackbits(np.frombuffer(bytes.fromhex(hx), dtype=np.uint8))[:np.prod(ep["obs_shape"])].reshape(ep["obs_shape"])
+        assert np.array_equal(sol.get_state().astype(np.uint8), unpack(ep["obs"][0]))
+        for k, a in enumerate(ep["actions"]):
+            sol.insert_nucleotide(a)
+            done = not (sol.index < tgt.len - 1)
+            if not done:
+                sol.find_next_unfilled()
+            assert done == ep["dones"][k]
+            assert np.array_equal(sol.get_state().astype(np.uint8), unpack(ep["obs"][k + 1])), (ep["target"], k)
+            steps += 1
+        assert sol.string == ep["sequence"]
+    assert steps >= 900
+
+
 def test_hamming_distance_signature():
     from rnagent_b200 import hamming_distance
     hd, idx = hamming_distance("((..))", "(....)")
