@@ -3,14 +3,14 @@
 // One CTA folds one sequence at a time (persistent CTAs, length-sorted queue).  Per anti-diagonal
 // d ("phase") the CTA's warps share a list of independent work items, one __syncthreads per phase:
 //
-//   I(b,r)  interior-loop partial minima of diagonal d for cell block b (32 consecutive cells) and
-//           loop-size range r.  Lanes run across cells, so for a fixed loop shape (n1,n2) every lane
-//           reads consecutive words (no bank conflicts) and the shape's energy term is warp-uniform:
-//           one LDS + one DPX VIADDMNMX (constant-bank operand) per candidate, fully unrolled.
+//   G(c)    the 375 generic interior-loop shapes of ONE pairable cell, lanes across shapes: per candidate one
+//           LDS [lane slot + uniform cell offset] and one DPX VIADDMNMX.
+//   E(b,r)  bulges and 1xn loops of loop-size range r for a block of 32 pairable cells (lanes across cells), the
+//           loop-size terms warp-uniform from the constant bank.
 //   M(b,m)  multibranch split partial minima  min_t fML(i,i+t) + fML(i+t+1,j)  of diagonal d.
 //   T(b)    the 9 tabulated small loop shapes (stack, 1-bulge, 1x1, 1x2, 2x1, 2x2, 2x3, 3x2) of diagonal d.
 //   F(b)    finalisation of diagonal d-1: hairpin, multiloop closing, combination of the partials,
-//           fML, and the pre-added table variants read by I().
+//           fML, and the pre-added table variants read by G() and E().
 //   X       one step of the exterior recursion f5[d-1].
 //
 // Storage (diagonal-major): full triangles of cB = c + TerminalAU(pair) and fML, plus 32-diagonal
@@ -76,33 +76,12 @@ __device__ unsigned long long g_phase_clk[640];
 namespace {
 
 constexpr int kWin = 32;    // rolling window depth (diagonals d-2 .. d-32 are read by phase d)
-#ifndef WAVE_PARTS
-#define WAVE_PARTS 3
-#endif
-#ifndef WAVE_FINE
-#define WAVE_FINE 0
-#endif
 #ifndef WAVE_CMM
 #define WAVE_CMM 0  // 1: the fill reads the mismatch tables from constant memory
 #endif
 #ifndef WAVE_MLWANT
 #define WAVE_MLWANT 1  // cluster kernel: multiloop work items per warp the split chunks aim for
 #endif
-#ifndef WAVE_DYN
-#define WAVE_DYN 0  // 1: work items of a phase are claimed dynamically (shared-memory counter) instead of round-robin
-#endif
-constexpr int kParts = WAVE_PARTS;   // loop-size ranges of the interior work items
-constexpr int kSlots = kParts + 1;  // one candidate minimum per part + the tabulated shapes
-__host__ __device__ constexpr int part_beg(int r) {
-#if WAVE_PARTS == 5
-  return r == 0 ? 2 : r == 1 ? 13 : r == 2 ? 19 : r == 3 ? 23 : r == 4 ? 27 : 31;
-#elif WAVE_PARTS == 4
-  return r == 0 ? 2 : r == 1 ? 15 : r == 2 ? 22 : r == 3 ? 27 : 31;
-#else
-  return r == 0 ? 2 : r == 1 ? 18 : r == 2 ? 26 : 31;
-#endif
-}
-__device__ __forceinline__ int part_beg_rt(int r) { return part_beg(r); }
 #ifndef WAVE_EPARTS
 #define WAVE_EPARTS 2
 #endif
@@ -258,59 +237,6 @@ struct WaveSmem {
 
 
 // ---------------------------------------------------------------------------------------------
-// I(b,r): all non-tabulated loop shapes with loop size L in part r, for 32 consecutive cells.
-// Element n1 of table row (d-2-L), counted from the lane's cell + 1, is the inner pair of shape
-// (n1, L-n1).  The two bulges and the two 1xn loops of a row are taken at its ends; the generic
-// shapes n1 = 2..L-2 run through one of four fixed-width unrolled bodies (shapes beyond L-2 carry
-// kBig in cW.GI and never win), so the whole scan is a few KB of code that stays in the I-cache.
-// ---------------------------------------------------------------------------------------------
-template <typename ST, int W>
-__device__ __forceinline__ void generic_body(const ST *__restrict__ row, const int *__restrict__ g, int (&a)[4]) {
-#pragma unroll
-  for (int k = 0; k < W; ++k) a[k & 3] = __viaddmin_s32((int)row[k], g[k], a[k & 3]);
-}
-
-template <typename ST, bool FULLW, bool BWIN = false, bool GEN = true>
-__device__ __forceinline__ void interior_item(const ST *__restrict__ pI, const ST *__restrict__ p1,
-                                              const ST *__restrict__ pB, int d, int n, int rs, int l0, int l1,
-                                              int (&aI)[4], int &a1, int &aB) {
-  int off = tri(n, d - 2 - l0);      // warp-uniform: first cell of diagonal d-2-L
-  int step = n - d + 3 + l0;         // off(L+1) = off(L) - step(L)
-  for (int L = l0; L <= l1; ++L) {
-    const int offw = ((d - 2 - L) & (kWin - 1)) * rs;
-    const int offi = FULLW ? off : offw;
-    const int gb = cW.GB[L], g1 = cW.G1[L];
-    const int offb = BWIN ? offw : off;
-    aB = __viaddmin_s32((int)pB[offb], gb, aB);
-    aB = __viaddmin_s32((int)pB[offb + L], gb, aB);
-    a1 = __viaddmin_s32((int)p1[offw + 1], g1, a1);
-    a1 = __viaddmin_s32((int)p1[offw + L - 1], g1, a1);
-    if (GEN && L >= 6) {  // generic shapes n1 = 2 .. L-2: smallest unrolled body that covers them
-      const ST *row = pI + offi + 2;
-      const int *g = &cW.GI[L][2];
-#if !WAVE_FINE
-      if (L <= 9) generic_body<ST, 6>(row, g, aI);
-      else if (L <= 17) generic_body<ST, 14>(row, g, aI);
-      else if (L <= 25) generic_body<ST, 22>(row, g, aI);
-      else generic_body<ST, 27>(row, g, aI);
-#else
-      switch ((L - 3 + 3) >> 2) {
-        case 1: generic_body<ST, 4>(row, g, aI); break;
-        case 2: generic_body<ST, 8>(row, g, aI); break;
-        case 3: generic_body<ST, 12>(row, g, aI); break;
-        case 4: generic_body<ST, 16>(row, g, aI); break;
-        case 5: generic_body<ST, 20>(row, g, aI); break;
-        case 6: generic_body<ST, 24>(row, g, aI); break;
-        default: generic_body<ST, 27>(row, g, aI); break;
-      }
-#endif
-    }
-    off -= step;
-    ++step;
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
 // G(cell): the generic interior shapes (n1, n2 >= 2, not 2x2 / 2x3 / 3x2) of ONE pairable cell, lanes
 // across SHAPES.  The 375 shapes with loop size 6..30 are numbered by (L, n1) ascending; lane l owns
 // shapes l, l+32, ... (12 register slots: element offset into the cI table, its per-diagonal step and
@@ -389,59 +315,6 @@ __device__ __forceinline__ int gen_cell_sa(unsigned xb, const int (&goff)[kGenIt
   return __reduce_min_sync(0xffffffffu, min(min(a0, a1), min(a2, a3)));
 }
 
-template <typename ST, bool ALL>
-__device__ __forceinline__ int gen_cell(const unsigned char *__restrict__ tab, int xb, const int (&goff)[kGenIters],
-                                        const int (&g)[kGenIters], int nvalid, int lane) {
-  // goff[] are BYTE offsets into the table, xb the (warp-uniform) byte offset of the cell
-  const unsigned char *base = tab + xb;
-  int a0 = Store<ST>::kInfS, a1 = Store<ST>::kInfS, a2 = Store<ST>::kInfS, a3 = Store<ST>::kInfS;
-  if (ALL) {
-#pragma unroll
-    for (int k = 0; k < kGenIters; ++k) {
-      const int v = (int)*reinterpret_cast<const ST *>(base + goff[k]);
-      if ((k & 3) == 0) a0 = __viaddmin_s32(v, g[k], a0);
-      else if ((k & 3) == 1) a1 = __viaddmin_s32(v, g[k], a1);
-      else if ((k & 3) == 2) a2 = __viaddmin_s32(v, g[k], a2);
-      else a3 = __viaddmin_s32(v, g[k], a3);
-    }
-  } else {
-    const int nv = nvalid - lane;
-#pragma unroll
-    for (int k = 0; k < kGenIters; ++k) {
-      if (32 * k < nvalid) {           // warp-uniform early out
-        if (32 * k < nv) {             // this lane's slot is a valid shape on this diagonal
-          const int v = (int)*reinterpret_cast<const ST *>(base + goff[k]);
-          if (k & 1) a1 = __viaddmin_s32(v, g[k], a1);
-          else a0 = __viaddmin_s32(v, g[k], a0);
-        }
-      }
-    }
-  }
-  return __reduce_min_sync(0xffffffffu, min(min(a0, a1), min(a2, a3)));
-}
-
-// two cells at once (kernels with registers to spare): twice the loads in flight per warp
-template <typename ST>
-__device__ __forceinline__ void gen_cell2(const unsigned char *__restrict__ tab, int xb0, int xb1,
-                                          const int (&goff)[kGenIters], const int (&g)[kGenIters], int &r0, int &r1) {
-  const unsigned char *b0 = tab + xb0, *b1 = tab + xb1;
-  int a0 = Store<ST>::kInfS, a1 = Store<ST>::kInfS, c0 = Store<ST>::kInfS, c1 = Store<ST>::kInfS;
-#pragma unroll
-  for (int k = 0; k < kGenIters; ++k) {
-    const int v = (int)*reinterpret_cast<const ST *>(b0 + goff[k]);
-    const int w = (int)*reinterpret_cast<const ST *>(b1 + goff[k]);
-    if (k & 1) {
-      a1 = __viaddmin_s32(v, g[k], a1);
-      c1 = __viaddmin_s32(w, g[k], c1);
-    } else {
-      a0 = __viaddmin_s32(v, g[k], a0);
-      c0 = __viaddmin_s32(w, g[k], c0);
-    }
-  }
-  r0 = __reduce_min_sync(0xffffffffu, min(a0, a1));
-  r1 = __reduce_min_sync(0xffffffffu, min(c0, c1));
-}
-
 template <typename ST>
 __device__ __forceinline__ void gen_cell2_sa(unsigned xb0, unsigned xb1, const int (&goff)[kGenIters], const int (&g)[kGenIters],
                                              int &r0, int &r1) {
@@ -469,14 +342,6 @@ __device__ __forceinline__ ST put(int v, int &flag) {
   return (ST)v;
 }
 
-__device__ __forceinline__ int nparts_of(int d, int n) {
-  if (d >= n) return 0;
-  const int lmax = min(kMaxLoop, d - 6);
-  int np = 0;
-#pragma unroll
-  for (int r = 0; r < kParts; ++r) np += (part_beg(r) <= lmax) ? 1 : 0;
-  return np;
-}
 __device__ __forceinline__ int mlparts_of(int d, int n) {
   const int nsplit = d - 2 * kTurn - 2;  // t = 4 .. d-5
   return (d < n && nsplit > 0) ? (nsplit + kMlChunk - 1) / kMlChunk : 0;
@@ -743,7 +608,6 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       misc[1] = 0;  // backtrack failure code
       misc[2] = 0;  // Hamming accumulator
       misc[3] = 0;  // range-check flag
-      misc[8] = misc[9] = misc[10] = misc[11] = 0;  // per-phase work counters (WAVE_DYN)
     }
     __syncthreads();
     const int slot = misc[0];
@@ -873,7 +737,6 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       const int nbI = (npair + 31) >> 5;
       // ---------------- G(cell): generic interior shapes, lanes across shapes, one pairable cell at a time
       const int nvalid = (d < n && !(WAVE_SKIP & 1)) ? gen_valid(d) : 0;
-#if !WAVE_DYN
       ITEM_CLK_BEGIN();
       if (nvalid == kGenSlots) {
 #pragma unroll 1
@@ -895,7 +758,6 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
         }
       }
       ITEM_CLK_END(5, d >= 68 ? 1 : 0);
-#endif
       // the block items start with the warp after the last one that took a cell, to even out the phase
       const int nG = nvalid > 0 ? npair : 0;
       int neparts = 0;
@@ -903,31 +765,13 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
       for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
       const int nI = (WAVE_SKIP & 2) ? 0 : nbI * neparts, nT = (lmax >= 0 && !(WAVE_SKIP & 4)) ? nbI : 0, nM = (WAVE_SKIP & 8) ? 0 : nb_d * mpd, nF = (WAVE_SKIP & 16) ? 0 : nb_1;
       const int total = nI + nT + nM + nF + ((WAVE_SKIP & 32) ? 0 : has_x);
-#if WAVE_DYN
-      // items are claimed from a per-phase counter, heaviest kinds first, the single-cell G items last as filler
-      int *qc = misc + 8 + (d & 3);
-      if (tid == 0) misc[8 + ((d + 1) & 3)] = 0;
-      for (;;) {
-        int k = 0;
-        if (lane == 0) k = atomicAdd(qc, 1);
-        k = __shfl_sync(0xffffffffu, k, 0);
-        if (k >= total + nG) break;
-        if (k >= total) {
-          const int xv = pl[pl0 + k - total];
-          const int xb = (int)__reduce_max_sync(0xffffffffu, (unsigned)xv * (unsigned)sizeof(ST));
-          const int r = (nvalid == kGenSlots)
-                            ? gen_cell_sa<ST, true>((unsigned)xb, goff, gterm, nvalid, lane)
-                            : gen_cell_sa<ST, false>((unsigned)xb, goff, gterm, nvalid, lane);
-          if (lane == 0) part[(par * kWSlots + 0) * np + xv] = (ST)min(r, kInfS);
-          continue;
-        }
-#else
       int k0 = warp - (nG % NW);
       if (k0 < 0) k0 += NW;
       for (int k = k0; k < total; k += NW) {
-#endif
         ITEM_CLK_BEGIN();
+#ifdef WAVE_PHASE_CLK
         const int item_kind = k < nI ? 0 : k < nI + nT ? 1 : k < nI + nT + nM ? 2 : k < nI + nT + nM + nF ? 3 : 4;
+#endif
         if (k < nI) {
           // ---------------- E(b,r): bulges and 1xn loops of the loop sizes in part r, lanes across pairable cells
           const int r = div_small(k, nbI, kEParts), blk = k - r * nbI;
