@@ -549,7 +549,10 @@ __device__ int backtrack_warp(int n, const unsigned char *S, const int *f5, cons
 #define WAVE_T128 128  // threads per CTA of the short-sequence instance (n <= 128)
 #endif
 constexpr int kSmallThreads = WAVE_T128;
-template <typename ST, int MAXT>
+// RS > 0: the row pitch of the folded fML table and of the windows is this compile-time constant (the launch's
+// length class must round up to it): the strides of the split scan become LDS immediates and the row offsets
+// shifts / small multiplies.  Instantiated for the pitches of the most common length classes; RS = 0 is generic.
+template <typename ST, int MAXT, int RS = 0>
 __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && sizeof(ST) == 2 ? WAVE_MAXREG128 : 128) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
                                                         int *__restrict__ queue) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -570,7 +573,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
   unsigned char *pl = smem + Ls.pl_off;
   unsigned short *plo = reinterpret_cast<unsigned short *>(smem + Ls.plo_off);
   unsigned *mlf = reinterpret_cast<unsigned *>(smem + Ls.mlf_off);
-  const int np = wave_np(nmax), rs = Ls.rs, mlparts = Ls.mlparts;
+  const int np = wave_np(nmax), rs = RS > 0 ? RS : Ls.rs, mlparts = Ls.mlparts;
   const int tid = threadIdx.x, lane = tid & 31;
   constexpr int NW = MAXT / 32, NT = MAXT;  // the kernel is always launched with MAXT threads
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // tells the compiler it is warp-uniform
@@ -1032,28 +1035,55 @@ cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
   return cudaStreamSynchronize(st);
 }
 
-template <typename ST, int MAXT>
-static cudaError_t launch_wave_t(const FoldParams *gp, const BatchArgs &a, int nmax, int grid, int *queue,
-                                 cudaStream_t st) {
+// pitches with a specialised instance of the short-sequence int16 kernel: the launch classes whose longest
+// sequence is 57..64, 73..80, 97..104 or 121..128 nt (the usual case when a class of a large batch is full)
+#define WAVE_RS_LIST(X) X(64) X(80) X(104) X(128)
+
+template <typename ST, int MAXT, int RS>
+static cudaError_t launch_wave_rs(const FoldParams *gp, const BatchArgs &a, int nmax, int grid, int *queue,
+                                  cudaStream_t st) {
   const size_t smem = wave_smem_bytes(nmax, (int)sizeof(ST));
   cudaError_t err =
-      cudaFuncSetAttribute(fold_wave_kernel<ST, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(fold_wave_kernel<ST, MAXT, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (err != cudaSuccess) return err;
-  fold_wave_kernel<ST, MAXT><<<grid, MAXT, smem, st>>>(gp, a, nmax, queue);
+  fold_wave_kernel<ST, MAXT, RS><<<grid, MAXT, smem, st>>>(gp, a, nmax, queue);
   return cudaGetLastError();
 }
 
 template <typename ST, int MAXT>
-static int occupancy_t(int nmax) {
+static cudaError_t launch_wave_t(const FoldParams *gp, const BatchArgs &a, int nmax, int grid, int *queue,
+                                 cudaStream_t st) {
+  if constexpr (sizeof(ST) == 2 && MAXT == kSmallThreads) {
+    const int rs = (nmax + 7) / 8 * 8;
+#define X(R) if (rs == R) return launch_wave_rs<ST, MAXT, R>(gp, a, nmax, grid, queue, st);
+    WAVE_RS_LIST(X)
+#undef X
+  }
+  return launch_wave_rs<ST, MAXT, 0>(gp, a, nmax, grid, queue, st);
+}
+
+template <typename ST, int MAXT, int RS>
+static int occupancy_rs(int nmax) {
   int nb = 0;
   const size_t smem = wave_smem_bytes(nmax, (int)sizeof(ST));
-  if (cudaFuncSetAttribute(fold_wave_kernel<ST, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+  if (cudaFuncSetAttribute(fold_wave_kernel<ST, MAXT, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
       cudaSuccess) {
     cudaGetLastError();
     return 0;
   }
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fold_wave_kernel<ST, MAXT>, MAXT, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fold_wave_kernel<ST, MAXT, RS>, MAXT, smem);
   return nb;
+}
+
+template <typename ST, int MAXT>
+static int occupancy_t(int nmax) {
+  if constexpr (sizeof(ST) == 2 && MAXT == kSmallThreads) {
+    const int rs = (nmax + 7) / 8 * 8;
+#define X(R) if (rs == R) return occupancy_rs<ST, MAXT, R>(nmax);
+    WAVE_RS_LIST(X)
+#undef X
+  }
+  return occupancy_rs<ST, MAXT, 0>(nmax);
 }
 
 #define WAVE_DISPATCH(FN, ...)                                                        \
