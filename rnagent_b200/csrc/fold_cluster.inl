@@ -56,7 +56,8 @@ struct ClusterSmem {
   }
 };
 
-template <typename ST>
+// RS > 0: compile-time row pitch (= the launch's length class), as in fold_wave_kernel
+template <typename ST, int RS = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads, 1)
 fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *__restrict__ queue,
                     ST *__restrict__ CBg, ST *__restrict__ Fg, long long gstride) {
@@ -81,7 +82,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
   int *peer_cst = cluster.map_shared_rank(cst, 1);
   int *peer_dml = cluster.map_shared_rank(dml, 0);
   int *peer_misc = cluster.map_shared_rank(misc, 1);
-  const int np = Ls.np, rs = Ls.rs, mlparts = Ls.mlparts;
+  const int np = Ls.np, rs = RS > 0 ? RS : Ls.rs, mlparts = Ls.mlparts;
   const int tid = threadIdx.x, lane = tid & 31, NW = kClusterThreads >> 5, NT = kClusterThreads;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const SmallParams &sp = gp->s;

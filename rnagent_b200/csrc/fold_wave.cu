@@ -1117,10 +1117,12 @@ extern "C" int rnafold_debug_phase_clocks(unsigned long long *out, int count, in
 size_t cluster_smem_bytes(int nmax, int esz) { return (size_t)ClusterSmem::make(nmax, esz).total; }
 size_t cluster_table_stride(int nmax) { return (size_t)(table_cells(nmax) + 64) / 8 * 8; }  // elements per table per sequence
 
-int cluster_max_active(int nmax) {
-  // co-resident 2-CTA clusters on the device for this length class
-  const size_t smem = cluster_smem_bytes(nmax, 2);
-  if (cudaFuncSetAttribute(fold_cluster_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+// one instance per cluster length class (capi.cu kClusterClasses: the class IS the row pitch) + the generic one
+#define CLUSTER_RS_LIST(X) X(288) X(320) X(352) X(400) X(432) X(464)
+
+template <int RS>
+static int cluster_max_active_rs(size_t smem) {
+  if (cudaFuncSetAttribute(fold_cluster_kernel<int16_t, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
     cudaGetLastError();
     return 0;
   }
@@ -1136,21 +1138,41 @@ int cluster_max_active(int nmax) {
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
   int nc = 0;
-  if (cudaOccupancyMaxActiveClusters(&nc, fold_cluster_kernel<int16_t>, &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&nc, fold_cluster_kernel<int16_t, RS>, &cfg) != cudaSuccess) {
     cudaGetLastError();
     return 0;
   }
   return nc;
 }
 
-cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nmax, int num_clusters, int *queue,
-                                void *cbg, void *fg, cudaStream_t st) {
+int cluster_max_active(int nmax) {
+  // co-resident 2-CTA clusters on the device for this length class
   const size_t smem = cluster_smem_bytes(nmax, 2);
-  cudaError_t err = cudaFuncSetAttribute(fold_cluster_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const int rs = (nmax + 7) / 8 * 8;
+#define X(R) if (rs == R) return cluster_max_active_rs<R>(smem);
+  CLUSTER_RS_LIST(X)
+#undef X
+  return cluster_max_active_rs<0>(smem);
+}
+
+template <int RS>
+static cudaError_t launch_fold_cluster_rs(const FoldParams *gp, const BatchArgs &a, int nmax, int num_clusters, int *queue,
+                                          void *cbg, void *fg, cudaStream_t st) {
+  const size_t smem = cluster_smem_bytes(nmax, 2);
+  cudaError_t err = cudaFuncSetAttribute(fold_cluster_kernel<int16_t, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (err != cudaSuccess) return err;
-  fold_cluster_kernel<int16_t><<<2 * num_clusters, kClusterThreads, smem, st>>>(
+  fold_cluster_kernel<int16_t, RS><<<2 * num_clusters, kClusterThreads, smem, st>>>(
       gp, a, nmax, queue, (int16_t *)cbg, (int16_t *)fg, (long long)cluster_table_stride(nmax));
   return cudaGetLastError();
+}
+
+cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nmax, int num_clusters, int *queue,
+                                void *cbg, void *fg, cudaStream_t st) {
+  const int rs = (nmax + 7) / 8 * 8;
+#define X(R) if (rs == R) return launch_fold_cluster_rs<R>(gp, a, nmax, num_clusters, queue, cbg, fg, st);
+  CLUSTER_RS_LIST(X)
+#undef X
+  return launch_fold_cluster_rs<0>(gp, a, nmax, num_clusters, queue, cbg, fg, st);
 }
 
 cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
