@@ -1038,6 +1038,8 @@ cudaError_t wave_upload_constants(const HostParams &hp, cudaStream_t st) {
 // pitches with a specialised instance of the short-sequence int16 kernel: the launch classes whose longest
 // sequence is 57..64, 73..80, 97..104 or 121..128 nt (the usual case when a class of a large batch is full)
 #define WAVE_RS_LIST(X) X(64) X(80) X(104) X(128)
+#define WAVE_RS_LIST_256(X) X(160) X(200)   // 256-thread instance: the 129..160 and 161..200 nt classes
+#define WAVE_RS_LIST_512(X) X(104) X(256)   // 512-thread instance: 225..256 nt, and small batches of ~100 nt (RL steps)
 
 template <typename ST, int MAXT, int RS>
 static cudaError_t launch_wave_rs(const FoldParams *gp, const BatchArgs &a, int nmax, int grid, int *queue,
@@ -1053,12 +1055,12 @@ static cudaError_t launch_wave_rs(const FoldParams *gp, const BatchArgs &a, int 
 template <typename ST, int MAXT>
 static cudaError_t launch_wave_t(const FoldParams *gp, const BatchArgs &a, int nmax, int grid, int *queue,
                                  cudaStream_t st) {
-  if constexpr (sizeof(ST) == 2 && MAXT == kSmallThreads) {
-    const int rs = (nmax + 7) / 8 * 8;
+  const int rs = (nmax + 7) / 8 * 8;
 #define X(R) if (rs == R) return launch_wave_rs<ST, MAXT, R>(gp, a, nmax, grid, queue, st);
-    WAVE_RS_LIST(X)
+  if constexpr (sizeof(ST) == 2 && MAXT == kSmallThreads) { WAVE_RS_LIST(X) }
+  if constexpr (sizeof(ST) == 2 && MAXT == 256) { WAVE_RS_LIST_256(X) }
+  if constexpr (sizeof(ST) == 2 && MAXT == 512) { WAVE_RS_LIST_512(X) }
 #undef X
-  }
   return launch_wave_rs<ST, MAXT, 0>(gp, a, nmax, grid, queue, st);
 }
 
@@ -1077,12 +1079,12 @@ static int occupancy_rs(int nmax) {
 
 template <typename ST, int MAXT>
 static int occupancy_t(int nmax) {
-  if constexpr (sizeof(ST) == 2 && MAXT == kSmallThreads) {
-    const int rs = (nmax + 7) / 8 * 8;
+  const int rs = (nmax + 7) / 8 * 8;
 #define X(R) if (rs == R) return occupancy_rs<ST, MAXT, R>(nmax);
-    WAVE_RS_LIST(X)
+  if constexpr (sizeof(ST) == 2 && MAXT == kSmallThreads) { WAVE_RS_LIST(X) }
+  if constexpr (sizeof(ST) == 2 && MAXT == 256) { WAVE_RS_LIST_256(X) }
+  if constexpr (sizeof(ST) == 2 && MAXT == 512) { WAVE_RS_LIST_512(X) }
 #undef X
-  }
   return occupancy_rs<ST, MAXT, 0>(nmax);
 }
 
