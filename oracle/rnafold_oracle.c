@@ -731,7 +731,7 @@ static void bf_rec(bf_ctx *x, int k, int *open, int nopen) {
 int orc_bruteforce_mfe(const orc_params *P, const char *seq_in, int n, int *mfe_dcal) {
   if (n > 20) return -1;
   char seq[32];
-  short S[34];
+  short S[34] = {0};
   int pt[34] = {0}, open[34];
   for (int k = 0; k < n; k++) {
     seq[k] = (char)toupper((unsigned char)seq_in[k]);
