@@ -41,6 +41,21 @@ def test_parameter_loader_matches_oracle(oracle_params):
     assert np.array_equal(_lib.parse_params(None), oracle_params("turner2004").export())  # built-in default
 
 
+def test_loader_reads_the_reference_original_parameter_files(oracle_params):
+    """In the build container (where the reference checkout is mounted): the C++ loader parses the reference's own
+    `rlif/utils/parameters/rna_*.par` -- enthalpy sections, C comments, INF / DEF tokens, sections in either order --
+    to exactly the tables of the shipped 37 C re-serialisations.  Skipped where the reference is absent (GPU box)."""
+    import pytest
+    from rnagent_b200 import _lib
+    ref = os.path.join(os.environ.get("RNAGENT_REFERENCE", "/root/reference"), "rlif", "utils", "parameters")
+    if not os.path.isdir(ref):
+        pytest.skip("reference checkout not present")
+    for name in ("turner2004", "turner1999", "andronescu2007", "langdon2018"):
+        ours = _lib.parse_params(os.path.join(ref, f"rna_{name}.par"))
+        assert np.array_equal(ours, _lib.parse_params(param_file(name))), name
+        assert np.array_equal(ours, oracle_params(name).export()), name
+
+
 def test_target_parser_matches_reference_dotbracket():
     from rnagent_b200 import DotBracket
     eps = json.load(open(os.path.join(GOLDEN, "env_episodes.json")))["episodes"]
