@@ -107,4 +107,12 @@ __device__ __forceinline__ int e_extloop(const SmallParams &sp, int type, int s5
   return e;
 }
 
+// E_ExtLoop without its TerminalAU term (for callers that read c + TerminalAU(pair) tables)
+__device__ __forceinline__ int e_extloop_mm(const SmallParams &sp, int type, int s5, int s3) {
+  if (s5 >= 0 && s3 >= 0) return sp.mmExt[type][s5][s3];
+  if (s5 >= 0) return sp.dangle5[type][s5];
+  if (s3 >= 0) return sp.dangle3[type][s3];
+  return 0;
+}
+
 }  // namespace rnafold

@@ -420,8 +420,8 @@ f5_backtrack_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, co
     for (int i = j - kTurn - 1 - lane; i >= 1; i -= 32) {
       const int type = pair_type(S[i], S[j]);
       if (!type) continue;
-      const int c = (int)CB[tri(n, j - i) + i - 1] - (type > 2 ? tau : 0);
-      best = min(best, f5[i - 1] + c + e_extloop(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
+      // cB = c + TerminalAU(pair): plus the mismatch / dangle part of E_ExtLoop it is c + E_ExtLoop
+      best = min(best, f5[i - 1] + (int)CB[tri(n, j - i) + i - 1] + e_extloop_mm(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
     }
     for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
     if (lane == 0) f5[j] = min(f5[j - 1], best);

@@ -901,8 +901,9 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           for (int i = j - kTurn - 1 - lane; i >= 1; i -= 32) {
             const int type = PT(S[i], S[j]);
             if (!type) continue;
-            best = min(best, f5[i - 1] + craw((int)CB[tri(n, j - i) + i - 1], type) +
-                                 e_extloop(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
+            // cB already carries TerminalAU(pair), which is also E_ExtLoop's first term: the stored value plus the
+            // mismatch / dangle part is c + E_ExtLoop
+            best = min(best, f5[i - 1] + (int)CB[tri(n, j - i) + i - 1] + e_extloop_mm(sp, type, i > 1 ? (int)S[i - 1] : -1, s3));
           }
           for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
           if (lane == 0) f5[j] = min(f5[j - 1], best);
