@@ -129,7 +129,6 @@ __global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int random
   // list: the finished environments of this step (one block each); nullptr: every environment
   const int e = list ? list[blockIdx.x] : (int)blockIdx.x;
   if (e >= n_envs) return;
-  __shared__ int t_next;
   if (threadIdx.x == 0) {
     const int epn = ep[e] + 1;
     int t;
@@ -138,7 +137,6 @@ __global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int random
     cur[e] = t;
     idx[e] = 0;
     ep[e] = epn;
-    t_next = t;
   }
   __syncthreads();
   for (int q = threadIdx.x; q < lmax; q += blockDim.x) {

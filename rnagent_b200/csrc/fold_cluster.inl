@@ -397,7 +397,6 @@ f5_backtrack_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, co
   unsigned char *S = reinterpret_cast<unsigned char *>(bt) + (np * 4 + 15) / 16 * 16;
   unsigned char *db = S + (np + 15) / 16 * 16;
   const SmallParams &sp = gp->s;
-  const int tau = cW.TerminalAU;
   const int beg = a.off[b];
   const int n = a.off[b + 1] - beg;
   const ST *CB = CBg + (long long)slot * gstride;
