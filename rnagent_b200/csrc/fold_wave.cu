@@ -861,7 +861,12 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           const int f_a = (int)F[pb + 1], f_b = (int)F[pb];
           int dm = kInf;
           const int mp1 = mlparts_of(d1, n);
-          for (int m = 0; m < mp1; ++m) dm = min(dm, (int)mlp[(par1 * mlparts + m) * np + xs]);
+          if constexpr (kFullW) {  // n <= 128: one multiloop part per diagonal
+            static_assert(kMlChunk >= kFullWinMax, "the short instance assumes a single multiloop part");
+            dm = mp1 > 0 ? (int)mlp[par1 * mlparts * np + xs] : kInf;
+          } else {
+            for (int m = 0; m < mp1; ++m) dm = min(dm, (int)mlp[(par1 * mlparts + m) * np + xs]);
+          }
           if (dm >= Store<ST>::kThr) dm = kInf;
 
           int cij = hbase + v_mmh;
