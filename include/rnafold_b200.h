@@ -23,6 +23,11 @@
  * device (detected with cudaPointerGetAttributes).  Host buffers are staged through pinned memory
  * inside the call; device buffers are used in place and the call is asynchronous on `stream`
  * (a cudaStream_t passed as void*, NULL = the context's own stream) unless any buffer is a host one.
+ * One context per process: fold calls share its scratch, so calls issued on different streams are
+ * ordered one behind the other on the device (each waits for the previous call's event); they never
+ * overlap.  A kernel-side failure of an asynchronous call (backtrack found no decomposition) is sticky:
+ * it is reported by the next call that returns host data, by the environment step's end-of-step
+ * synchronisation, or by rnafold_last_status().
  *
  * Batches are CSR: `seq` holds the ASCII nucleotides of all B sequences back to back and `off[B+1]`
  * their start offsets (off[0] = 0).  Structures are written with the same offsets.
@@ -86,6 +91,10 @@ int rnafold_fold_hamming_batch(const uint8_t *seq, const int32_t *off, int32_t B
                                double *reward_out, uint8_t *mismatch_out, double reward_exp,
                                void *stream);
 
+/* Wait for the last fold call and report the sticky device status word: 0, or the failure code of a kernel whose
+ * backtrack found no decomposition (then the return value is RNAFOLD_ECUDA).  clear != 0 resets it. */
+int rnafold_last_status(int32_t *status, int32_t clear);
+
 /* Counters of the last fold call: kernel launches issued, and sequences routed to each kernel
  * family (0: shared-memory CTA kernel, 1: cluster/DSMEM kernel, 2: global-memory kernel). */
 int rnafold_last_launch_info(int32_t *launches, int32_t routed[3]);
@@ -112,10 +121,15 @@ int rnafold_env_destroy(int32_t handle);
 /* auto_reset: re-arm finished environments inside step (VecEnv behaviour); randomize: hashed random target
  * choice instead of round-robin (RLIFenv.py:87-92; Python's RNG stream is not reproduced). */
 int rnafold_env_config(int32_t handle, int32_t auto_reset, int32_t randomize, uint64_t seed);
+/* Reward shaping of Solution.evaluate (rlif/rna/solution.py:150-151, config keys gc_penalty / gc):
+ * r = r * 0.85 + clip(fraction of U, 0, 0.15) on the terminal step. */
+int rnafold_env_config_reward(int32_t handle, int32_t gc_penalty);
 /* RnaDesign.set_data: CSR list of dot-bracket targets (host pointers). */
 int rnafold_env_set_targets(int32_t handle, const uint8_t *bytes, const int32_t *off, int32_t n_targets);
 int rnafold_env_reset(int32_t handle, uint8_t *obs_out);
-/* actions int32[N] in 0..3; reward_out float64[N]; done_out uint8[N]; any output may be NULL. */
+/* actions int32[N] in 0..3; reward_out float64[N]; done_out uint8[N]; any output may be NULL.  The step is
+ * enqueued without any host round trip (the terminal batch and its size stay on the device); it synchronises once,
+ * at its end, iff an output is a host buffer -- with device (or NULL) outputs it returns as soon as it is enqueued. */
 int rnafold_env_step(int32_t handle, const int32_t *actions, double reward_exp, uint8_t *obs_out,
                      double *reward_out, uint8_t *done_out);
 /* istat = {episodes, solved, sum HD, env steps}; fstat = {sum reward, sum MFE kcal/mol}. */

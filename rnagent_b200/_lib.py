@@ -16,9 +16,9 @@ EXPORTS = [
     "rnafold_init", "rnafold_shutdown", "rnafold_last_error", "rnafold_version",
     "rnafold_read_parameter_file", "rnafold_export_params", "rnafold_parse_params", "rnafold_set_md", "rnafold_get_md",
     "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch",
-    "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
+    "rnafold_last_status", "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
     "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes", "rnafold_current_device",
-    "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_set_targets", "rnafold_env_reset",
+    "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_config_reward", "rnafold_env_set_targets", "rnafold_env_reset",
     "rnafold_env_step", "rnafold_env_stats", "rnafold_env_snapshot", "rnafold_parse_target",
     "rnafold_permute_batch", "rnafold_permute_draw", "rnafold_env_config_permute",
 ]
@@ -56,6 +56,7 @@ def load_library():
         L.rnafold_fold_batch.argtypes = [vp, vp, ci, vp, vp, vp]
         L.rnafold_fold_hamming_batch.argtypes = [vp, vp, ci, vp, vp, vp, vp, vp, vp, cd, vp]
         L.rnafold_last_launch_info.argtypes = [ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+        L.rnafold_last_status.argtypes = [ctypes.POINTER(ctypes.c_int32), ci]
         L.rnafold_set_timing.argtypes = [ci]
         L.rnafold_last_kernel_ms.argtypes = [ctypes.POINTER(ctypes.c_float)]
         L.rnafold_measure_onchip_peaks.argtypes = [ctypes.POINTER(cd), ctypes.POINTER(cd)]
@@ -65,6 +66,7 @@ def load_library():
         L.rnafold_env_create.argtypes = [ci, ci, i32p]
         L.rnafold_env_destroy.argtypes = [ci]
         L.rnafold_env_config.argtypes = [ci, ci, ci, u64]
+        L.rnafold_env_config_reward.argtypes = [ci, ci]
         L.rnafold_env_set_targets.argtypes = [ci, vp, vp, ci]
         L.rnafold_env_reset.argtypes = [ci, vp]
         L.rnafold_env_step.argtypes = [ci, vp, cd, vp, vp, vp]
@@ -137,6 +139,13 @@ def last_launch_info():
     routed = (ctypes.c_int32 * 3)()
     check(L.rnafold_last_launch_info(ctypes.byref(n), routed))
     return n.value, list(routed)
+
+
+def last_status(clear=True):
+    """Wait for the last (asynchronous) fold call; raises RnaFoldError if a kernel reported a failure."""
+    v = ctypes.c_int32(0)
+    check(lib().rnafold_last_status(ctypes.byref(v), 1 if clear else 0))
+    return v.value
 
 
 def set_timing(enabled):

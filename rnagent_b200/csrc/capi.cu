@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <numeric>
 #include <string>
@@ -90,12 +91,19 @@ struct Context {
   int max_smem_optin = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // ev_done: end of the last fold call's device work (the next call, on whatever stream, waits for it before it
+  // touches the shared scratch); ev_staged: the last call's H2D copies out of the pinned staging blocks
+  cudaEvent_t ev_done = nullptr, ev_staged = nullptr;
+  bool have_done = false, have_staged = false;
+  int32_t *d_status = nullptr;   // sticky: set by a kernel whose backtrack found no decomposition
+  uint64_t params_epoch = 0;     // bumped by every parameter upload (device-routed plans are rebuilt)
+  std::map<uint64_t, int> occ_cache;
   HostParams hp;
   FoldParams *d_params = nullptr;
   // model details (RNA.cvar)
   double md_temperature = 37.0, md_dangles = 2, md_noGU = 0, md_no_closingGU = 0, md_uniq_ML = 0;
   // device staging for host-side callers
-  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws, d_redo;
+  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws, d_redo, d_dyn;
   PinBuf h_in, h_out, h_off;
   std::vector<int32_t> off_host, order_host;
   int32_t last_launches = 0, last_routed[3] = {0, 0, 0};
@@ -127,9 +135,11 @@ bool is_pinned_host_ptr(const void *p) {
 }
 
 int upload_params(Context *c) {
+  CUDA_TRY(cudaDeviceSynchronize());  // folds in flight on any stream still read the live tables
   CUDA_TRY(cudaMemcpyAsync(c->d_params, &c->hp.dev, sizeof(FoldParams), cudaMemcpyHostToDevice, c->stream));
   CUDA_TRY(wave_upload_constants(c->hp, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
+  c->params_epoch++;
   return RNAFOLD_OK;
 }
 
@@ -143,17 +153,133 @@ void init_host_params(HostParams *hp) {
 // so mixed batches are split into classes.  Sequences that fit the fast wavefront kernel (int16
 // tables in shared memory) go there; longer ones use the int32 CTA kernel with global tables.
 const int kWaveClasses[] = {32, 48, 64, 80, 100, 128, 160, 200, 256};
+const int kNumWaveClasses = (int)(sizeof(kWaveClasses) / sizeof(int));
 const int kLegacySmemLimit = 232;
 
 const int kClusterClasses[] = {288, 320, 352, 400, 432, 464};
+const int kNumClusterClasses = (int)(sizeof(kClusterClasses) / sizeof(int));
 const size_t kClusterWorkspaceCap = (size_t)24 << 30;  // bytes of global tables per cluster launch
 
 enum { kKindWave = 0, kKindLegacySmem = 1, kKindLegacyGlobal = 2, kKindCluster = 3 };
 struct Launch {
-  int begin, end;  // slice of the length-sorted order
+  int begin, end;  // slice of the length-sorted order (host-planned path); end - begin = upper bound otherwise
   int nmax;
   int kind;
+  bool wide;       // wave kernel: latency-bound launch (fewer sequences than SMs) -> 512-thread CTAs
 };
+
+// what the live parameter set and the device allow
+struct Limits {
+  int wave_esz;       // int16 tables unless the parameter set's terms are too large
+  int wave_limit;     // longest sequence of the single-CTA wavefront kernel
+  int cluster_limit;  // longest sequence of the 2-CTA cluster kernel (= wave_limit when unavailable)
+};
+Limits make_limits(Context *c) {
+  Limits m;
+  m.wave_esz = wave_int16_ok(c->hp) ? 2 : 4;
+  m.wave_limit = 0;
+  for (int k = 0; k < kNumWaveClasses; ++k)
+    if (wave_smem_bytes(kWaveClasses[k], m.wave_esz) + 1024 <= (size_t)c->max_smem_optin) m.wave_limit = kWaveClasses[k];
+  m.cluster_limit = m.wave_limit;
+  if (m.wave_esz == 2)
+    for (int q = 0; q < kNumClusterClasses; ++q)
+      if (cluster_smem_bytes(kClusterClasses[q], 2) + 1024 <= (size_t)c->max_smem_optin) m.cluster_limit = kClusterClasses[q];
+  return m;
+}
+
+// occupancy queries are CUDA API calls: cached per (kernel family, length class, element size, threads)
+int cached_occ(Context *c, int family, int nmax, int esz, int threads) {
+  const uint64_t key = ((uint64_t)family << 48) | ((uint64_t)nmax << 24) | ((uint64_t)esz << 16) | (uint64_t)threads;
+  auto it = c->occ_cache.find(key);
+  if (it != c->occ_cache.end()) return it->second;
+  int v = 0;
+  if (family == 0) v = wave_occupancy(nmax, esz, threads);
+  else if (family == 1) v = cluster_max_active(nmax);
+  else v = cta_kernel_occupancy(nmax, esz != 0);
+  c->occ_cache[key] = v;
+  return v;
+}
+
+// Issue the kernels of one launch record.  `count` is the number of sequences of the launch when the host knows
+// it, otherwise (a.dyn != nullptr: the count lives on the device) an upper bound that sizes grids and workspaces.
+// q: two queue counters (main kernel, range-check re-run).
+int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, BatchArgs a, int32_t *q, cudaStream_t st) {
+  auto legacy = [&](BatchArgs la, bool smem_tables, int32_t *queue) -> int {
+    const int occ = std::max(1, cached_occ(c, 2, L.nmax, smem_tables ? 1 : 0, kCtaThreads));
+    const int grid = std::min(count, c->num_sms * occ);
+    int *ws = nullptr;
+    long long stride = 0;
+    if (!smem_tables) {
+      stride = 2LL * table_cells(L.nmax);
+      CUDA_TRY(c->d_ws.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
+      ws = (int *)c->d_ws.p;
+    }
+    CUDA_TRY(launch_fold_cta(c->d_params, la, L.nmax, smem_tables, grid, ws, stride, queue, st));
+    c->last_launches++;
+    return RNAFOLD_OK;
+  };
+  a.redo_filter = 0;
+  if (L.kind == kKindWave) {
+    // A launch that cannot even fill the SMs is latency-bound per fold: give each sequence a wider CTA
+    // (the per-diagonal items spread over more warps).  RNAFOLD_SMALL_THREADS overrides for experiments.
+    int threads = wave_threads(L.nmax);
+    if (L.wide) {
+      static const int forced = getenv("RNAFOLD_SMALL_THREADS") ? atoi(getenv("RNAFOLD_SMALL_THREADS")) : 512;
+      if (forced == 256 || forced == 512) threads = std::max(threads, forced);
+    }
+    const int occ = std::max(1, cached_occ(c, 0, L.nmax, lim.wave_esz, threads));
+    const int grid = std::min(count, c->num_sms * occ);
+    CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, lim.wave_esz, grid, threads, q, st));
+    c->last_launches++;
+    c->last_routed[0] += count;
+    if (lim.wave_esz == 2) {
+      // sequences whose values left the int16 range (flagged on the device) are re-run in int32
+      a.redo_filter = 1;
+      return legacy(a, L.nmax <= kLegacySmemLimit, q + 1);
+    }
+  } else if (L.kind == kKindCluster) {
+    const size_t stride = cluster_table_stride(L.nmax);
+    CUDA_TRY(c->d_ws.reserve(2 * stride * sizeof(int16_t) * (size_t)count));
+    int16_t *cbg = (int16_t *)c->d_ws.p, *fg = cbg + stride * (size_t)count;
+    const int ncl = std::max(1, std::min(count, cached_occ(c, 1, L.nmax, 2, 0)));
+    CUDA_TRY(launch_fold_cluster(c->d_params, a, L.nmax, ncl, q, cbg, fg, st));
+    CUDA_TRY(launch_f5_backtrack(c->d_params, a, L.nmax, count, cbg, fg, st));
+    c->last_launches += 2;
+    c->last_routed[1] += count;
+    a.redo_filter = 1;  // int16 range violations -> int32 kernel with global tables
+    return legacy(a, false, q + 1);
+  } else {
+    int rc = legacy(a, L.kind == kKindLegacySmem, q);
+    if (rc) return rc;
+    c->last_routed[L.kind == kKindLegacySmem ? 0 : 2] += count;
+  }
+  return RNAFOLD_OK;
+}
+
+// Calls may arrive on different streams while sharing the context's scratch (order, queue counters, redo flags,
+// workspace): every call first waits, on its stream, for the previous call's device work.
+int enter_call(Context *c, cudaStream_t st) {
+  if (c->have_done) CUDA_TRY(cudaStreamWaitEvent(st, c->ev_done, 0));
+  return RNAFOLD_OK;
+}
+int leave_call(Context *c, cudaStream_t st) {
+  CUDA_TRY(cudaEventRecord(c->ev_done, st));
+  c->have_done = true;
+  return RNAFOLD_OK;
+}
+// the pinned staging blocks are rewritten by the host: the previous call's H2D copies out of them must be over
+int staging_ready(Context *c) {
+  if (c->have_staged) CUDA_TRY(cudaEventSynchronize(c->ev_staged));
+  c->have_staged = false;
+  return RNAFOLD_OK;
+}
+
+// sticky device status word -> error (and clear); the stream must have been synchronised past the D2H of `status`
+int status_result(Context *c, int32_t status, cudaStream_t st) {
+  if (!status) return RNAFOLD_OK;
+  cudaMemsetAsync(c->d_status, 0, sizeof(int32_t), st);
+  return fail(RNAFOLD_ECUDA, "backtrack found no decomposition (code %d)", status);
+}
 
 int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target,
               uint8_t *db_out, int32_t *mfe_out, int32_t *hd_out, double *reward_out,
@@ -171,6 +297,10 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
                             (hd_out && !is_device_ptr(hd_out)) || (reward_out && !is_device_ptr(reward_out)) ||
                             (mismatch_out && !is_device_ptr(mismatch_out));
   cudaStream_t st = stream_v ? (cudaStream_t)stream_v : c->stream;
+  {
+    int rc = enter_call(c, st);
+    if (rc) return rc;
+  }
 
   // offsets on the host (needed for routing)
   c->off_host.resize((size_t)B + 1);
@@ -198,50 +328,46 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   auto len_at = [&](int k) { return oh[c->order_host[k] + 1] - oh[c->order_host[k]]; };
 
   // split into launches
-  const int wave_esz = wave_int16_ok(c->hp) ? 2 : 4;  // int16 tables unless the parameter set's terms are too large
+  const Limits lim = make_limits(c);
   std::vector<Launch> launches;
   {
-    const int ncls = (int)(sizeof(kWaveClasses) / sizeof(int));
-    int wave_limit = 0;
-    for (int k = 0; k < ncls; ++k)
-      if (wave_smem_bytes(kWaveClasses[k], wave_esz) + 1024 <= (size_t)c->max_smem_optin) wave_limit = kWaveClasses[k];
+    const int wave_limit = lim.wave_limit, cluster_limit = lim.cluster_limit;
     // longest first: beyond every shared-memory design -> int32 CTA kernel with global tables
-    const int nccls = (int)(sizeof(kClusterClasses) / sizeof(int));
-    int cluster_limit = wave_limit;
-    if (wave_esz == 2)
-      for (int q = 0; q < nccls; ++q)
-        if (cluster_smem_bytes(kClusterClasses[q], 2) + 1024 <= (size_t)c->max_smem_optin) cluster_limit = kClusterClasses[q];
     int k = 0;
     while (k < B && len_at(k) > cluster_limit) ++k;
-    if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal});
+    if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal, false});
     // 2-CTA cluster kernel (tables split over DSMEM) for lengths above the single-CTA kernel's reach
-    for (int q = nccls - 1; q >= 0 && k < B; --q) {
+    for (int q = kNumClusterClasses - 1; q >= 0 && k < B; --q) {
       if (kClusterClasses[q] > cluster_limit) continue;
       const int lo = q > 0 ? std::max(kClusterClasses[q - 1], wave_limit) : wave_limit;
       int e = k;
       while (e < B && len_at(e) > lo) ++e;
       const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q]) * sizeof(int16_t);
       const int chunk = (int)std::max<size_t>(1, kClusterWorkspaceCap / per_seq);
-      for (int s0 = k; s0 < e; s0 += chunk) launches.push_back(Launch{s0, std::min(e, s0 + chunk), kClusterClasses[q], kKindCluster});
+      for (int s0 = k; s0 < e; s0 += chunk) launches.push_back(Launch{s0, std::min(e, s0 + chunk), kClusterClasses[q], kKindCluster, false});
       k = e;
     }
     if (k < B && B - k <= c->num_sms && !getenv("RNAFOLD_NO_MERGE")) {
       // fewer sequences than SMs: one launch of the longest sequence's class (every CTA has an SM to itself,
       // so the step costs one fold latency instead of one per length class)
-      launches.push_back(Launch{k, B, std::max(len_at(k), 8), kKindWave});
+      launches.push_back(Launch{k, B, std::max(len_at(k), 8), kKindWave, true});
       k = B;
     }
-    for (int cls = ncls - 1; cls >= 0 && k < B; --cls) {
+    for (int cls = kNumWaveClasses - 1; cls >= 0 && k < B; --cls) {
       if (kWaveClasses[cls] > wave_limit) continue;
       const int lo = cls > 0 ? kWaveClasses[cls - 1] : -1;
       int e = k;
       while (e < B && len_at(e) > lo) ++e;
-      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), kKindWave});
+      if (e > k) launches.push_back(Launch{k, e, std::max(len_at(k), 8), kKindWave, e - k <= c->num_sms});
       k = e;
     }
   }
 
   // ---- device views of the inputs
+  {
+    int rc = staging_ready(c);
+    if (rc) return rc;
+  }
   const uint8_t *d_seq = seq;
   const int32_t *d_off = off;
   const uint8_t *d_target = target;
@@ -278,6 +404,8 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     CUDA_TRY(cudaMemcpyAsync(c->d_order.p, ho, sizeof(int32_t) * (2 * (size_t)B + 1), cudaMemcpyHostToDevice, st));
     if (!off_dev) d_off = (const int32_t *)c->d_order.p;
   }
+  CUDA_TRY(cudaEventRecord(c->ev_staged, st));
+  c->have_staged = true;
   const int32_t *d_order = (const int32_t *)c->d_order.p + B + 1;
 
   // ---- device views of the outputs
@@ -301,40 +429,22 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   CUDA_TRY(out_view(target ? reward_out : nullptr, c->d_reward, sizeof(double) * (size_t)B, &v_rw));
   CUDA_TRY(out_view(target ? mismatch_out : nullptr, c->d_mismatch, total + 16, &v_mm));
 
-  // ---- control words: two queue counters per launch (+ range-check re-run) + status; redo flags
+  // ---- control words: two queue counters per launch (+ range-check re-run); redo flags
   const int nl = (int)launches.size();
-  const int nctl = 2 * nl + 1;
-  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)nctl));
-  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)nctl, st));
+  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(2 * nl)));
+  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)(2 * nl), st));
   int32_t *d_ctl = (int32_t *)c->d_ctl.p;
   CUDA_TRY(c->d_redo.reserve(sizeof(int32_t) * (size_t)B));
   CUDA_TRY(cudaMemsetAsync(c->d_redo.p, 0, sizeof(int32_t) * (size_t)B, st));
 
-  auto legacy = [&](const Launch &L, BatchArgs a, bool smem_tables, int32_t *queue) -> int {
-    const int count = L.end - L.begin;
-    const int occ = std::max(1, cta_kernel_occupancy(L.nmax, smem_tables));
-    const int grid = std::min(count, c->num_sms * occ);
-    int *ws = nullptr;
-    long long stride = 0;
-    if (!smem_tables) {
-      stride = 2LL * table_cells(L.nmax);
-      CUDA_TRY(c->d_ws.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
-      ws = (int *)c->d_ws.p;
-    }
-    CUDA_TRY(launch_fold_cta(c->d_params, a, L.nmax, smem_tables, grid, ws, stride, queue, st));
-    c->last_launches++;
-    return RNAFOLD_OK;
-  };
-
   if (c->timed) CUDA_TRY(cudaEventRecord(c->ev0, st));
   for (int li = 0; li < nl; ++li) {
     const Launch &L = launches[li];
-    const int count = L.end - L.begin;
     BatchArgs a;
     a.seq = d_seq;
     a.off = d_off;
     a.order = d_order + L.begin;
-    a.B = count;
+    a.B = L.end - L.begin;
     a.target = d_target;
     a.db = (uint8_t *)v_db;
     a.mfe = (int32_t *)v_mfe;
@@ -342,45 +452,12 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     a.reward = (double *)v_rw;
     a.mismatch = (uint8_t *)v_mm;
     a.reward_exp = reward_exp;
-    a.status = d_ctl + 2 * nl;
+    a.status = c->d_status;
     a.redo = (int32_t *)c->d_redo.p;
     a.redo_filter = 0;
-    if (L.kind == kKindWave) {
-      // A launch that cannot even fill the SMs is latency-bound per fold: give each sequence a wider CTA
-      // (the per-diagonal items spread over more warps).  RNAFOLD_SMALL_THREADS overrides for experiments.
-      int threads = wave_threads(L.nmax);
-      if (count <= c->num_sms) {
-        static const int forced = getenv("RNAFOLD_SMALL_THREADS") ? atoi(getenv("RNAFOLD_SMALL_THREADS")) : 512;
-        if (forced == 256 || forced == 512) threads = std::max(threads, forced);
-      }
-      const int occ = std::max(1, wave_occupancy(L.nmax, wave_esz, threads));
-      const int grid = std::min(count, c->num_sms * occ);
-      CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, wave_esz, grid, threads, d_ctl + 2 * li, st));
-      c->last_launches++;
-      c->last_routed[0] += count;
-      if (wave_esz == 2) {
-        // sequences whose values left the int16 range (flagged on the device) are re-run in int32
-        a.redo_filter = 1;
-        int rc = legacy(L, a, L.nmax <= kLegacySmemLimit, d_ctl + 2 * li + 1);
-        if (rc) return rc;
-      }
-    } else if (L.kind == kKindCluster) {
-      const size_t stride = cluster_table_stride(L.nmax);
-      CUDA_TRY(c->d_ws.reserve(2 * stride * sizeof(int16_t) * (size_t)count));
-      int16_t *cbg = (int16_t *)c->d_ws.p, *fg = cbg + stride * (size_t)count;
-      const int ncl = std::max(1, std::min(count, cluster_max_active(L.nmax)));
-      CUDA_TRY(launch_fold_cluster(c->d_params, a, L.nmax, ncl, d_ctl + 2 * li, cbg, fg, st));
-      CUDA_TRY(launch_f5_backtrack(c->d_params, a, L.nmax, cbg, fg, st));
-      c->last_launches += 2;
-      c->last_routed[1] += count;
-      a.redo_filter = 1;  // int16 range violations -> int32 kernel with global tables
-      int rc = legacy(L, a, false, d_ctl + 2 * li + 1);
-      if (rc) return rc;
-    } else {
-      int rc = legacy(L, a, L.kind == kKindLegacySmem, d_ctl + 2 * li);
-      if (rc) return rc;
-      c->last_routed[L.kind == kKindLegacySmem ? 0 : 2] += count;
-    }
+    a.dyn = nullptr;
+    int rc = issue_launch(c, lim, L, a.B, a, d_ctl + 2 * li, st);
+    if (rc) return rc;
   }
   if (c->timed) CUDA_TRY(cudaEventRecord(c->ev1, st));
 
@@ -410,7 +487,11 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     CUDA_TRY(back(target ? reward_out : nullptr, v_rw, o_rw, 8 * (size_t)B));
     CUDA_TRY(back(target ? mismatch_out : nullptr, v_mm, o_mm, total));
     int32_t status = 0;
-    CUDA_TRY(cudaMemcpyAsync(&status, d_ctl + 2 * nl, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&status, c->d_status, 4, cudaMemcpyDeviceToHost, st));
+    {
+      int rc = leave_call(c, st);
+      if (rc) return rc;
+    }
     CUDA_TRY(cudaStreamSynchronize(st));
     auto fin = [&](void *user, size_t off_b, size_t bytes) {
       if (user && !is_device_ptr(user) && !is_pinned_host_ptr(user) && bytes) std::memcpy(user, ho + off_b, bytes);
@@ -420,11 +501,142 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     fin(target ? hd_out : nullptr, o_hd, 4 * (size_t)B);
     fin(target ? reward_out : nullptr, o_rw, 8 * (size_t)B);
     fin(target ? mismatch_out : nullptr, o_mm, total);
-    if (status) return fail(RNAFOLD_ECUDA, "backtrack found no decomposition (code %d)", status);
-  } else if ((!seq_dev || (target && !tgt_dev) || !off_dev) && !defer_sync) {
-    // pinned staging buffers are reused by the next call
+    return status_result(c, status, st);
+  }
+  {
+    int rc = leave_call(c, st);
+    if (rc) return rc;
+  }
+  if ((!seq_dev || (target && !tgt_dev)) && !defer_sync) {
+    // host inputs are consumed when the call returns (a caller may rewrite them at once)
     CUDA_TRY(cudaStreamSynchronize(st));
   }
+  return RNAFOLD_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Device-routed batches: the batch (CSR on the device) and its SIZE are produced by a kernel and never cross to
+// the host.  The host only knows which lengths can occur (the environment's target lengths) and an upper bound
+// of the count: it enqueues one routing kernel that bins the sequences by length class, then one launch per class
+// that can occur; every kernel reads its own count from device memory and CTAs without work exit.
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxDynLaunches = 24;
+struct RouteTable {
+  int nl;                         // launches
+  int merged;                     // index of the latency launch that takes a batch of <= num_sms sequences whole, or -1
+  int num_sms;
+  int first_class;                // first class launch (the classes follow in ASCENDING order of `upper`)
+  int upper[kMaxDynLaunches];     // class launches: longest sequence routed to launch k
+};
+
+__global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__ count_ptr, const int32_t *__restrict__ total_ptr,
+                                                     int32_t *off, int cap, RouteTable rt, int32_t *__restrict__ order,
+                                                     int32_t *__restrict__ dyn) {
+  __shared__ int cnt[kMaxDynLaunches], beg[kMaxDynLaunches], fill[kMaxDynLaunches];
+  const int tid = threadIdx.x;
+  const int count = min(max(*count_ptr, 0), cap);
+  const int total = total_ptr ? *total_ptr : 0;
+  if (tid < kMaxDynLaunches) cnt[tid] = fill[tid] = 0;
+  __syncthreads();
+  const bool merge = rt.merged >= 0 && count <= rt.num_sms;
+  auto cls_of = [&](int s) -> int {
+    const int n = ((s + 1 == count && total_ptr) ? total : off[s + 1]) - off[s];
+    int k = rt.first_class;
+    while (k + 1 < rt.nl && n > rt.upper[k]) ++k;
+    return k;
+  };
+  if (merge) {
+    for (int s = tid; s < count; s += blockDim.x) order[s] = s;
+    if (tid < rt.nl) {
+      dyn[2 * tid] = tid == rt.merged ? count : 0;
+      dyn[2 * tid + 1] = 0;
+    }
+  } else {
+    for (int s = tid; s < count; s += blockDim.x) atomicAdd(&cnt[cls_of(s)], 1);
+    __syncthreads();
+    if (tid == 0) {
+      int o = 0;
+      for (int k = 0; k < rt.nl; ++k) {
+        beg[k] = o;
+        o += cnt[k];
+        dyn[2 * k] = cnt[k];
+        dyn[2 * k + 1] = beg[k];
+      }
+    }
+    __syncthreads();
+    for (int s = tid; s < count; s += blockDim.x) {
+      const int k = cls_of(s);
+      order[beg[k] + atomicAdd(&fill[k], 1)] = s;
+    }
+  }
+  __syncthreads();
+  if (tid == 0 && total_ptr) off[count] = total;  // closes the CSR (the producers wrote off[0..count-1])
+}
+
+struct DynPlanImpl {
+  uint64_t epoch = ~0ull;
+  int cap = 0;
+  Limits lim;
+  std::vector<Launch> launches;
+  RouteTable rt;
+};
+
+int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen, int cap) {
+  p->lim = make_limits(c);
+  p->cap = cap;
+  p->launches.clear();
+  const Limits &lim = p->lim;
+  int lmax = 0;
+  for (int k = 0; k < nlen; ++k) lmax = std::max(lmax, lengths[k]);
+  auto any_in = [&](int lo, int hi) {  // a possible length in (lo, hi]
+    for (int k = 0; k < nlen; ++k)
+      if (lengths[k] > lo && lengths[k] <= hi) return true;
+    return false;
+  };
+  auto top_in = [&](int lo, int hi) {
+    int top = 8;
+    for (int k = 0; k < nlen; ++k)
+      if (lengths[k] > lo && lengths[k] <= hi) top = std::max(top, lengths[k]);
+    return top;
+  };
+  RouteTable &rt = p->rt;
+  std::memset(&rt, 0, sizeof(rt));
+  rt.merged = -1;
+  rt.num_sms = c->num_sms;
+  // the latency launch: everything in one wide-CTA launch of the longest possible class
+  if (lmax <= lim.wave_limit) {
+    rt.merged = 0;
+    p->launches.push_back(Launch{0, std::min(cap, c->num_sms), std::max(lmax, 8), kKindWave, true});
+  }
+  rt.first_class = (int)p->launches.size();
+  // class launches in ascending order of their upper bound (the routing kernel walks them upwards)
+  int lo = -1;
+  for (int cls = 0; cls < kNumWaveClasses; ++cls) {
+    if (kWaveClasses[cls] > lim.wave_limit) break;
+    if (any_in(lo, kWaveClasses[cls]) && (int)p->launches.size() < kMaxDynLaunches) {
+      p->launches.push_back(Launch{0, cap, top_in(lo, kWaveClasses[cls]), kKindWave, false});
+      rt.upper[p->launches.size() - 1] = kWaveClasses[cls];
+    }
+    lo = kWaveClasses[cls];
+  }
+  lo = lim.wave_limit;
+  for (int q = 0; q < kNumClusterClasses; ++q) {
+    if (kClusterClasses[q] > lim.cluster_limit || kClusterClasses[q] <= lim.wave_limit) continue;
+    if (any_in(lo, kClusterClasses[q]) && (int)p->launches.size() < kMaxDynLaunches) {
+      const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q]) * sizeof(int16_t);
+      if (per_seq * (size_t)cap > kClusterWorkspaceCap) return fail(RNAFOLD_EINVAL, "device-routed batch too large for the cluster workspace");
+      p->launches.push_back(Launch{0, cap, kClusterClasses[q], kKindCluster, false});
+      rt.upper[p->launches.size() - 1] = kClusterClasses[q];
+    }
+    lo = kClusterClasses[q];
+  }
+  if (lmax > lim.cluster_limit && (int)p->launches.size() < kMaxDynLaunches) {
+    p->launches.push_back(Launch{0, cap, lmax, lmax <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal, false});
+    rt.upper[p->launches.size() - 1] = RNAFOLD_MAX_LEN;
+  }
+  rt.nl = (int)p->launches.size();
+  if (rt.nl == 0 || rt.nl > kMaxDynLaunches) return fail(RNAFOLD_EINVAL, "bad length classes for a device-routed batch");
+  p->epoch = c->params_epoch;
   return RNAFOLD_OK;
 }
 
@@ -440,6 +652,66 @@ int fold_hamming_batch_enqueue(const uint8_t *seq, const int32_t *off, int32_t B
   if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
   return run_batch(g_ctx, seq, off, B, target, db_out, mfe_out, hd_out, reward_out, nullptr, reward_exp, stream, true);
 }
+
+// env.cu: the same for a batch whose size lives on the device (no host round trip at all).  `lengths` lists the
+// sequence lengths that can occur, `cap` bounds the count; off[0..count-1] are filled by the producer and
+// off[count] = *total_ptr is written here.  *plan caches the launch list between calls.
+int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int cap, const uint8_t *seq, int32_t *off,
+                             const int32_t *count_ptr, const int32_t *total_ptr, const uint8_t *target, uint8_t *db_out,
+                             int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  Context *c = g_ctx;
+  if (!c) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (!plan || !lengths || nlen <= 0 || cap <= 0 || !seq || !off || !count_ptr) return fail(RNAFOLD_EINVAL, "bad arguments");
+  DynPlanImpl *p = (DynPlanImpl *)*plan;
+  if (!p) *plan = p = new DynPlanImpl();
+  if (p->epoch != c->params_epoch || p->cap != cap) {
+    int rc = build_dyn_plan(c, p, lengths, nlen, cap);
+    if (rc) return rc;
+  }
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+  c->last_launches = 0;
+  c->last_routed[0] = c->last_routed[1] = c->last_routed[2] = 0;
+  int rc = enter_call(c, st);
+  if (rc) return rc;
+  const int nl = p->rt.nl;
+  CUDA_TRY(c->d_order.reserve(sizeof(int32_t) * (2 * (size_t)cap + 2)));
+  CUDA_TRY(c->d_dyn.reserve(sizeof(int32_t) * 2 * kMaxDynLaunches));
+  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(2 * nl)));
+  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)(2 * nl), st));
+  CUDA_TRY(c->d_redo.reserve(sizeof(int32_t) * (size_t)cap));
+  CUDA_TRY(cudaMemsetAsync(c->d_redo.p, 0, sizeof(int32_t) * (size_t)cap, st));
+  route_kernel<<<1, 1024, 0, st>>>(count_ptr, total_ptr, off, cap, p->rt, (int32_t *)c->d_order.p, (int32_t *)c->d_dyn.p);
+  CUDA_TRY(cudaGetLastError());
+  c->last_launches++;
+  for (int li = 0; li < nl; ++li) {
+    const Launch &L = p->launches[li];
+    BatchArgs a;
+    a.seq = seq;
+    a.off = off;
+    a.order = (const int32_t *)c->d_order.p;
+    a.B = 0;
+    a.target = target;
+    a.db = db_out;
+    a.mfe = mfe_out;
+    a.hd = target ? hd_out : nullptr;
+    a.reward = target ? reward_out : nullptr;
+    a.mismatch = nullptr;
+    a.reward_exp = reward_exp;
+    a.status = c->d_status;
+    a.redo = (int32_t *)c->d_redo.p;
+    a.redo_filter = 0;
+    a.dyn = (const int32_t *)c->d_dyn.p + 2 * li;
+    rc = issue_launch(c, p->lim, L, L.end - L.begin, a, (int32_t *)c->d_ctl.p + 2 * li, st);
+    if (rc) return rc;
+  }
+  return leave_call(c, st);
+}
+void fold_dyn_plan_free(void *plan) { delete (DynPlanImpl *)plan; }
+
+// device address of the sticky status word (env.cu reads it with its end-of-step copies)
+const int32_t *status_word() { return g_ctx ? g_ctx->d_status : nullptr; }
+
 // error channel shared with env.cu
 int set_error(int code, const char *msg) {
   g_err = msg ? msg : "";
@@ -477,6 +749,10 @@ int rnafold_init(int device) {
   CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreate(&c->ev0));
   CUDA_TRY(cudaEventCreate(&c->ev1));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_staged, cudaEventDisableTiming));
+  CUDA_TRY(cudaMalloc((void **)&c->d_status, sizeof(int32_t)));
+  CUDA_TRY(cudaMemset(c->d_status, 0, sizeof(int32_t)));
   CUDA_TRY(cudaMalloc((void **)&c->d_params, sizeof(FoldParams)));
   init_host_params(&c->hp);
   char err[256] = "";
@@ -500,12 +776,15 @@ void rnafold_shutdown(void) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   for (DevBuf *b : {&c->d_seq, &c->d_off, &c->d_order, &c->d_target, &c->d_db, &c->d_mfe, &c->d_hd,
-                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws, &c->d_redo})
+                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws, &c->d_redo, &c->d_dyn})
     b->release();
   for (PinBuf *b : {&c->h_in, &c->h_out, &c->h_off}) b->release();
   cudaFree(c->d_params);
+  cudaFree(c->d_status);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
+  cudaEventDestroy(c->ev_done);
+  cudaEventDestroy(c->ev_staged);
   cudaStreamDestroy(c->stream);
   delete c;
   g_ctx = nullptr;
@@ -622,6 +901,20 @@ int rnafold_fold_batch(const uint8_t *seq, const int32_t *off, int32_t B, uint8_
   std::lock_guard<std::mutex> lk(g_mu);
   if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
   return run_batch(g_ctx, seq, off, B, nullptr, db_out, mfe_dcal_out, nullptr, nullptr, nullptr, 1.0, stream);
+}
+
+int rnafold_last_status(int32_t *status, int32_t clear) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  Context *c = g_ctx;
+  CUDA_TRY(cudaSetDevice(c->device));
+  if (c->have_done) CUDA_TRY(cudaEventSynchronize(c->ev_done));
+  int32_t v = 0;
+  CUDA_TRY(cudaMemcpy(&v, c->d_status, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (v && clear) CUDA_TRY(cudaMemset(c->d_status, 0, sizeof(int32_t)));
+  if (status) *status = v;
+  if (v) return fail(RNAFOLD_ECUDA, "backtrack found no decomposition (code %d)", v);
+  return RNAFOLD_OK;
 }
 
 int rnafold_last_launch_info(int32_t *launches, int32_t routed[3]) {

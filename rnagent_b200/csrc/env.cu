@@ -8,12 +8,12 @@
 // auto-reset of the reference's VecEnv), and one kernel emits the [N, 10, 2k] observation windows.
 // Nothing here runs on the CPU except target parsing (once per data set) and launch bookkeeping.
 #include <cuda_runtime.h>
-#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <stdint.h>
 
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -41,6 +41,7 @@ constexpr int kRows = 10;  // 6 structure-motif rows (O C I H M E) + 4 nucleotid
 struct Env {
   int n_envs = 0, k = 25, n_targets = 0, lmax = 0;
   bool auto_reset = true, randomize = false;
+  bool gc_penalty = false;  // reward shaping of solution.py:150-151 (config keys gc_penalty / gc)
   uint64_t seed = 0;
   // Solution.permute at the terminal evaluation (RLIFenv.py:13,69-73)
   bool permute = false;
@@ -60,7 +61,10 @@ struct Env {
   int32_t *d_list = nullptr, *d_off = nullptr, *d_hd = nullptr, *d_mfe = nullptr;
   uint8_t *d_bseq = nullptr, *d_btgt = nullptr, *d_bdb = nullptr;
   double *d_brw = nullptr;
-  int32_t *h_off = nullptr;  // pinned: [0] = total length, [1] = count, [2..] offsets
+  int32_t *h_off = nullptr;  // pinned: [0] = total length, [1] = count, [2..] offsets (host-routed path: local search)
+  int32_t *h_status = nullptr;  // pinned: the library's sticky status word, read with the end-of-step copies
+  std::vector<int32_t> lens;    // distinct target lengths (what the device-routed fold must be prepared for)
+  void *plan = nullptr;         // launch list of the device-routed fold (capi.cu)
   // statistics: episodes, solved, sum_hd, steps (int64) ; sum_reward, sum_mfe_kcal (double)
   unsigned long long *d_istat = nullptr;
   double *d_fstat = nullptr;
@@ -124,24 +128,25 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
 
 // (re)arm environments: next target (round-robin per env, or hashed random), empty sequence
 __global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int randomize, unsigned long long seed,
-                                 const int32_t *__restrict__ list, int32_t *cur, int32_t *idx, int32_t *ep,
-                                 uint8_t *seq, uint8_t *mask) {
-  // list: the finished environments of this step (one block each); nullptr: every environment
-  const int e = list ? list[blockIdx.x] : (int)blockIdx.x;
-  if (e >= n_envs) return;
-  if (threadIdx.x == 0) {
-    const int epn = ep[e] + 1;
-    int t;
-    if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
-    else t = (cur[e] + 1) % n_targets;
-    cur[e] = t;
-    idx[e] = 0;
-    ep[e] = epn;
-  }
-  __syncthreads();
-  for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
-    seq[(size_t)e * lmax + q] = '-';
-    mask[(size_t)e * lmax + q] = 0;
+                                 const int32_t *__restrict__ list, const int32_t *__restrict__ count_ptr, int32_t *cur,
+                                 int32_t *idx, int32_t *ep, uint8_t *seq, uint8_t *mask) {
+  // list: the finished environments of this step (their number lives on the device); nullptr: every environment
+  const int count = list ? min(*count_ptr, n_envs) : n_envs;
+  for (int s = blockIdx.x; s < count; s += gridDim.x) {
+    const int e = list ? list[s] : s;
+    if (threadIdx.x == 0) {
+      const int epn = ep[e] + 1;
+      int t;
+      if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
+      else t = (cur[e] + 1) % n_targets;
+      cur[e] = t;
+      idx[e] = 0;
+      ep[e] = epn;
+    }
+    for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
+      seq[(size_t)e * lmax + q] = '-';
+      mask[(size_t)e * lmax + q] = 0;
+    }
   }
 }
 
@@ -190,41 +195,62 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
 }
 
 // scatter fold results back to their environments and update the rollout statistics
-__global__ void env_scatter_kernel(int count, int lmax, const int32_t *__restrict__ list, const int32_t *__restrict__ off,
+__global__ void env_scatter_kernel(const int32_t *__restrict__ count_ptr, int n_envs, int lmax, const int32_t *__restrict__ list, const int32_t *__restrict__ off,
                                    const double *__restrict__ brw, const int32_t *__restrict__ bhd,
                                    const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb,
                                    const uint8_t *__restrict__ bseq, const int32_t *__restrict__ cur,
                                    const int32_t *__restrict__ toff, double *reward,
                                    uint8_t *last_db, uint8_t *last_seq, int32_t *last_hd, int32_t *last_mfe,
-                                   int32_t *last_t, unsigned long long *istat, double *fstat) {
-  const int s = blockIdx.x;
-  if (s >= count) return;
-  const int e = list[s];
-  const int o0 = off[s], len = toff[cur[e] + 1] - toff[cur[e]];
-  for (int q = threadIdx.x; q < len; q += blockDim.x) {
-    last_db[(size_t)e * lmax + q] = bdb[o0 + q];
-    last_seq[(size_t)e * lmax + q] = bseq[o0 + q];
-  }
-  if (threadIdx.x == 0) {
-    reward[e] = brw[s];
-    last_hd[e] = bhd[s];
-    last_mfe[e] = bmfe[s];
-    last_t[e] = cur[e];
-    atomicAdd(&istat[0], 1ull);
-    if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
-    atomicAdd(&istat[2], (unsigned long long)bhd[s]);
-    atomicAdd(&fstat[0], brw[s]);
-    atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
+                                   int32_t *last_t, unsigned long long *istat, double *fstat, int gc_penalty) {
+  __shared__ int n_u;
+  const int count = min(*count_ptr, n_envs);
+  for (int s = blockIdx.x; s < count; s += gridDim.x) {
+    const int e = list[s];
+    const int o0 = off[s], len = toff[cur[e] + 1] - toff[cur[e]];
+    if (gc_penalty) {
+      if (threadIdx.x == 0) n_u = 0;
+      __syncthreads();
+    }
+    int my_u = 0;
+    for (int q = threadIdx.x; q < len; q += blockDim.x) {
+      const uint8_t ch = bseq[o0 + q];
+      last_db[(size_t)e * lmax + q] = bdb[o0 + q];
+      last_seq[(size_t)e * lmax + q] = ch;
+      my_u += ch == 'U';
+    }
+    double rw = brw[s];
+    if (gc_penalty) {
+      if (my_u) atomicAdd(&n_u, my_u);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        // r * 0.85 + clip(gcau['U'], 0, .15); gcau['U'] accumulates one increment per U like gcau_content (solution.py:257-268)
+        const double inc = 1.0 / (double)len;
+        double u = 0.0;
+        for (int k = 0; k < n_u; ++k) u += inc;
+        rw = rw * 0.85 + fmin(fmax(u, 0.0), 0.15);
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      reward[e] = rw;
+      last_hd[e] = bhd[s];
+      last_mfe[e] = bmfe[s];
+      last_t[e] = cur[e];
+      atomicAdd(&istat[0], 1ull);
+      if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
+      atomicAdd(&istat[2], (unsigned long long)bhd[s]);
+      atomicAdd(&fstat[0], rw);
+      atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
+    }
   }
 }
 
 // observation window encoding[:, i:i+2k] of the zero-padded [10, len+2k] encoding (solution.py:62-75,116-123)
 __global__ void env_obs_kernel(int n_envs, int lmax, int k, const int32_t *__restrict__ cur, const int32_t *__restrict__ idx,
                                const int32_t *__restrict__ toff, const uint8_t *__restrict__ mot,
-                               const uint8_t *__restrict__ mask, uint8_t *obs, unsigned long long *packed) {
+                               const uint8_t *__restrict__ mask, uint8_t *obs) {
   const int e = blockIdx.x;
   if (e >= n_envs) return;
-  if (e == 0 && threadIdx.x == 0) *packed = 0ull;  // last kernel of every step: the next step's terminal batch starts empty
   const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
   const int w = 2 * k;
   auto cell = [&](int q) -> unsigned {
@@ -280,6 +306,8 @@ static void env_free(Env *e) {
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (e->h_off) cudaFreeHost(e->h_off);
+  if (e->h_status) cudaFreeHost(e->h_status);
+  if (e->plan) rnafold::fold_dyn_plan_free(e->plan);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
 }
@@ -315,6 +343,8 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_fstat, 2));
   ENV_TRY(dalloc(&e->d_obs, N * kRows * 2 * (size_t)kernel_size));
   ENV_TRY(cudaMallocHost((void **)&e->h_off, sizeof(int32_t) * (N + 4)));
+  ENV_TRY(cudaMallocHost((void **)&e->h_status, sizeof(int32_t)));
+  *e->h_status = 0;
   ENV_TRY(cudaMemset(e->d_istat, 0, 4 * sizeof(unsigned long long)));
   ENV_TRY(cudaMemset(e->d_fstat, 0, 2 * sizeof(double)));
   ENV_TRY(cudaMemset(e->d_cur, 0xff, N * sizeof(int32_t)));  // current_sequence = -1 (RLIFenv.py:25)
@@ -345,6 +375,14 @@ int rnafold_env_config(int32_t h, int32_t auto_reset, int32_t randomize, uint64_
   e->auto_reset = auto_reset != 0;
   e->randomize = randomize != 0;
   e->seed = seed;
+  return RNAFOLD_OK;
+}
+
+int rnafold_env_config_reward(int32_t h, int32_t gc_penalty) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  e->gc_penalty = gc_penalty != 0;
   return RNAFOLD_OK;
 }
 
@@ -413,8 +451,15 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
   e->lmax = lmax;
   ENV_TRY(cudaMemset(e->d_cur, 0xff, N * sizeof(int32_t)));
   ENV_TRY(cudaMemset(e->d_ep, 0xff, N * sizeof(int32_t)));  // the constructor's next_target_structure() is not an episode
+  e->lens.clear();
+  for (int t = 0; t < n_targets; ++t) {
+    const int32_t n = off[t + 1] - off[t];
+    if (std::find(e->lens.begin(), e->lens.end(), n) == e->lens.end()) e->lens.push_back(n);
+  }
+  if (e->plan) rnafold::fold_dyn_plan_free(e->plan);
+  e->plan = nullptr;
   env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
-                                                     e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
+                                                     nullptr, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
   ENV_TRY(cudaGetLastError());
   ENV_TRY(cudaStreamSynchronize(e->stream));
   return RNAFOLD_OK;
@@ -424,8 +469,7 @@ static int env_emit_obs(Env *e, uint8_t *obs_out) {
   // a device destination is written by the kernel itself (no 2 MB device-to-device copy per step)
   const bool direct = obs_out && env_is_device_ptr(obs_out);
   env_obs_kernel<<<e->n_envs, 128, 0, e->stream>>>(e->n_envs, e->lmax, e->k, e->d_cur, e->d_idx, e->d_toff, e->d_mot,
-                                                    e->d_mask, direct ? obs_out : e->d_obs,
-                                                    reinterpret_cast<unsigned long long *>(e->d_off));
+                                                    e->d_mask, direct ? obs_out : e->d_obs);
   ENV_TRY(cudaGetLastError());
   if (!direct) ENV_TRY(copy_out(obs_out, e->d_obs, (size_t)e->n_envs * kRows * 2 * e->k, e->stream));
   return RNAFOLD_OK;
@@ -438,7 +482,7 @@ int rnafold_env_reset(int32_t h, uint8_t *obs_out) {
   if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
   ENV_TRY(cudaSetDevice(rnafold_current_device()));
   env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
-                                                     e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
+                                                     nullptr, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
   ENV_TRY(cudaGetLastError());
   int rc = env_emit_obs(e, obs_out);
   if (rc) return rc;
@@ -446,16 +490,16 @@ int rnafold_env_reset(int32_t h, uint8_t *obs_out) {
   return RNAFOLD_OK;
 }
 
-// RnaDesign.step for every environment (RLIFenv.py:59-81) + the VecEnv auto-reset when enabled
-static double g_env_t[6];
-static long g_env_calls;
-static inline double env_now() {
-  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
-}
-
+// RnaDesign.step for every environment (RLIFenv.py:59-81) + the VecEnv auto-reset when enabled.
+//
+// The whole step is enqueued without a host round trip: the terminal environments compact themselves into a CSR
+// batch on the device, a routing kernel bins that batch by length class, the fold kernels read their counts from
+// device memory (CTAs without work exit), and scatter / reset / observation follow on the same stream.  The host
+// synchronises ONCE, at the end, and only when an output is a host buffer; with device outputs the call returns
+// as soon as the work is enqueued.  (The local search, permute=True, sizes its rounds on the host and keeps the
+// host-routed path.)
 int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8_t *obs_out, double *reward_out,
                      uint8_t *done_out) {
-  const double t_a = env_now();
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e || !e->n_targets || !actions) return set_error(RNAFOLD_EINVAL, "bad env handle, no targets set or null actions");
@@ -468,60 +512,66 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
     d_act = e->d_act;
   }
   // d_off: [0] total length, [1] count (one 64-bit word advanced atomically by the terminal environments), [2..] offsets
+  ENV_TRY(cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st));  // this step's terminal batch starts empty
   env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
                                                    e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
                                                    reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
                                                    e->d_bseq, e->d_btgt);
   ENV_TRY(cudaGetLastError());
-  const double t_b = env_now();
-  // the count and the first offsets travel together (1 KB): a second round trip only for large terminal batches
-  const int prefetch = N + 3 < 259 ? N + 3 : 259;
-  ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t) * (size_t)prefetch, cudaMemcpyDeviceToHost, st));
-  ENV_TRY(cudaStreamSynchronize(st));
-  const double t_c = env_now();
-  const int count = e->h_off[1];
-  if (count > 0) {
-    if (count + 2 > prefetch) {
-      ENV_TRY(cudaMemcpyAsync(e->h_off + prefetch, e->d_off + prefetch, sizeof(int32_t) * (size_t)(count + 2 - prefetch),
-                              cudaMemcpyDeviceToHost, st));
-      ENV_TRY(cudaStreamSynchronize(st));
-    }
-    int32_t *boff = e->h_off + 2;   // CSR offsets of the terminal batch (slot order = arrival order)
-    boff[count] = e->h_off[0];
-    int rc;
-    if (e->permute) {
-      // evaluate(permute=True): fold, local search on the near misses, results of the best sequence (solution.py:133-141)
+  int rc = RNAFOLD_OK;
+  if (e->permute) {
+    // evaluate(permute=True): fold, local search on the near misses, results of the best sequence (solution.py:133-141).
+    // The count and the first offsets travel together (1 KB): a second round trip only for large terminal batches.
+    const int prefetch = N + 3 < 259 ? N + 3 : 259;
+    ENV_TRY(cudaMemcpyAsync(e->h_off, e->d_off, sizeof(int32_t) * (size_t)prefetch, cudaMemcpyDeviceToHost, st));
+    ENV_TRY(cudaStreamSynchronize(st));
+    const int count = e->h_off[1];
+    if (count > 0) {
+      if (count + 2 > prefetch) {
+        ENV_TRY(cudaMemcpyAsync(e->h_off + prefetch, e->d_off + prefetch, sizeof(int32_t) * (size_t)(count + 2 - prefetch),
+                                cudaMemcpyDeviceToHost, st));
+        ENV_TRY(cudaStreamSynchronize(st));
+      }
+      int32_t *boff = e->h_off + 2;   // CSR offsets of the terminal batch (slot order = arrival order)
+      boff[count] = e->h_off[0];
       rc = rnafold_permute_batch(e->d_bseq, boff, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
                                  e->pm_allow_gu, e->seed + 0x632be59bd9b4e019ull * ++e->pm_calls, reward_exp, e->d_bdb, e->d_mfe,
                                  e->d_hd, e->d_brw, nullptr, nullptr);
-    } else {
-      rc = rnafold::fold_hamming_batch_enqueue(e->d_bseq, boff, count, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd,
-                                               e->d_brw, reward_exp, (void *)st);
+      if (rc) return rc;
     }
+  } else {
+    rc = rnafold::fold_hamming_dyn_enqueue(&e->plan, e->lens.data(), (int)e->lens.size(), N, e->d_bseq, e->d_off + 2,
+                                           e->d_off + 1, e->d_off, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
+                                           reward_exp, (void *)st);
     if (rc) return rc;
-    env_scatter_kernel<<<count, 64, 0, st>>>(count, e->lmax, e->d_list, e->d_off + 2, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb,
-                                             e->d_bseq, e->d_cur, e->d_toff, e->d_reward, e->d_last_db, e->d_last_seq, e->d_last_hd,
-                                             e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat);
-    ENV_TRY(cudaGetLastError());
-    if (e->auto_reset) {
-      env_reset_kernel<<<count, 64, 0, st>>>(N, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, e->d_list, e->d_cur,
-                                             e->d_idx, e->d_ep, e->d_seq, e->d_mask);
-      ENV_TRY(cudaGetLastError());
-    }
   }
-  const double t_d = env_now();
-  int rc = env_emit_obs(e, obs_out);
+  const int tail_grid = N < 592 ? N : 592;  // grid-stride over the terminal list (its length lives on the device)
+  env_scatter_kernel<<<tail_grid, 64, 0, st>>>(e->d_off + 1, N, e->lmax, e->d_list, e->d_off + 2, e->d_brw, e->d_hd, e->d_mfe,
+                                               e->d_bdb, e->d_bseq, e->d_cur, e->d_toff, e->d_reward, e->d_last_db,
+                                               e->d_last_seq, e->d_last_hd, e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat,
+                                               e->gc_penalty ? 1 : 0);
+  ENV_TRY(cudaGetLastError());
+  if (e->auto_reset) {
+    env_reset_kernel<<<tail_grid, 64, 0, st>>>(N, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, e->d_list, e->d_off + 1,
+                                               e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
+    ENV_TRY(cudaGetLastError());
+  }
+  rc = env_emit_obs(e, obs_out);
   if (rc) return rc;
   ENV_TRY(copy_out(reward_out, e->d_reward, sizeof(double) * (size_t)N, st));
   ENV_TRY(copy_out(done_out, e->d_done, (size_t)N, st));
-  const double t_e = env_now();
-  ENV_TRY(cudaStreamSynchronize(st));
-  const double t_f = env_now();
-  g_env_t[0] += t_b - t_a; g_env_t[1] += t_c - t_b; g_env_t[2] += t_d - t_c; g_env_t[3] += t_e - t_d; g_env_t[4] += t_f - t_e;
-  if (++g_env_calls % 200 == 0 && getenv("RNAFOLD_ENV_TIMING")) {
-    fprintf(stderr, "[env] per step us: launch step %.1f | count D2H+sync %.1f | fold+scatter+reset %.1f | obs+copies enqueue %.1f | final sync %.1f\n",
-            g_env_t[0] / 200, g_env_t[1] / 200, g_env_t[2] / 200, g_env_t[3] / 200, g_env_t[4] / 200);
-    for (double &v : g_env_t) v = 0;
+  const bool host_out = (obs_out && !env_is_device_ptr(obs_out)) || (reward_out && !env_is_device_ptr(reward_out)) ||
+                        (done_out && !env_is_device_ptr(done_out));
+  if (host_out) {
+    // the one synchronisation of the step; the library's sticky status word (a backtrack that found no
+    // decomposition) is read with it
+    ENV_TRY(cudaMemcpyAsync(e->h_status, rnafold::status_word(), sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    ENV_TRY(cudaStreamSynchronize(st));
+    if (*e->h_status) {
+      char buf[96];
+      std::snprintf(buf, sizeof(buf), "backtrack found no decomposition (code %d)", *e->h_status);
+      return set_error(RNAFOLD_ECUDA, buf);
+    }
   }
   return RNAFOLD_OK;
 }

@@ -62,6 +62,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads, 1)
 fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *__restrict__ queue,
                     ST *__restrict__ CBg, ST *__restrict__ Fg, long long gstride) {
   extern __shared__ __align__(16) unsigned char smem[];
+  if (a.dyn && a.dyn[0] == 0) return;  // device-counted launch with nothing routed to it (uniform over the cluster)
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
   const ClusterSmem Ls = ClusterSmem::make(nmax, (int)sizeof(ST));
@@ -113,8 +114,8 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
     }
     cluster.sync();
     const int slot = misc[0];
-    if (slot >= a.B) break;
-    const int b = a.order ? a.order[slot] : slot;
+    if (slot >= batch_count(a)) break;
+    const int b = batch_entry(a, slot);
     const int beg = a.off[b];
     const int n = a.off[b + 1] - beg;
     ST *cbg = CBg + (long long)slot * gstride;
@@ -387,8 +388,8 @@ f5_backtrack_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, co
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = blockIdx.x * kBtWarps + warp;
-  if (slot >= a.B) return;
-  const int b = a.order ? a.order[slot] : slot;
+  if (slot >= batch_count(a)) return;
+  const int b = batch_entry(a, slot);
   if (a.redo && a.redo[b]) return;  // left to the int32 re-run
   const int np = wave_np(nmax);
   unsigned char *base = smem + (size_t)warp * bt_warp_bytes(nmax);

@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(kCtaThreads)
 fold_cta_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *__restrict__ gws,
                 long long ws_stride, int *__restrict__ queue) {
   extern __shared__ __align__(16) unsigned char smem[];
+  if (a.dyn && a.dyn[0] == 0) return;  // device-counted launch with nothing routed to it
   const SmemLayout L = SmemLayout::make(nmax, kSmemTables);
   SmallParams &sp = *reinterpret_cast<SmallParams *>(smem + L.sp_off);
   int *f5 = reinterpret_cast<int *>(smem + L.f5_off);
@@ -101,8 +102,8 @@ fold_cta_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, int *_
     }
     __syncthreads();
     const int slot = misc[0];
-    if (slot >= a.B) break;
-    const int b = a.order ? a.order[slot] : slot;
+    if (slot >= batch_count(a)) break;
+    const int b = batch_entry(a, slot);
     if (a.redo_filter && !a.redo[b]) continue;
     const int beg = a.off[b];
     const int n = a.off[b + 1] - beg;

@@ -28,7 +28,15 @@ struct BatchArgs {
   int32_t *status;  // set non-zero by a CTA whose backtrack found no decomposition
   int32_t *redo;    // per sequence: set by the int16 kernel when a value left its checked range
   int32_t redo_filter;  // non-zero: fold only sequences whose redo flag is set (int32 re-run)
+  // Batch size known only on the device (environment step: the terminal batch is compacted by a kernel and never
+  // crosses to the host): dyn[0] = number of sequences of this launch, dyn[1] = its first entry in `order`.
+  // nullptr: B / order as given.
+  const int32_t *dyn;
 };
+__device__ __forceinline__ int batch_count(const BatchArgs &a) { return a.dyn ? a.dyn[0] : a.B; }
+__device__ __forceinline__ int batch_entry(const BatchArgs &a, int slot) {
+  return a.order ? a.order[slot + (a.dyn ? a.dyn[1] : 0)] : slot;
+}
 
 size_t cta_kernel_smem_bytes(int nmax, bool tables_in_smem);
 int cta_kernel_occupancy(int nmax, bool tables_in_smem);
@@ -51,13 +59,22 @@ size_t cluster_table_stride(int nmax);
 int cluster_max_active(int nmax);
 cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nmax, int num_clusters, int *queue,
                                 void *cbg, void *fg, cudaStream_t st);
-cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
-                                cudaStream_t st);
+cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, int count, const void *cbg,
+                                const void *fg, cudaStream_t st);
 
 // capi.cu: fold + Hamming of a device-resident batch with host offsets, enqueued on `stream` without a trailing
 // synchronisation (the caller synchronises before the next fold call)
 int fold_hamming_batch_enqueue(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, uint8_t *db_out,
                                int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream);
+
+// capi.cu: the same for a batch whose SIZE lives on the device (count_ptr; cap bounds it; `lengths` = the sequence
+// lengths that can occur): a routing kernel bins the sequences by length class, every fold kernel reads its own
+// count from device memory -- nothing crosses to the host.  *plan caches the launch list (fold_dyn_plan_free).
+int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int cap, const uint8_t *seq, int32_t *off,
+                             const int32_t *count_ptr, const int32_t *total_ptr, const uint8_t *target, uint8_t *db_out,
+                             int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream);
+void fold_dyn_plan_free(void *plan);
+const int32_t *status_word();
 
 // capi.cu: records the message returned by rnafold_last_error() and passes `code` through
 int set_error(int code, const char *msg);

@@ -556,6 +556,7 @@ template <typename ST, int MAXT, int RS = 0>
 __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && sizeof(ST) == 2 ? WAVE_MAXREG128 : 128) fold_wave_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax,
                                                         int *__restrict__ queue) {
   extern __shared__ __align__(16) unsigned char smem[];
+  if (a.dyn && a.dyn[0] == 0) return;  // device-counted launch with nothing routed to it
   const WaveSmem Ls = WaveSmem::make(nmax, (int)sizeof(ST));
   int *f5 = reinterpret_cast<int *>(smem + Ls.f5_off);
   int *dml = reinterpret_cast<int *>(smem + Ls.dml_off);
@@ -614,9 +615,9 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
     }
     __syncthreads();
     const int slot = misc[0];
-    if (slot >= a.B) break;
+    if (slot >= batch_count(a)) break;
     PHASE_CLK_BEGIN();
-    const int b = a.order ? a.order[slot] : slot;
+    const int b = batch_entry(a, slot);
     const int beg = a.off[b];
     const int n = a.off[b + 1] - beg;
     int flag = 0;
@@ -997,8 +998,9 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
 // ---------------------------------------------------------------------------------------------
 size_t wave_smem_bytes(int nmax, int esz) { return (size_t)WaveSmem::make(nmax, esz).total; }
 
-// The two-cells-per-lane int16 scan adds the loop-size terms in 16-bit lanes: every term must keep
-// table value + term inside int16 (tables are checked to lie in (-25000, 30000]).
+// int16 tables hold values checked to lie in (-25000, 3000) or the stored infinity 30000; candidates are summed in
+// 32-bit registers, but the partial minima of the interior items go back into int16 rows: the loop-size terms of the
+// parameter set must keep table value + term inside int16, otherwise the int32 instances are used.
 bool wave_int16_ok(const HostParams &hp) {
   const SmallParams &s = hp.dev.s;
   int lo = 0, hi = 0;
@@ -1183,12 +1185,12 @@ cudaError_t launch_fold_cluster(const FoldParams *gp, const BatchArgs &a, int nm
   return launch_fold_cluster_rs<0>(gp, a, nmax, num_clusters, queue, cbg, fg, st);
 }
 
-cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, const void *cbg, const void *fg,
-                                cudaStream_t st) {
+cudaError_t launch_f5_backtrack(const FoldParams *gp, const BatchArgs &a, int nmax, int count, const void *cbg,
+                                const void *fg, cudaStream_t st) {
   const size_t smem = (size_t)kBtWarps * bt_warp_bytes(nmax);
   cudaError_t err = cudaFuncSetAttribute(f5_backtrack_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (err != cudaSuccess) return err;
-  const int grid = (a.B + kBtWarps - 1) / kBtWarps;
+  const int grid = (count + kBtWarps - 1) / kBtWarps;  // count bounds the batch size when it lives on the device
   f5_backtrack_kernel<int16_t><<<grid, kBtWarps * 32, smem, st>>>(gp, a, nmax, (const int16_t *)cbg, (const int16_t *)fg,
                                                                  (long long)cluster_table_stride(nmax));
   return cudaGetLastError();

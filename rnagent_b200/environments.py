@@ -25,10 +25,16 @@ ROWS = 10
 class _PrevSolution(object):
     """What callers read from env.get_attr('prev_solution') (rlif/learning/trainer.py:311-313)."""
 
-    def __init__(self, target, string, folded, hd, fe, reward_exp):
+    def __init__(self, target, string, folded, hd, fe, reward_exp, gc_penalty=False):
         self.target, self.string, self.folded_structure, self.hd, self.fe = target, string, folded, hd, fe
         n = max(1, len(string))
         self.r = (1 - float(hd) / float(n)) ** reward_exp + (0.25 if hd == 0 else 0.0)
+        if gc_penalty:                      # solution.py:150-151, gcau_content accumulates one increment per U
+            u, inc = 0.0, 1. / n
+            for ch in string:
+                if ch == 'U':
+                    u += inc
+            self.r = self.r * 0.85 + float(np.clip(u, 0, .15))
         self.source = 'rlif'  # the local search's 'rlif*' tag (solution.py:215) is not tracked per environment
 
     def __repr__(self):
@@ -40,15 +46,24 @@ class RnaDesignBatch(object):
 
     config keys read (same names as rlif/config/RnaDesign.yml `environment`): kernel_size, reward_exp, permute,
     permutation_budget / _radius / _threshold, mutation_probability, allow_gu_permutations, encoding_type,
-    use_nucleotides.  With permute=True the terminal evaluation runs the batched local search
+    use_nucleotides, gc_penalty / gc.  With permute=True the terminal evaluation runs the batched local search
     (Solution.permute, rlif/rna/solution.py:157-219 -> rnafold_permute_batch).  boosting / testing-mode
     statistics are not part of this path and raise NotImplementedError instead of silently returning something else.
+
+    step() / reset() return fresh arrays like the reference's VecEnvs (copy=False hands out the environment's own
+    buffers, which the next call overwrites).
     """
 
-    def __init__(self, config, n_envs, targets=None, rank=0, auto_reset=True, randomize=False, seed=0):
+    def __init__(self, config, n_envs, targets=None, rank=0, auto_reset=True, randomize=False, seed=0, copy=True):
         self.config = dict(config)
-        if self.config.get('encoding_type', 2) != 2 or not self.config.get('use_nucleotides', True):
-            raise NotImplementedError("only encoding_type=2 with use_nucleotides=True is implemented")
+        if self.config.get('encoding_type', 2) != 2:
+            raise NotImplementedError("only encoding_type=2 (rlif/config/RnaDesign.yml:26) is implemented")
+        if not self.config.get('use_nucleotides'):
+            # config_check('use_nucleotides') is False when the key is absent (solution.py:51-59, :71): the reference
+            # then allocates 6 rows and insert_nucleotide indexes row 6+ -> IndexError on the first step
+            raise NotImplementedError("use_nucleotides must be true (rlif/config/RnaDesign.yml:27); without it the "
+                                      "reference's insert_nucleotide fails (solution.py:92)")
+        self.copy = bool(copy)
         self.n_envs = int(n_envs)
         self.env_id = rank
         self.kernel_size = int(self.config.get('kernel_size', 25))
@@ -77,6 +92,8 @@ class RnaDesignBatch(object):
     def _configure(self):
         from .permute import DEFAULTS
         _lib.check(self.L.rnafold_env_config(self._h, int(self.auto_reset), int(self.randomize), self.seed))
+        self.gc_penalty = bool(self.config.get('gc_penalty') or self.config.get('gc'))   # solution.py:150
+        _lib.check(self.L.rnafold_env_config_reward(self._h, int(self.gc_penalty)))
         c = {k: self.config.get(k, v) for k, v in DEFAULTS.items()}
         _lib.check(self.L.rnafold_env_config_permute(
             self._h, int(bool(self.permute)), int(c['permutation_budget']), int(c['permutation_radius']),
@@ -100,7 +117,7 @@ class RnaDesignBatch(object):
     # ---- VecEnv surface
     def reset(self):
         _lib.check(self.L.rnafold_env_reset(self._h, self._obs.ctypes.data))
-        return self._obs
+        return self._obs.copy() if self.copy else self._obs
 
     def step(self, actions):
         a = np.ascontiguousarray(actions, dtype=np.int32)
@@ -108,6 +125,8 @@ class RnaDesignBatch(object):
             raise ValueError(f"expected {self.n_envs} actions")
         _lib.check(self.L.rnafold_env_step(self._h, a.ctypes.data, self.reward_exp, self._obs.ctypes.data,
                                            self._rew.ctypes.data, self._done.ctypes.data))
+        if self.copy:
+            return self._obs.copy(), self._rew.copy(), self._done.view(np.bool_).copy(), [{} for _ in range(self.n_envs)]
         return self._obs, self._rew, self._done.view(np.bool_), self._infos
 
     def step_device(self, actions, obs=None, reward=None, done=None):
@@ -149,7 +168,8 @@ class RnaDesignBatch(object):
                 n = len(self.dataset[t])
                 out.append(_PrevSolution(self.dataset[t], s['last_seq'][e, :n].tobytes().decode(),
                                          s['last_db'][e, :n].tobytes().decode(), int(s['last_hd'][e]),
-                                         float(np.float32(s['last_mfe'][e] / 100.0)), self.reward_exp))
+                                         float(np.float32(s['last_mfe'][e] / 100.0)), self.reward_exp,
+                                         self.gc_penalty))
             return out
         if name == 'target_structure':
             return [DotBracket(self.dataset[int(t)]) for t in self.snapshot()['cur']]

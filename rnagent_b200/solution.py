@@ -55,7 +55,7 @@ class Solution(object):
         self.rows, length = self.target.structure_encoding.shape
         structure_encoding = np.zeros([self.rows, length + k * 2])
         structure_encoding[:, k:k + length] = self.target.structure_encoding
-        if self.config.get('use_nucleotides', True):
+        if self.config_check('use_nucleotides'):   # absent -> False, as the reference (solution.py:51-59, :71)
             self.encoding = np.vstack([structure_encoding, np.zeros([4, length + k * 2])])
         else:
             self.encoding = structure_encoding
