@@ -18,7 +18,7 @@ constexpr int kPeakThreads = 256;
 constexpr int kPeakIters = 512;
 constexpr int kPeakUnroll = 16;
 
-__global__ void __launch_bounds__(kPeakThreads) lds_stream_kernel(int *out, int iters) {
+__global__ void __launch_bounds__(kPeakThreads) lds_stream_kernel(int *out, int iters, unsigned rot) {
   __shared__ int buf[kPeakThreads * kPeakUnroll];
   for (int k = threadIdx.x; k < kPeakThreads * kPeakUnroll; k += kPeakThreads) buf[k] = k * 7 + blockIdx.x;
   __syncthreads();
@@ -26,15 +26,23 @@ __global__ void __launch_bounds__(kPeakThreads) lds_stream_kernel(int *out, int 
   int acc[kPeakUnroll];
 #pragma unroll
   for (int u = 0; u < kPeakUnroll; ++u) acc[u] = 0;
+  // Consecutive lanes -> consecutive words (conflict free).  Each of the 16 loads of an iteration reads its own
+  // row; the rows move by `rot` (a run-time value) per iteration and the loads are ld.volatile, so ptxas can
+  // neither prove two loads equal nor reuse one across iterations: 16 LDS execute per iteration, as counted
+  // (profiles/r2_peaks_sass.txt).  Round 1's version rotated the rows by a compile-time 1 without volatile: ptxas
+  // shared each load between two iterations and the kernel executed half the loads it was credited with.
+  unsigned row = 0;
   for (int it = 0; it < iters; ++it) {
 #pragma unroll
     for (int u = 0; u < kPeakUnroll; ++u) {
       int v;
-      // consecutive lanes -> consecutive words (conflict free); rows rotate so loads stay distinct
-      // 16 distinct rows per iteration, rotating with `it`: no two loads of an iteration share an address
-      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + 4u * kPeakThreads * (unsigned)((u + it) & (kPeakUnroll - 1))));
+      asm volatile("ld.volatile.shared.b32 %0, [%1];"
+                   : "=r"(v)
+                   : "r"(base + 4u * kPeakThreads * ((row + (unsigned)u) & (kPeakUnroll - 1)))
+                   : "memory");
       acc[u] += v;
     }
+    row += rot;
   }
   int r = 0;
 #pragma unroll
@@ -72,7 +80,7 @@ cudaError_t measure_onchip_peaks(int num_sms, cudaStream_t st, double *lds_per_s
   float best_lds = 1e30f, best_alu = 1e30f;
   for (int rep = 0; rep < 5; ++rep) {
     cudaEventRecord(e0, st);
-    lds_stream_kernel<<<grid, kPeakThreads, 0, st>>>(d_out, kPeakIters);
+    lds_stream_kernel<<<grid, kPeakThreads, 0, st>>>(d_out, kPeakIters, 5u);
     cudaEventRecord(e1, st);
     cudaEventSynchronize(e1);
     float ms = 0;
