@@ -75,6 +75,10 @@ def main():
         targets.append(open(os.path.join(REF, "rlif", "data", "eterna", f"{k}.rna")).read().strip())
     targets += ["((((....))))", "....", "(((...)))..", "..((..((...))..((...))..))", ".(((((...)))))", "((...))((...))",
                 "(((((((..((((........)))).(((((.......))))).....(((((.......))))))))))))....", "(.(...).)" + "." * 40 + "((....))"]
+    # long Eterna100 targets: 100, 151, 200 nt (wave kernel, 128- and 256-thread classes), 258 and 400 nt (cluster kernel);
+    # every episode crosses the observation window (2k = 50) many times over
+    for k in (92, 36, 69, 9, 22):
+        targets.append(open(os.path.join(REF, "rlif", "data", "eterna", f"{k}.rna")).read().strip())
 
     class FakeData:
         def __init__(self, seqs):
