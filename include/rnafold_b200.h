@@ -91,6 +91,26 @@ int rnafold_fold_hamming_batch(const uint8_t *seq, const int32_t *off, int32_t B
                                double *reward_out, uint8_t *mismatch_out, double reward_exp,
                                void *stream);
 
+/* Allocation-free fold + Hamming + reward.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same results as rnafold_fold_hamming_batch, but the call allocates nothing -- no cudaMalloc,
+ * cudaFree or growing buffer: the kernels' scratch (queue counters, device-side batch count, one range-check flag
+ * per sequence) is a file-scope static __device__ array in the library image, (8 + RNAFOLD_NOALLOC_MAX_BATCH) * 4 =
+ * 262,176 bytes, held by every GPU that loads the library until exit.
+ * Limits: B <= RNAFOLD_NOALLOC_MAX_BATCH; every sequence <= nmax <= RNAFOLD_NOALLOC_MAX_LEN (the shared-memory
+ * kernels; nmax sizes the launch, a longer sequence makes the call fold nothing and sets status code 100, see
+ * rnafold_last_status); larger values are rejected with RNAFOLD_EINVAL.  EVERY buffer (seq, off, target, outputs)
+ * must be a device pointer; outputs may be NULL as in rnafold_fold_hamming_batch (no mismatch flags).  Sequences
+ * are folded in batch order (sort by length yourself for mixed batches).  Asynchronous on `stream`.
+ * All calls share the one array, which keeps the last call's contents (the call clears what it needs): calls that
+ * overlap on the GPU -- different streams without an ordering between them -- race.  Not ordered against the other
+ * fold entry points either, except through the stream you pass. */
+#define RNAFOLD_NOALLOC_MAX_BATCH 65536
+#define RNAFOLD_NOALLOC_MAX_LEN 200
+int rnafold_fold_hamming_batch_noalloc(const uint8_t *seq, const int32_t *off, int32_t B, int32_t nmax,
+                                       const uint8_t *target, uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
+                                       double *reward_out, double reward_exp, void *stream);
+
 /* Wait for the last fold call and report the sticky device status word: 0, or the failure code of a kernel whose
  * backtrack found no decomposition (then the return value is RNAFOLD_ECUDA).  clear != 0 resets it. */
 int rnafold_last_status(int32_t *status, int32_t clear);

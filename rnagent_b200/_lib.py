@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("RNAFOLD_LIB") or os.path.join(_HERE, "librnafold_b200
 EXPORTS = [
     "rnafold_init", "rnafold_shutdown", "rnafold_last_error", "rnafold_version",
     "rnafold_read_parameter_file", "rnafold_export_params", "rnafold_parse_params", "rnafold_set_md", "rnafold_get_md",
-    "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch",
+    "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch", "rnafold_fold_hamming_batch_noalloc",
     "rnafold_last_status", "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
     "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes", "rnafold_current_device",
     "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_config_reward", "rnafold_env_set_targets", "rnafold_env_reset",
@@ -56,6 +56,7 @@ def load_library():
         L.rnafold_fold_batch.argtypes = [vp, vp, ci, vp, vp, vp]
         L.rnafold_fold_hamming_batch.argtypes = [vp, vp, ci, vp, vp, vp, vp, vp, vp, cd, vp]
         L.rnafold_last_launch_info.argtypes = [ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+        L.rnafold_fold_hamming_batch_noalloc.argtypes = [vp, vp, ci, ci, vp, vp, vp, vp, vp, cd, vp]
         L.rnafold_last_status.argtypes = [ctypes.POINTER(ctypes.c_int32), ci]
         L.rnafold_set_timing.argtypes = [ci]
         L.rnafold_last_kernel_ms.argtypes = [ctypes.POINTER(ctypes.c_float)]

@@ -113,6 +113,36 @@ struct Context {
 Context *g_ctx = nullptr;
 std::mutex g_mu;
 
+// ---- scratch of rnafold_fold_hamming_batch_noalloc: lives in the library image, never cudaMalloc'd.
+// Layout (int32 words): [0] queue counter of the fold kernel, [1] queue counter of the int32 re-run, [2] number of
+// sequences the launches may fold (written by the validation kernel: B, or 0 when a sequence is longer than nmax),
+// [3] first entry (always 0), [4..7] unused, [8 .. 8 + RNAFOLD_NOALLOC_MAX_BATCH) range-check flags, one per sequence.
+// In HOST code the name below is only a stand-in for the symbol; its device address is resolved once, at set-up,
+// with cudaGetSymbolAddress (g_noalloc_ptr) -- kernels are always handed that pointer.
+constexpr int kNoallocHeader = 8;
+constexpr size_t kNoallocWords = (size_t)kNoallocHeader + RNAFOLD_NOALLOC_MAX_BATCH;
+static __device__ __align__(256) int32_t g_noalloc_scratch[kNoallocWords];
+int32_t *g_noalloc_ptr = nullptr;        // device address of g_noalloc_scratch on the context's device
+cudaError_t g_noalloc_err = cudaSuccess;  // outcome of the address lookup
+
+// every sequence must fit the launch's length class (the fold kernels size their shared memory by nmax): otherwise
+// nothing is folded and the sticky status word reports code 100
+__global__ void noalloc_validate_kernel(const int32_t *__restrict__ off, int B, int nmax, int32_t *scratch, int32_t *status) {
+  __shared__ int bad;
+  if (threadIdx.x == 0) bad = 0;
+  __syncthreads();
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    const int n = off[b + 1] - off[b];
+    if (n < 0 || n > nmax) bad = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    scratch[2] = bad ? 0 : B;
+    scratch[3] = 0;
+    if (bad) atomicExch(status, 100);
+  }
+}
+
 bool is_device_ptr(const void *p) {
   if (!p) return false;
   cudaPointerAttributes at;
@@ -766,6 +796,14 @@ int rnafold_init(int device) {
     return rc;
   }
   g_ctx = c;
+  // set-up of the allocation-free entry point: device address of its static scratch, once per device, with that
+  // device current (a failure only disables that entry point)
+  g_noalloc_ptr = nullptr;
+  g_noalloc_err = cudaGetSymbolAddress((void **)&g_noalloc_ptr, g_noalloc_scratch);
+  if (g_noalloc_err != cudaSuccess) {
+    g_noalloc_ptr = nullptr;
+    cudaGetLastError();
+  }
   return RNAFOLD_OK;
 }
 
@@ -903,12 +941,72 @@ int rnafold_fold_batch(const uint8_t *seq, const int32_t *off, int32_t B, uint8_
   return run_batch(g_ctx, seq, off, B, nullptr, db_out, mfe_dcal_out, nullptr, nullptr, nullptr, 1.0, stream);
 }
 
+// Allocation-free variant of rnafold_fold_hamming_batch (see include/rnafold_b200.h): no cudaMalloc / cudaFree /
+// growing buffer anywhere on this path; the kernels' scratch is the static device array above.
+int rnafold_fold_hamming_batch_noalloc(const uint8_t *seq, const int32_t *off, int32_t B, int32_t nmax, const uint8_t *target,
+                                       uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out, double *reward_out,
+                                       double reward_exp, void *stream) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  Context *c = g_ctx;
+  if (!c) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
+  if (!g_noalloc_ptr)
+    return fail(RNAFOLD_ECUDA, "static scratch unavailable: cudaGetSymbolAddress: %s", cudaGetErrorString(g_noalloc_err));
+  if (B < 0 || !off || (B > 0 && !seq)) return fail(RNAFOLD_EINVAL, "null seq/off or negative batch size");
+  if (B > RNAFOLD_NOALLOC_MAX_BATCH)
+    return fail(RNAFOLD_EINVAL, "noalloc: batch of %d sequences exceeds the static scratch (RNAFOLD_NOALLOC_MAX_BATCH = %d)", B,
+                RNAFOLD_NOALLOC_MAX_BATCH);
+  if (nmax < 0 || nmax > RNAFOLD_NOALLOC_MAX_LEN)
+    return fail(RNAFOLD_EINVAL, "noalloc: nmax %d exceeds RNAFOLD_NOALLOC_MAX_LEN = %d", nmax, RNAFOLD_NOALLOC_MAX_LEN);
+  if (B == 0) return RNAFOLD_OK;
+  if (!is_device_ptr(seq) || !is_device_ptr(off) || (target && !is_device_ptr(target)) || (db_out && !is_device_ptr(db_out)) ||
+      (mfe_dcal_out && !is_device_ptr(mfe_dcal_out)) || (hd_out && !is_device_ptr(hd_out)) ||
+      (reward_out && !is_device_ptr(reward_out)))
+    return fail(RNAFOLD_EINVAL, "noalloc: every buffer must be a device pointer (host buffers would need staging memory)");
+  CUDA_TRY(cudaSetDevice(c->device));
+  const Limits lim = make_limits(c);
+  const int cls = std::max(nmax, 8);
+  if (cls > lim.wave_limit) return fail(RNAFOLD_EINVAL, "noalloc: nmax %d is beyond the shared-memory kernel's reach (%d)", nmax, lim.wave_limit);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+  int32_t *scr = g_noalloc_ptr;
+  // the array keeps the previous call's contents: queue counters, count and this batch's flags start at zero
+  CUDA_TRY(cudaMemsetAsync(scr, 0, sizeof(int32_t) * ((size_t)kNoallocHeader + (size_t)B), st));
+  noalloc_validate_kernel<<<1, 1024, 0, st>>>(off, B, nmax, scr, c->d_status);
+  CUDA_TRY(cudaGetLastError());
+  BatchArgs a;
+  a.seq = seq;
+  a.off = off;
+  a.order = nullptr;  // sequences are folded in batch order (no sorted copy: that would need scratch per call)
+  a.B = B;
+  a.target = target;
+  a.db = db_out;
+  a.mfe = mfe_dcal_out;
+  a.hd = target ? hd_out : nullptr;
+  a.reward = target ? reward_out : nullptr;
+  a.mismatch = nullptr;
+  a.reward_exp = reward_exp;
+  a.status = c->d_status;
+  a.redo = scr + kNoallocHeader;
+  a.redo_filter = 0;
+  a.dyn = scr + 2;
+  int threads = wave_threads(cls);
+  if (B <= c->num_sms) threads = 512;
+  const int occ = std::max(1, wave_occupancy(cls, lim.wave_esz, threads));
+  CUDA_TRY(launch_fold_wave(c->d_params, a, cls, lim.wave_esz, std::min(B, c->num_sms * occ), threads, scr + 0, st));
+  if (lim.wave_esz == 2) {
+    // sequences whose values left the int16 range are re-folded with int32 tables in shared memory
+    a.redo_filter = 1;
+    const int occ2 = std::max(1, cta_kernel_occupancy(cls, true));
+    CUDA_TRY(launch_fold_cta(c->d_params, a, cls, true, std::min(B, c->num_sms * occ2), nullptr, 0, scr + 1, st));
+  }
+  return RNAFOLD_OK;
+}
+
 int rnafold_last_status(int32_t *status, int32_t clear) {
   std::lock_guard<std::mutex> lk(g_mu);
   if (!g_ctx) return fail(RNAFOLD_ENOINIT, "rnafold_init was not called");
   Context *c = g_ctx;
   CUDA_TRY(cudaSetDevice(c->device));
-  if (c->have_done) CUDA_TRY(cudaEventSynchronize(c->ev_done));
+  CUDA_TRY(cudaDeviceSynchronize());  // whatever stream the last (asynchronous) call was enqueued on
   int32_t v = 0;
   CUDA_TRY(cudaMemcpy(&v, c->d_status, sizeof(int32_t), cudaMemcpyDeviceToHost));
   if (v && clear) CUDA_TRY(cudaMemset(c->d_status, 0, sizeof(int32_t)));
