@@ -172,6 +172,13 @@ int rnafold_permute_batch(uint8_t *seq, const int32_t *off, int32_t B, const uin
                           int32_t radius, int32_t threshold, double mutation_probability, int32_t allow_gu,
                           uint64_t seed, double reward_exp, uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
                           double *reward_out, int32_t *rounds_out, int32_t *folds_out);
+/* Order in which a round visits its candidate positions -- the reference iterates a Python set (solution.py:183,189),
+ * and the order decides which write wins when two mutations touch the same nucleotide.  0 (default): CPython >= 3.7 set
+ * order (what recorded tests/golden/permute_cases.json); 1: CPython 3.6 (the interpreter rlif.yml:5 pins: the table
+ * grows at 2/3 full instead of 3/5); 2: ascending positions. */
+int rnafold_permute_set_order(int32_t mode);
+/* Host-only: that order for one sequence's mismatch flags (n bytes) and radius -> positions in out[<= n]; returns their number. */
+int rnafold_permute_candidate_order(const uint8_t *mismatch, int32_t n, int32_t radius, int32_t mode, int32_t *out);
 /* Host-only: the draw behind random.random() (kind 0: (v >> 11) * 2^-53), random.randint(0,3) (kind 1: (v >> 33) % 4)
  * and random.randint(0,5) (kind 2: (v >> 33) % 6) of round `step` at position `pos` of sequence `index`. */
 uint64_t rnafold_permute_draw(uint64_t seed, int32_t index, int32_t step, int32_t pos, int32_t kind);

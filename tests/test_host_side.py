@@ -204,3 +204,37 @@ def test_rollout_stats_all_reduce_gloo_world2(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=120)
         assert p.returncode == 0, out.decode()
+
+
+def test_permute_candidate_order_is_cpythons_set_order():
+    """The local search visits its candidate positions in the order the reference's `for mismatch in
+    best_mismatch_indices` walks a Python set (rlif/rna/solution.py:166-189).  The library replays CPython's set
+    insertion; here it is compared with real `set` objects built by the reference's own get_surrounding arithmetic
+    (this interpreter is CPython >= 3.7: mode 0), and mode 2 with the ascending order."""
+    import random
+    import sys
+    from rnagent_b200 import _lib
+    assert sys.implementation.name == "cpython" and sys.version_info >= (3, 7)
+    L = _lib.load_library()
+    rng = random.Random(5)
+    for trial in range(3000):
+        n = rng.randint(1, 460)
+        radius = rng.choice([1, 1, 2, 3, 5, 5, 8])
+        mm = np.zeros(n, dtype=np.uint8)
+        for _ in range(rng.randint(0, min(n, 40))):
+            mm[rng.randrange(n)] = 1
+        all_indices = []
+        for index in np.where(mm)[0]:
+            for i in range(1, radius + 1):
+                if index - i >= 0:
+                    all_indices.append(int(index - i))
+                if index + i <= n - 1:
+                    all_indices.append(int(index + i))
+        want = list(set(all_indices))
+        out = np.zeros(n + 1, dtype=np.int32)
+        k = L.rnafold_permute_candidate_order(mm.ctypes.data, n, radius, 0, out.ctypes.data)
+        assert out[:k].tolist() == want, (n, radius, np.where(mm)[0].tolist())
+        k2 = L.rnafold_permute_candidate_order(mm.ctypes.data, n, radius, 2, out.ctypes.data)
+        assert out[:k2].tolist() == sorted(want)
+        k1 = L.rnafold_permute_candidate_order(mm.ctypes.data, n, radius, 1, out.ctypes.data)   # CPython 3.6 growth rule
+        assert sorted(out[:k1].tolist()) == sorted(want)
