@@ -141,6 +141,9 @@ int rnafold_env_destroy(int32_t handle);
 /* auto_reset: re-arm finished environments inside step (VecEnv behaviour); randomize: hashed random target
  * choice instead of round-robin (RLIFenv.py:87-92; Python's RNG stream is not reproduced). */
 int rnafold_env_config(int32_t handle, int32_t auto_reset, int32_t randomize, uint64_t seed);
+/* env.set_attr('current_sequence', v) of the reference's evaluation loop (rlif/learning/tester.py:63): sets every
+ * environment's round-robin position; the next reset takes target (v + 1) % n_targets (RLIFenv.py:89-90). */
+int rnafold_env_set_current(int32_t handle, int32_t value);
 /* Reward shaping of Solution.evaluate (rlif/rna/solution.py:150-151, config keys gc_penalty / gc):
  * r = r * 0.85 + clip(fraction of U, 0, 0.15) on the terminal step. */
 int rnafold_env_config_reward(int32_t handle, int32_t gc_penalty);

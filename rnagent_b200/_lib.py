@@ -18,7 +18,7 @@ EXPORTS = [
     "rnafold_workspace_bytes", "rnafold_fold_batch", "rnafold_fold_hamming_batch", "rnafold_fold_hamming_batch_noalloc",
     "rnafold_last_status", "rnafold_last_launch_info", "rnafold_set_timing", "rnafold_last_kernel_ms",
     "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes", "rnafold_current_device",
-    "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_config_reward", "rnafold_env_set_targets", "rnafold_env_reset",
+    "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_config_reward", "rnafold_env_set_current", "rnafold_env_set_targets", "rnafold_env_reset",
     "rnafold_env_step", "rnafold_env_stats", "rnafold_env_snapshot", "rnafold_parse_target",
     "rnafold_permute_batch", "rnafold_permute_draw", "rnafold_permute_set_order", "rnafold_permute_candidate_order", "rnafold_env_config_permute",
 ]
@@ -68,6 +68,7 @@ def load_library():
         L.rnafold_env_destroy.argtypes = [ci]
         L.rnafold_env_config.argtypes = [ci, ci, ci, u64]
         L.rnafold_env_config_reward.argtypes = [ci, ci]
+        L.rnafold_env_set_current.argtypes = [ci, ci]
         L.rnafold_env_set_targets.argtypes = [ci, vp, vp, ci]
         L.rnafold_env_reset.argtypes = [ci, vp]
         L.rnafold_env_step.argtypes = [ci, vp, cd, vp, vp, vp]

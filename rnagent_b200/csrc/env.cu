@@ -378,6 +378,19 @@ int rnafold_env_config(int32_t h, int32_t auto_reset, int32_t randomize, uint64_
   return RNAFOLD_OK;
 }
 
+// env.set_attr('current_sequence', v) (rlif/learning/tester.py:63): every environment's round-robin position;
+// the next reset moves on to (v + 1) % n_targets (RLIFenv.py:89-90)
+int rnafold_env_set_current(int32_t h, int32_t value) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
+  if (value < -1 || value >= e->n_targets) return set_error(RNAFOLD_EINVAL, "current_sequence out of range");
+  std::vector<int32_t> v((size_t)e->n_envs, value);
+  ENV_TRY(cudaMemcpyAsync(e->d_cur, v.data(), sizeof(int32_t) * v.size(), cudaMemcpyHostToDevice, e->stream));
+  ENV_TRY(cudaStreamSynchronize(e->stream));
+  return RNAFOLD_OK;
+}
+
 int rnafold_env_config_reward(int32_t h, int32_t gc_penalty) {
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);

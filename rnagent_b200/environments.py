@@ -26,7 +26,11 @@ class _PrevSolution(object):
     """What callers read from env.get_attr('prev_solution') (rlif/learning/trainer.py:311-313)."""
 
     def __init__(self, target, string, folded, hd, fe, reward_exp, gc_penalty=False):
+        # target: the DotBracket of the episode (file_nr indexes the tester's per-target arrays, tester.py:91)
         self.target, self.string, self.folded_structure, self.hd, self.fe = target, string, folded, hd, fe
+        self.str = list(string)
+        self.time = None
+        self.mismatch_indices = np.where([a != b for a, b in zip(target.seq, folded)])[0]
         n = max(1, len(string))
         self.r = (1 - float(hd) / float(n)) ** reward_exp + (0.25 if hd == 0 else 0.0)
         if gc_penalty:                      # solution.py:150-151, gcau_content accumulates one increment per U
@@ -36,6 +40,17 @@ class _PrevSolution(object):
                     u += inc
             self.r = self.r * 0.85 + float(np.clip(u, 0, .15))
         self.source = 'rlif'  # the local search's 'rlif*' tag (solution.py:215) is not tracked per environment
+
+    def gcau_content(self):
+        from .solution import gcau_content
+        return gcau_content(self.str)
+
+    def summary(self, print_output=False, colorize=False):
+        from .solution import summary_lines
+        lines = summary_lines(self)
+        if print_output:
+            print('\n'.join(lines))
+        return lines
 
     def __repr__(self):
         return f"<solution hd={self.hd} fe={self.fe:.2f} {self.string}>"
@@ -101,10 +116,13 @@ class RnaDesignBatch(object):
 
     # ---- RnaDesign.set_data / set_sequence (RLIFenv.py:106-113)
     def set_data(self, data):
-        seqs = [d.seq if hasattr(d, 'seq') else str(d) for d in (data.sequences if hasattr(data, 'sequences') else data)]
+        items = list(data.sequences if hasattr(data, 'sequences') else data)
+        seqs = [d.seq if hasattr(d, 'seq') else str(d) for d in items]
         if not seqs:
             raise ValueError("empty data set")
         self.dataset = seqs
+        self._data = data            # what get_attr('dataset') hands back (tester.py:66)
+        self._dots = [d if isinstance(d, DotBracket) else DotBracket(s, None, k + 1) for k, (d, s) in enumerate(zip(items, seqs))]
         raw = np.frombuffer(''.join(seqs).encode(), dtype=np.uint8).copy()
         off = np.zeros(len(seqs) + 1, dtype=np.int32)
         off[1:] = np.cumsum([len(s) for s in seqs])
@@ -166,18 +184,26 @@ class RnaDesignBatch(object):
                     out.append(None)
                     continue
                 n = len(self.dataset[t])
-                out.append(_PrevSolution(self.dataset[t], s['last_seq'][e, :n].tobytes().decode(),
+                out.append(_PrevSolution(self._dots[t], s['last_seq'][e, :n].tobytes().decode(),
                                          s['last_db'][e, :n].tobytes().decode(), int(s['last_hd'][e]),
                                          float(np.float32(s['last_mfe'][e] / 100.0)), self.reward_exp,
                                          self.gc_penalty))
             return out
         if name == 'target_structure':
-            return [DotBracket(self.dataset[int(t)]) for t in self.snapshot()['cur']]
+            return [self._dots[int(t)] for t in self.snapshot()['cur']]
+        if name == 'dataset':
+            return [self._data] * self.n_envs
+        if name == 'next_target_structure':      # fetched, never called, by tester.py:67
+            return [self.reset] * self.n_envs
         return [getattr(self, name)] * self.n_envs
 
     def set_attr(self, name, value):
         if name == 'dataset':
             return self.set_data(value)
+        if name == 'current_sequence':       # tester.py:63; the next reset moves on to (value + 1) % len(dataset)
+            return _lib.check(self.L.rnafold_env_set_current(self._h, int(value)))
+        if name == 'meta_learning' and not value:
+            raise NotImplementedError("meta_learning=False (same target every episode): use a one-target data set")
         if name == 'boosting' and value:
             raise NotImplementedError("boosting=True is not on the batched path")
         if name == 'testing_mode' and value:

@@ -17,6 +17,29 @@ from .permute import permute_batch
 from .vienna import fold_hamming_batch
 
 
+def gcau_content(chars):
+    """rlif/rna/solution.py:257-268: proportions of G, C, A, U, accumulated one increment per nucleotide."""
+    gcau = dict(G=0, C=0, A=0, U=0)
+    increment = 1. / max(1, len(chars))
+    for nucleotide in chars:
+        if nucleotide in gcau:
+            gcau[nucleotide] += increment
+    return gcau
+
+
+def summary_lines(sol):
+    """Solution.summary (rlif/rna/solution.py:329-345) without the console colouring: the six lines the result
+    logs hold per solution (header with sequence number / length / unpaired fraction / HD / reward / nucleotide
+    proportions, S:, F:, T:, D2; and FE:)."""
+    gcau = sol.gcau_content()
+    t = sol.target
+    nr = t.file_nr if t.file_nr is not None else 0
+    header = '\n\nSeq Nr. {:5}, Len: {:3}, DBr: {:.2f}, HD: {:3}, Reward: {:.5f}'.format(nr, t.len, t.percent_unpaired, sol.hd, sol.r)
+    header += '  ||   G:{:.2f} | C:{:.2f} | A:{:.2f} | U:{:.2f} |'.format(gcau['G'], gcau['C'], gcau['A'], gcau['U'])
+    return [header, 'S:  ' + sol.string, 'F:  ' + sol.folded_structure, 'T:  ' + t.seq, 'D2; ' + t.struct_motifs,
+            'FE: {:.3f}'.format(sol.fe)]
+
+
 class Solution(object):
     def __init__(self, target, config=None, string=None, time=None, source='rlif'):
         self.config = dict(config or {})
@@ -130,12 +153,13 @@ class Solution(object):
         return list(res.sequences[0]), int(res.hd[0])
 
     def gcau_content(self):
-        gcau = dict(G=0, C=0, A=0, U=0)
-        increment = 1. / max(1, len(self.str))
-        for nucleotide in self.str:
-            if nucleotide in gcau:
-                gcau[nucleotide] += increment
-        return gcau
+        return gcau_content(self.str)
+
+    def summary(self, print_output=False, colorize=False):
+        lines = summary_lines(self)
+        if print_output:
+            print('\n'.join(lines))
+        return lines
 
     def __repr__(self):
         return "<Solution hd={} fe={} {}>".format(self.hd, self.fe, self.string)

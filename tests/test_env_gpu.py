@@ -48,7 +48,7 @@ def test_replays_reference_episodes_bit_for_bit(golden):
         for k in range(n_envs):
             assert sol[k].string == e["sequence"] and sol[k].folded_structure == e["folded"]
             assert sol[k].hd == e["hd"] and sol[k].fe == pytest.approx(e["fe"], abs=1e-6)
-            assert sol[k].target == e["target"]
+            assert sol[k].target.seq == e["target"]
     st = env.stats()
     assert st.episodes == n_envs * len(eps) and st.steps == n_envs * sum(len(e["actions"]) for e in eps)
     assert st.solved == n_envs * sum(1 for e in eps if e["hd"] == 0)
@@ -107,3 +107,98 @@ def test_solution_object_evaluates_like_the_reference(golden):
         assert (better.hd, better.folded_structure) == (ep["hd"], ep["folded"])
         r2, hd2, _ = better.evaluate(permute=True, reward=True)
         assert hd2 <= hd and rb.fold(better.string)[0] == better.folded_structure
+
+
+def _pair_policy(obs):
+    """G for an opening bracket (its partner gets C), A elsewhere: row 0 of the window's centre column is motif 'O'."""
+    k = obs.shape[2] // 2
+    return np.where(obs[:, 0, k, 0] == 1, 2, 0).astype(np.int32)
+
+
+def test_gc_penalty_reward_shaping(golden):
+    """config gc_penalty / gc (rlif/rna/solution.py:150-151): r * 0.85 + clip(U fraction, 0, .15) on the batched path,
+    against the reference formula evaluated on the recorded episodes' own sequences."""
+    import rnagent_b200
+    rnagent_b200.set_vienna_params(1)
+    eps = [e for e in golden["episodes"] if len(e["target"]) <= 100][:12]
+    for key in ("gc_penalty", "gc"):
+        for e in eps[:6] if key == "gc" else eps:
+            env = rnagent_b200.RnaDesignBatch(dict(golden["config"], **{key: True}), 2, targets=[e["target"]], auto_reset=False)
+            env.reset()
+            for a in e["actions"]:
+                obs, r, done, _ = env.step(np.full(2, a, dtype=np.int32))
+            assert done.all()
+            n = len(e["sequence"])
+            u, inc = 0.0, 1. / n
+            for ch in e["sequence"]:
+                if ch == "U":
+                    u += inc
+            want = e["rewards"][-1] * 0.85 + float(np.clip(u, 0, .15))
+            assert abs(r[0] - want) < 1e-12 and r[0] == r[1]
+            assert abs(env.get_attr("prev_solution")[0].r - want) < 1e-12
+            env.close()
+
+
+def test_create_env_rollout_and_timed_evaluation(tmp_path):
+    """The rollout surface of rlif/learning/trainer.py:523-565, :307-313 and rlif/learning/tester.py:43-128 on the
+    batched environment: create_env / rollout / set_attr('dataset' | 'randomize' | 'current_sequence' | 'permute') /
+    get_attr('prev_solution'), the tester's bookkeeping and the files it writes."""
+    import re
+    import rnagent_b200 as rb
+    from rnagent_b200 import Dataset, PolicyModel, Tester
+    rb.set_vienna_params(1)
+    cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True, permutation_budget=15,
+               permutation_radius=5, permutation_threshold=15, allow_gu_permutations=True, mutation_probability=0.5)
+    targets = ["((((....))))", "..((((...))))..", "(((..(((...)))..)))", "....", "((((....))))..((((....))))", ".((((((....)))))).",
+               "(((((.....)))))"]
+    # -- trainer.py:523-565 / :307-313
+    env = rb.create_env("RnaDesign", cfg, 16, targets=targets)
+    stats, total_r = rb.rollout(env, _pair_policy, 60)
+    assert stats.steps == 16 * 60 and stats.episodes > 16 and stats.solved > 0 and total_r > 0
+    prev = env.get_attr("prev_solution")
+    assert all(p is not None and rb.fold(p.string)[0] == p.folded_structure for p in prev)
+    assert all(p.target.seq in targets and p.hd == rb.hamming_distance(p.target.seq, p.folded_structure)[0] for p in prev)
+    with pytest.raises(NotImplementedError):
+        rb.create_env("RankedRnaDesign", cfg, 4)
+    # -- tester.py:43-128 with the reference's attribute round trip
+    class Wrapper(object):
+        config = {"environment": cfg}
+        _model_path, current_checkpoint = "models/x", 7
+    w = Wrapper()
+    w.test_env = rb.create_env("RnaDesign", cfg, 1, targets=["...."])        # replaced by set_attr('dataset', ...)
+    w.env = env
+    w.model = PolicyModel(_pair_policy, env)
+    tester = Tester(w, results_dir=str(tmp_path))
+    data = Dataset("toyset", sequences=targets)
+    solved, summary = tester.timed_evaluation(dataset="toyset", time_limit=1e9, permute=True, verbose=False, test_set=data,
+                                              max_episodes=21)
+    assert w.model.env is env                                   # training environment restored (tester.py:121)
+    assert w.test_env.dataset == targets and w.test_env.permute is True and w.test_env.randomize is False
+    # current_sequence = 0 then reset(): the walk starts at target index 1 (file_nr 2) and goes round-robin
+    assert tester.attempts.tolist() == [3] * 7 and int(tester.attempts.sum()) == 21
+    assert len(solved) >= 12 and summary[1] == len(solved) and summary[3:] == ["models/x", 7, "toyset"]
+    for target_id, sol, att, mhd, secs, limit in solved:
+        assert sol.hd == 0 and mhd == 0 and sol.target.file_nr - 1 == target_id and sol.target.seq == targets[target_id]
+        assert rb.fold(sol.string)[0] == sol.target.seq and 1 <= att <= 3 and limit == 1e9
+    assert all(tester.min_hd[t] == 0 for t in {s[0] for s in solved})
+    # -- the files (tester.py:130-196)
+    log = open(tester.last_log).read().split("\n")
+    assert re.fullmatch(r"Dataset: toyset, date: \d\d-\d\d_\d\d-\d\d, solved %d/7 sequences with 1000000000.0s eval budget\." % len(solved), log[0])
+    assert log[1] == "=" * 100 and log[2] == "Permutation strategy: False, budget: 15, threshold: 15, radius: 5"
+    body = "\n".join(log[3:])
+    first = solved[0][1]
+    assert ("\n\nSeq Nr. {:5}, Len: {:3}, DBr: {:.2f}, HD: {:3}, Reward: {:.5f}".format(first.target.file_nr, first.target.len,
+            first.target.percent_unpaired, 0, first.r)) in "\n" + body
+    assert body.count("S:  ") == len(solved) and body.count("Solved in: ") == len(solved)
+    assert "S:  " + first.string + "\nF:  " + first.folded_structure + "\nT:  " + first.target.seq + "\nD2; " + first.target.struct_motifs in body
+    rows = open(tmp_path / "toyset.csv").read().split("\n")
+    assert rows[0] == "Date, Solved, Time(s), Model, Checkpoint, Dataset" + "".join(", seq%d" % (i + 1) for i in range(7)) + \
+        "".join(", seq%d(t)" % (i + 1) for i in range(7))
+    cells = rows[1].split(", ")
+    assert cells[1:6] == [str(len(solved)), "1000000000.0", "models/x", "7", "toyset"]
+    assert [int(c) for c in cells[6:13]] == tester.min_hd.tolist() and all(re.fullmatch(r"\(\d+\.\d+\)", c) for c in cells[13:])
+    tester.evaluate(time_limit=1e9, datasets=("toyset",), test_set=data, max_episodes=7)
+    assert open(tmp_path / "training_tests.csv").read() == \
+        "Date, Solved, Time(s), Model, Checkpoint, learn_test, taneda, learn_validation, eterna\n"   # first call: header only (quirk)
+    env.close()
+    w.test_env.close()

@@ -232,6 +232,46 @@ def test_full_size_c3_8192_x_n400(engine, oracle_params):
     assert _lib.last_launch_info()[1][1] == 8192   # all through the cluster kernel
 
 
+def test_full_size_c5_16384_mixed_turner1999(engine, oracle_params):
+    """BASELINE.json configs[4] at full size, bench.py's own workload (16,384 sequences, Eterna100 length mix 12..400,
+    Turner 1999): one call that spans every wave class and the cluster classes.  Size-independent properties on every
+    sequence + bit-equality with the oracle on a subset drawn across all lengths."""
+    from rnagent_b200 import _lib, synth
+    engine.set_vienna_params(2)
+    try:
+        P = oracle_params("turner1999")
+        count, seed = 16384, 1999
+        seq, off = synth.random_sequences_mixed(synth.eterna_mixed_lengths(count, seed), seed)
+        tgt = synth.random_targets(off, seed + 1)
+        out = []
+        for _ in range(2):
+            db = np.zeros_like(seq)
+            mfe = np.zeros(count, dtype=np.int32)
+            hd = np.zeros(count, dtype=np.int32)
+            _lib.fold_hamming_raw(seq, off, count, target=tgt, db=db, mfe=mfe, hd=hd, reward_exp=9.0)
+            out.append((db, mfe, hd))
+        launches, routed = _lib.last_launch_info()
+        assert routed[0] > 0 and routed[1] > 0 and routed[0] + routed[1] + routed[2] == count and launches >= 10
+        (db, mfe, hd), (db2, mfe2, hd2) = out
+        assert np.array_equal(db, db2) and np.array_equal(mfe, mfe2) and np.array_equal(hd, hd2)   # idempotent
+        assert set(np.unique(db).tolist()) <= {ord("("), ord(")"), ord(".")}
+        mism = (db != tgt).astype(np.int64)
+        assert np.array_equal(hd, np.add.reduceat(mism, off[:-1].astype(np.int64)))                  # HD == byte comparison
+        sraw, draw = seq.tobytes().decode(), db.tobytes().decode()
+        bad = sum(P.eval_structure(sraw[off[k]:off[k + 1]], draw[off[k]:off[k + 1]]) != int(mfe[k]) for k in range(count))
+        assert bad == 0, bad                                   # energy of the returned structure == returned MFE
+        assert (mfe <= 0).all()
+        pick = np.sort(np.random.default_rng(5).choice(count, 768, replace=False))
+        sub = np.concatenate([seq[off[k]:off[k + 1]] for k in pick])
+        soff = np.concatenate([[0], np.cumsum([off[k + 1] - off[k] for k in pick])]).astype(np.int32)
+        wdb, wmfe, _ = P.fold_batch(sub, soff, nthreads=0)
+        assert np.array_equal(wmfe, mfe[pick])
+        assert np.array_equal(wdb, np.concatenate([db[off[k]:off[k + 1]] for k in pick]))
+        assert len(set((off[k + 1] - off[k]) for k in pick)) > 60        # the subset spans the length mix
+    finally:
+        engine.set_vienna_params(1)
+
+
 def test_load_fasta_folds_all_records_in_one_batch(engine, tmp_path):
     engine.set_vienna_params(1)
     fa = tmp_path / "x.fasta"

@@ -238,3 +238,71 @@ def test_permute_candidate_order_is_cpythons_set_order():
         assert out[:k2].tolist() == sorted(want)
         k1 = L.rnafold_permute_candidate_order(mm.ctypes.data, n, radius, 1, out.ctypes.data)   # CPython 3.6 growth rule
         assert sorted(out[:k1].tolist()) == sorted(want)
+
+
+def test_tester_loop_and_writers_on_a_scripted_env(tmp_path):
+    """rlif/learning/tester.py:43-196 on the host: the evaluation loop's attribute round trip, bookkeeping and the
+    three result files, driven by a scripted VecEnv (no GPU): episodes of three steps, every second one solved."""
+    from rnagent_b200 import Dataset, PolicyModel, Tester
+    from rnagent_b200.environments import _PrevSolution
+    targets = ["((((....))))", "..((...))..", "....."]
+    data = Dataset("scripted", sequences=targets)
+    assert [t.file_nr for t in data.sequences] == [1, 2, 3] and data.n_seqs == 3
+
+    class FakeEnv(object):
+        n_envs = 1
+
+        def __init__(self):
+            self.attrs, self.t, self.ep, self.cur, self.prev = {}, 0, 0, -1, None
+
+        def set_attr(self, k, v):
+            self.attrs[k] = v
+            if k == 'dataset':
+                self.cur = 0
+            if k == 'current_sequence':
+                self.cur = v
+
+        def get_attr(self, k):
+            if k == 'prev_solution':
+                return [self.prev]
+            if k == 'next_target_structure':
+                return [None]
+            return [self.attrs[k]]
+
+        def reset(self):
+            self.cur = (self.cur + 1) % 3
+            self.t = 0
+            return np.zeros((1, 10, 50, 1), dtype=np.uint8)
+
+        def step(self, a):
+            self.t += 1
+            done = self.t == 3
+            if done:
+                tgt = data[self.cur]
+                hd = self.ep % 2
+                self.prev = _PrevSolution(tgt, "A" * tgt.len, tgt.seq if hd == 0 else "." * tgt.len, hd, -1.5, 9)
+                self.ep += 1
+                self.reset()
+            return np.zeros((1, 10, 50, 1), dtype=np.uint8), np.zeros(1), np.array([done]), [{}]
+
+    class Wrapper(object):
+        config = {"environment": dict(encoding_type=2, permute=False, permutation_budget=50, permutation_threshold=5, permutation_radius=1)}
+        _model_path, current_checkpoint, env = "m", 3, None
+    w = Wrapper()
+    w.test_env = FakeEnv()
+    w.model = PolicyModel(lambda s: np.zeros(1, dtype=np.int32))
+    t = Tester(w, results_dir=str(tmp_path))
+    solved, summary = t.timed_evaluation(dataset="scripted", time_limit=1e6, permute=False, verbose=False, test_set=data, max_episodes=6)
+    assert w.test_env.attrs['randomize'] is False and w.test_env.attrs['meta_learning'] is True and w.test_env.attrs['permute'] is False
+    assert t.attempts.tolist() == [2, 2, 2] and [s[0] for s in solved] == [1, 0, 2]      # walk starts at index 1 (tester.py:63)
+    assert t.min_hd.tolist() == [0, 0, 0] and summary[1] == 3
+    log = open(t.last_log).read()
+    assert "solved 3/3 sequences with 1000000.0s eval budget.\n" + "=" * 100 + "\nPermutation strategy: False, budget: 50, threshold: 5, radius: 1\n" in log
+    assert "\n\n\nSeq Nr.     2, Len:  11, DBr: 0.64, HD:   0, Reward: 1.25000  ||   G:0.00 | C:0.00 | A:1.00 | U:0.00 |\nS:  AAAAAAAAAAA\nF:  ..((...))..\nT:  ..((...))..\nD2; EEOOHHHCCEE\nFE: -1.500\nSolved in: 1 attempts, " in log
+    rows = open(tmp_path / "scripted.csv").read().split("\n")
+    assert rows[0] == "Date, Solved, Time(s), Model, Checkpoint, Dataset, seq1, seq2, seq3, seq1(t), seq2(t), seq3(t)"
+    assert rows[1].split(", ")[1:9] == ["3", "1000000.0", "m", "3", "scripted", "0", "0", "0"]
+    t.write_csv([solved], str(tmp_path / "tt.csv"), summary, 1e6)
+    t.write_csv([solved], str(tmp_path / "tt.csv"), summary, 1e6)
+    lines = open(tmp_path / "tt.csv").read().split("\n")
+    assert lines[0].startswith("Date, Solved, Time(s), Model, Checkpoint, learn_test") and lines[1].endswith(", 3, 1000000.0, m, 3, 3")

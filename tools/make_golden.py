@@ -57,6 +57,9 @@ def main():
                 rows.append({
                     "file": rel, "line": lineno, "source": cols[1], "target": target,
                     "seq": seq, "hd": int(float(cols[3])), "fe": cols[5],
+                    # mountain distance and ensemble defect of the row's solution (Solution.compute_statistics,
+                    # rlif/rna/solution.py:221-238, written by rlif/utils/comparison.py:225-233): the fixture for row N3
+                    "md": cols[4], "ed": cols[6] if len(cols) > 6 else "",
                 })
     with open(OUT, "w") as f:
         for r in rows:
