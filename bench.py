@@ -128,6 +128,77 @@ def cpu_fold_rate(seq, off, tgt, setno, budget_s, nthreads=0):
     return sample / dt, cores, sample, dt
 
 
+def cpu_executed_candidates(seq, off, setno, sample=48):
+    """W_eff: min-plus candidates the oracle actually evaluates per fold (unpairable cells and inner
+    pairs skipped), averaged over the first `sample` sequences -> (executed per fold, algorithmic W per fold)."""
+    import oracle
+    P = oracle.Params(os.path.join(ROOT, "rnagent_b200", "data", f"{PARAM_NAMES[setno]}_37.par"))
+    k = min(sample, len(off) - 1)
+    ex = alg = kern = 0
+    canpair = np.zeros((256, 256), dtype=bool)
+    for a_, b_ in ("AU", "UA", "CG", "GC", "GU", "UG"):
+        canpair[ord(a_), ord(b_)] = True
+    for b in range(k):
+        raw = seq[off[b]:off[b + 1]]
+        s_ = raw.tobytes().decode()
+        n = len(s_)
+        P.fold_dcal(s_)
+        ex += P.last_candidates()
+        alg += synth.work_candidates(n)
+        # what the GPU kernels execute: interior-loop candidates of the cells whose OUTER ends can pair (unpairable inner
+        # pairs hold a stored infinity and are still loaded), every multiloop split, hairpin / closing / extension terms
+        for d in range(4, n):
+            npair = int(canpair[raw[:n - d], raw[d:]].sum())
+            kern += npair * synth.interior_candidates(d) + (n - d) * (max(0, d - 8) + 3)
+        kern += sum(j - 4 for j in range(5, n + 1))
+    k = max(k, 1)
+    return ex / k, alg / k, kern / k
+
+
+def cpu_env_rate(targets, budget_s, n_envs=32, seed=0):
+    """C4 on the host: the reference's per-environment logic (RnaDesign.step / Solution.insert_nucleotide /
+    find_next_unfilled / get_state, rlif/environments/RLIFenv.py:59-81, rlif/rna/solution.py:84-123 -- the host state
+    machine of rnagent_b200.Solution mirrors it line for line) with the terminal evaluation served by the oracle fold.
+    One Python process, like one worker of the reference's SubprocVecEnv.  -> (env steps/s, episodes/s, steps)"""
+    import oracle
+    from rnagent_b200 import DotBracket, Solution
+    from rnagent_b200.utils import hamming_distance
+    P = oracle.Params(os.path.join(ROOT, "rnagent_b200", "data", "turner2004_37.par"))
+    cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True)
+    dots = [DotBracket(t, None, k + 1) for k, t in enumerate(targets)]
+    rng = np.random.default_rng(seed)
+    sols = [Solution(target=dots[int(rng.integers(len(dots)))], config=cfg) for _ in range(n_envs)]
+    steps = episodes = 0
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < budget_s:
+        acts = rng.integers(0, 4, n_envs)
+        for e in range(n_envs):
+            sol = sols[e]
+            sol.insert_nucleotide(int(acts[e]))
+            if sol.index < sol.target.len - 1:
+                sol.find_next_unfilled()
+            else:
+                folded, fe = P.fold(sol.string)
+                hd, _ = hamming_distance(sol.target.seq, folded)
+                sol.r = (1 - float(hd) / float(sol.target.len)) ** 9 + (.25 if hd == 0 else 0)
+                episodes += 1
+                sols[e] = sol = Solution(target=dots[int(rng.integers(len(dots)))], config=cfg)
+            sol.get_state()
+            steps += 1
+    dt = time.perf_counter() - t0
+    return steps / dt, episodes / dt, steps
+
+
+def measured_traffic(kernel_key):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the named kernel from this build's
+    `ncu --set full` capture, as summarised in profiles/r2_traffic.json (tools/ncu_summary.py) -> (bytes per fold, source)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))[kernel_key]
+        return (t["dram_read_bytes"] + t["dram_write_bytes"]) / t["folds"], t.get("source")
+    except (OSError, KeyError, ValueError):
+        return None, None
+
+
 def run_reference(args):
     """`--impl reference`: CPU path on all host threads, rank 0 only; same metric/unit/config."""
     rank = int(os.environ.get("RANK", "0"))
@@ -148,7 +219,7 @@ def run_reference(args):
         "impl": "reference", "metric": f"mfe_folds_per_sec_n{n_label}", "value": value, "unit": "folds/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": desc, "sample_per_step": sample},
+        "config": {"workload": desc, "sample_per_step": sample, "us_per_fold_per_thread": 1e6 * cores / value},
         "cpu_baseline": {"value": value, "unit": "folds/s", "cores": cores, "kind": "port",
                          "sample": f"first {sample} sequences of the workload per step, OpenMP over {cores} host threads; "
                                    "oracle port of ViennaRNA 2.4.14 RNA.fold (ViennaRNA itself is not in the "
@@ -263,7 +334,8 @@ def run_ours(args):
     # ---- the other two figures BASELINE.json's metric names: folds/s at n=400 and RL env steps/s
     extra = {}
     if args.workload == "c2" and not args.no_extra:
-        extra = secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_over_ranks)
+        extra = secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_over_ranks,
+                                  cpu_budget=0.0 if (world > 1 or args.no_cpu) else max(3.0, args.cpu_seconds / 2))
 
     if rank != 0:
         if world > 1:
@@ -281,15 +353,25 @@ def run_ours(args):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_bytes = float(sum(synth.algorithmic_hbm_bytes(int(n)) for n in np.diff(off)))
-    # dram__bytes_read.sum + dram__bytes_write.sum of the fold kernel from the committed `ncu --set full` capture
-    # (profiles/r1_v16_wave16_full.txt: 5.12 MB read, 0 written for 23,680 folds of n = 100), scaled to this launch
-    traffic = (5122304.0 / 23680.0) * B if args.workload == "c2" else None
+    per_fold, traffic_src = measured_traffic({"c2": "wave_n100", "c3": "cluster_n400"}.get(args.workload, ""))
+    traffic = per_fold * B if per_fold is not None else None
+    w_exec = w_alg = w_kern = None
+    if world == 1 and not args.no_cpu:
+        w_exec, w_alg, w_kern = cpu_executed_candidates(seq, off, setno)
     roofline = {
         "bound": "smem-load/int32-alu (on-chip; neither hbm nor tensor binds this integer min-plus DP)",
         "achieved": cand_per_s / 1e9, "peak": lds_peak / 1e9, "unit": "G min-plus candidates/s (1 shared load each)",
         "frac": cand_per_s / lds_peak, "peak_source": "conflict-free ld.shared.b32 stream measured on this device by bench.py",
         "alu_peak": alu_peak / 1e9, "alu_frac": cand_per_s / alu_peak,
-        "work_per_launch": W, "kernel_ms": k_ms, "traffic": traffic,
+        "work_per_launch": W, "kernel_ms": k_ms, "traffic": traffic, "traffic_source": traffic_src,
+        "frac_is": "ALGORITHMIC candidates (every cell, every interior shape) per second / measured shared-load peak; the "
+                   "kernel skips unpairable cells, so executed shared loads are fewer -- see w_eff",
+        "w_eff": None if w_exec is None else {
+            "algorithmic_per_fold": w_alg, "oracle_executed_per_fold": w_exec, "oracle_ratio": w_exec / w_alg,
+            "kernel_executed_per_fold": w_kern, "kernel_ratio": w_kern / w_alg,
+            "kernel_executed_per_s": cand_per_s * w_kern / w_alg / 1e9, "kernel_executed_frac_of_peak": cand_per_s * w_kern / w_alg / lds_peak,
+            "source": "first 48 sequences: the CPU oracle's candidate counter (outer AND inner pair pairable), and the count of "
+                      "what the GPU kernels load (interior candidates of cells whose outer ends pair + every multiloop split)"},
         "hbm": {"bound": "hbm", "achieved": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650 GB/s"},
@@ -300,14 +382,14 @@ def run_ours(args):
         r, cores, sample, dt = cpu_fold_rate(seq, off, tgt, setno, args.cpu_seconds)
         cpu = {"value": r, "unit": "folds/s", "cores": cores, "kind": "port",
                "sample": f"first {sample} sequences of the same workload, {dt:.1f} s on {cores} host threads (OpenMP), "
-                         "oracle port of ViennaRNA RNA.fold"}
+                         f"oracle port of ViennaRNA RNA.fold, {1e6 * cores / r:.0f} us per fold per thread"}
 
     n_label = WORKLOADS[args.workload][1] or "mixed"
     line = {
         "metric": f"mfe_folds_per_sec_n{n_label}", "value": world * B * args.steps / (resident_ms * 1e-3),
         "unit": "folds/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": resident_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "int32", "data": "synthetic",
+        "dtype": "int16 tables / int32 arithmetic (int32 re-run of sequences that leave the int16 range)", "data": "synthetic",
         "config": {"workload": desc, "folds_per_gpu_per_step": B, "l2": "flushed between timed steps (256 MiB memset)",
                    "parallelism": f"dp{world} (independent shards, no data-path collective)"},
         "e2e": {"value": world * B * args.steps / e2e_s, "unit": "folds/s", "h2d_bytes_per_step": h2d,
@@ -322,10 +404,15 @@ def run_ours(args):
     return 0
 
 
-def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_over_ranks):
+def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_over_ranks, cpu_budget=0.0):
     """n=400 fold rate (config C3) and RL environment steps/s (config C4), every rank on its own shard."""
     import rnagent_b200
     out = {}
+    lds_peak, _alu = _lib.measure_onchip_peaks()
+
+    def roof(cand_per_s_one_gpu, note):
+        return {"bound": "smem-load (on-chip)", "achieved": cand_per_s_one_gpu / 1e9, "peak": lds_peak / 1e9,
+                "unit": "G min-plus candidates/s (1 shared load each), per GPU", "frac": cand_per_s_one_gpu / lds_peak, "note": note}
     # C3: 8192 x n=400 per GPU, device-resident, 2 timed passes
     seq, off, tgt, setno, desc = make_workload("c3", rank)
     vienna.set_vienna_params(setno)
@@ -351,9 +438,17 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
         e1.synchronize()
     ms = max_over_ranks(e0.elapsed_time(e1))
     W = total_work(off)
+    k400 = _lib.last_kernel_ms()
+    tr400, tr400_src = measured_traffic("cluster_n400")
     out["n400"] = {"metric": "mfe_folds_per_sec_n400", "value": world * 2 * B / (ms * 1e-3), "unit": "folds/s",
                    "workload": desc, "ms_per_pass": ms / 2, "candidates_per_s": world * 2 * W / (ms * 1e-3),
-                   "routed": _lib.last_launch_info()[1]}
+                   "routed": _lib.last_launch_info()[1], "kernel_ms": k400,
+                   "roofline": dict(roof(W / (k400 * 1e-3), "fold_cluster_kernel (2-CTA cluster, DSMEM) + f5_backtrack_kernel + int32 re-run, CUDA events around the launches"),
+                                    traffic=None if tr400 is None else tr400 * B, traffic_source=tr400_src)}
+    if cpu_budget > 0 and rank == 0:
+        r, cores, sample, dt = cpu_fold_rate(seq, off, tgt, setno, cpu_budget)
+        out["n400"]["cpu_baseline"] = {"value": r, "unit": "folds/s", "cores": cores, "kind": "port",
+                                       "sample": f"first {sample} sequences, {dt:.1f} s on {cores} host threads, {1e3 * cores / r:.1f} ms per fold per thread"}
     # C5: Turner 1999, Eterna100-shaped length mix 12..400 (wave, cluster and re-run kernels in one call)
     seq5, off5, tgt5, setno5, desc5 = make_workload("c5", rank)
     vienna.set_vienna_params(setno5)
@@ -372,9 +467,11 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
         e1.record(st)
         e1.synchronize()
     ms5 = max_over_ranks(e0.elapsed_time(e1))
+    k5 = _lib.last_kernel_ms()
     out["mixed"] = {"metric": "mfe_folds_per_sec_mixed_12_400", "value": world * B5 / (ms5 * 1e-3), "unit": "folds/s",
                     "workload": desc5, "ms_per_pass": ms5, "candidates_per_s": world * total_work(off5) / (ms5 * 1e-3),
-                    "routed": _lib.last_launch_info()[1]}
+                    "routed": _lib.last_launch_info()[1], "launches": _lib.last_launch_info()[0], "kernel_ms": k5,
+                    "roofline": roof(total_work(off5) / (k5 * 1e-3), "all length classes of one call (wave + cluster kernels), CUDA events around the launches")}
     # A8 / N1: batched local search (Solution.permute) over 4096 near misses of n=100, the reference's Testing.yml settings
     vienna.set_vienna_params(1)
     rngp = np.random.default_rng(515 + rank)
@@ -399,7 +496,8 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
                       "solved_by_search": int(((res.hd == 0) & (res.rounds > 0)).sum()),
                       "workload": "4096 near misses (1-3 point mutations of a solving sequence) of n=100 per GPU, "
                                   "permutation_budget 15, radius 5, threshold 15, GU allowed (rlif/config/Testing.yml:3-8); "
-                                  "host strings in, host strings out"}
+                                  "host strings in, host strings out",
+                      "roofline": roof(res.folds * synth.work_candidates(100) / psecs, "one batched fold per search round; wall clock incl. host strings")}
     # C4: 4096 environments per GPU, n=100 targets (folds of random sequences), random actions, auto-reset
     vienna.set_vienna_params(1)
     sseq, soff = synth.random_sequences(256, 100, 4100 + rank)
@@ -426,10 +524,43 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
     stats = env.stats().all_reduce(device=dev)          # the path's only collective: rollout statistics over NCCL
     env.close()
     out["env"] = {"metric": "rl_env_steps_per_sec", "value": stats.steps / secs, "unit": "env steps/s",
+                  "per_gpu": stats.steps / secs / world, "us_per_vector_step": 1e6 * secs / steps,
                   "episodes_per_s": stats.episodes / secs, "envs_per_gpu": N, "steps_timed": steps,
+                  "host_syncs_per_step": 0,
+                  "roofline": roof(stats.episodes / secs / world * synth.work_candidates(100),
+                                   "terminal folds only (one per episode); the step is bound by ONE fold's latency, not by throughput"),
                   "workload": "4096 RnaDesign envs per GPU, n=100 targets (folds of random sequences), uniform random actions, "
                               "auto-reset, steady state (300 untimed steps first); observations, rewards and dones stay on the device",
                   "stats": stats.summary()}
+    if cpu_budget > 0 and rank == 0:
+        r_steps, r_eps, n_steps = cpu_env_rate(targets, cpu_budget)
+        out["env"]["cpu_baseline"] = {"value": r_steps, "unit": "env steps/s", "cores": 1, "kind": "port", "episodes_per_s": r_eps,
+                                      "sample": f"{n_steps} steps of 32 environments in one Python process (one SubprocVecEnv worker of the "
+                                                "reference): host state machine of Solution + oracle fold at the terminal step"}
+    # second C4 point: the C5 length mix as targets
+    lens = synth.eterna_mixed_lengths(128, 77 + rank)
+    mseq, moff = synth.random_sequences_mixed(lens, 4200 + rank)
+    mtargets, _ = rnagent_b200.fold_batch([mseq[moff[k]:moff[k + 1]].tobytes().decode() for k in range(128)])
+    env = rnagent_b200.RnaDesignBatch(cfg, N, targets=mtargets, rank=rank, auto_reset=True, randomize=True, seed=rank)
+    msteps, msettle = 120, 400
+    macts = torch.randint(0, 4, (msteps + msettle, N), dtype=torch.int32, device=dev, generator=g)
+    env.reset()
+    for k in range(msettle):
+        env.step_device(macts[k], d_obs, d_r, d_done)
+    env.stats(clear=True)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(msteps):
+        env.step_device(macts[msettle + k], d_obs, d_r, d_done)
+    torch.cuda.synchronize()
+    msecs = max_over_ranks(time.perf_counter() - t0)
+    mstats = env.stats().all_reduce(device=dev)
+    env.close()
+    out["env_mixed"] = {"metric": "rl_env_steps_per_sec_mixed_targets", "value": mstats.steps / msecs, "unit": "env steps/s",
+                        "per_gpu": mstats.steps / msecs / world, "us_per_vector_step": 1e6 * msecs / msteps,
+                        "episodes_per_s": mstats.episodes / msecs, "envs_per_gpu": N, "steps_timed": msteps,
+                        "workload": "4096 RnaDesign envs per GPU, targets = folds of 128 random sequences with the Eterna100 length mix "
+                                    "(12-400 nt), uniform random actions, auto-reset, 400 untimed steps first"}
     return out
 
 

@@ -129,7 +129,7 @@ def test_environment_with_permute():
     better = 0
     for e in range(N):
         a, b = plain[e], srch[e]
-        assert b.hd <= a.hd and b.target == a.target
+        assert b.hd <= a.hd and b.target.seq == a.target.seq
         if a.hd == 0 or a.hd > 15:
             assert b.string == a.string and b.folded_structure == a.folded_structure
         assert rb.fold(b.string) == (b.folded_structure, b.fe)
