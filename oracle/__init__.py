@@ -18,7 +18,7 @@ _lib = None
 
 
 def build(force=False):
-    src = [os.path.join(_HERE, f) for f in ("rnafold_oracle.c", "rnafold_oracle.h", "Makefile")]
+    src = [os.path.join(_HERE, f) for f in ("rnafold_oracle.c", "rnafold_pf.c", "rnafold_oracle.h", "Makefile")]
     if (not force and os.path.exists(_SO)
             and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in src)):
         return _SO
@@ -45,6 +45,12 @@ def lib():
         L.orc_fold_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                      ctypes.c_int]
+        L.orc_pf.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_int, ctypes.c_int,
+                             ctypes.c_void_p, ctypes.c_char_p, ctypes.c_void_p]
+        L.orc_dist_mountain.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_int]
+        L.orc_dist_mountain.restype = ctypes.c_double
+        L.orc_pf_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                   ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
         _lib = L
     return _lib
 
@@ -94,6 +100,37 @@ class Params:
     def last_candidates(self):
         return int(self._L.orc_last_fold_candidates())
 
+    PF_STATS = ("ensemble_energy", "ensemble_defect", "probability", "ensemble_diversity", "centroid_dist")
+
+    def pf(self, seq, structure, e_dcal, smooth=True, bpp=False):
+        """Ensemble statistics of Solution.compute_statistics (rlif/rna/solution.py:221-238) for `seq`, with `structure`
+        (its MFE fold) and that structure's energy in dcal/mol -> dict (+ 'centroid_structure', + 'bpp' n x n if asked)."""
+        n = len(seq)
+        stats = np.zeros(5, dtype=np.float64)
+        cen = ctypes.create_string_buffer(n + 1)
+        mat = np.zeros((n, n), dtype=np.float64) if bpp else None
+        rc = self._L.orc_pf(self._p, seq.encode(), n, structure.encode(), int(e_dcal), 1 if smooth else 0, stats.ctypes.data,
+                            cen, mat.ctypes.data if bpp else None)
+        if rc:
+            raise RuntimeError("orc_pf failed")
+        out = dict(zip(self.PF_STATS, (float(v) for v in stats)))
+        out["centroid_structure"] = cen.value.decode()
+        if bpp:
+            out["bpp"] = mat
+        return out
+
+    def pf_batch(self, seqs_u8, off, structs_u8, mfe_dcal, smooth=True, nthreads=0):
+        B = len(off) - 1
+        out = np.zeros((B, 5), dtype=np.float64)
+        seqs_u8, structs_u8 = np.ascontiguousarray(seqs_u8), np.ascontiguousarray(structs_u8)
+        off = np.ascontiguousarray(off, dtype=np.int32)
+        e = np.ascontiguousarray(mfe_dcal, dtype=np.int32)
+        rc = self._L.orc_pf_batch(self._p, seqs_u8.ctypes.data, off.ctypes.data, B, structs_u8.ctypes.data, e.ctypes.data,
+                                  1 if smooth else 0, out.ctypes.data, int(nthreads))
+        if rc:
+            raise RuntimeError("orc_pf_batch failed")
+        return out
+
     def eval_structure(self, seq, db):
         e = ctypes.c_int(0)
         rc = self._L.orc_eval_structure(self._p, seq.encode(), len(seq), db.encode(), ctypes.byref(e))
@@ -131,3 +168,10 @@ def hamming_distance(a, b):
     """rlif/rna/utils.py:67-75 restated: zip-truncating; returns (hd, mismatch indices)."""
     m = [x != y for x, y in zip(a, b)]
     return sum(m), np.where(m)[0]
+
+
+def dist_mountain(a, b, weighted=True):
+    """RNA.dist_mountain(a, b) as used by Solution.compute_statistics (rlif/rna/solution.py:238)."""
+    if len(a) != len(b):
+        raise ValueError("structures of unequal length")
+    return float(lib().orc_dist_mountain(a.encode(), b.encode(), len(a), 1 if weighted else 0))

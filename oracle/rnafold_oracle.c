@@ -272,6 +272,10 @@ int orc_params_load(orc_params *P, const char *path) {
 
   /* ViennaRNA get_scaled_params at 37 C with dangles != 0: exterior/multiloop mismatches and
    * dangles are bonuses only (clamped to <= 0). */
+  memcpy(P->raw_mismatchM, P->mismatchM, sizeof(P->mismatchM));
+  memcpy(P->raw_mismatchExt, P->mismatchExt, sizeof(P->mismatchExt));
+  memcpy(P->raw_dangle5, P->dangle5, sizeof(P->dangle5));
+  memcpy(P->raw_dangle3, P->dangle3, sizeof(P->dangle3));
   for (int p = 0; p < 8; p++)
     for (int a = 0; a < 5; a++) {
       if (P->dangle5[p][a] > 0) P->dangle5[p][a] = 0;

@@ -46,6 +46,8 @@ typedef struct orc_params {
   char tri[ORC_MAXSPECIAL][8];
   char hexa[ORC_MAXSPECIAL][12];
   int tetra_E[ORC_MAXSPECIAL], tri_E[ORC_MAXSPECIAL], hexa_E[ORC_MAXSPECIAL];
+  /* as read from the file, before the <= 0 clamp of the MFE model (the partition function smooths them instead) */
+  int raw_mismatchM[8][5][5], raw_mismatchExt[8][5][5], raw_dangle5[8][5], raw_dangle3[8][5];
 } orc_params;
 
 /* Allocate / free a parameter set (zero-initialised; must be loaded before use). */
@@ -82,6 +84,26 @@ int orc_hamming(const char *a, int na, const char *b, int nb, unsigned char *mis
  * bytes with CSR offsets off[B+1]; targets may be NULL.  db_out has the same layout as seqs. */
 int orc_fold_batch(const orc_params *P, const char *seqs, const int *off, int B, const char *targets,
                    char *db_out, int *mfe_out, int *hd_out, int nthreads);
+
+/* ---- ensemble statistics (rnafold_pf.c): Solution.compute_statistics, rlif/rna/solution.py:221-238 --------------
+ * McCaskill partition function of the same loop model (dangles=2) + base-pair probabilities.
+ * PARITY PIN: the `ed` (ensemble defect of the MFE structure) and `md` (mountain distance target <-> MFE structure)
+ * columns of the same 1,726 logged rows (written by rlif/utils/comparison.py:225-233 with '{:.3f}').
+ * stats[0] ensemble free energy (kcal/mol)         fc.pf()[1]
+ * stats[1] ensemble defect of `structure`, / n      fc.ensemble_defect(fold)
+ * stats[2] probability of `structure`               fc.pr_structure(fold)   (needs its energy: e_dcal)
+ * stats[3] mean base-pair distance                  fc.mean_bp_distance()
+ * stats[4] distance of the centroid to the ensemble fc.centroid()[1]
+ * centroid (n + 1 bytes, may be NULL): pairs with p > 0.5; bpp (may be NULL): n * n doubles, row-major, 0-based, upper triangle.
+ * smooth != 0: ViennaRNA's SMOOTH() of the dangle / multiloop- and exterior-mismatch terms in the Boltzmann factors. */
+#define ORC_PF_NSTATS 5
+int orc_pf(const orc_params *P, const char *seq, int n, const char *structure, int e_dcal, int smooth, double *stats,
+           char *centroid, double *bpp);
+/* RNA.dist_mountain(a, b): L1 distance of the mountain functions; weighted != 0: a pair (i, j) raises by 1 / (j - i). */
+double orc_dist_mountain(const char *a, const char *b, int n, int weighted);
+/* Batched (OpenMP): stats_out[B][ORC_PF_NSTATS]; structures / e_dcal as returned by orc_fold_batch. */
+int orc_pf_batch(const orc_params *P, const char *seqs, const int *off, int B, const char *structures, const int *e_dcal,
+                 int smooth, double *stats_out, int nthreads);
 
 #ifdef __cplusplus
 }
