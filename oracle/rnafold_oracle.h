@@ -90,7 +90,7 @@ int orc_fold_batch(const orc_params *P, const char *seqs, const int *off, int B,
  * PARITY PIN: the `ed` (ensemble defect of the MFE structure) and `md` (mountain distance target <-> MFE structure)
  * columns of the same 1,726 logged rows (written by rlif/utils/comparison.py:225-233 with '{:.3f}').
  * stats[0] ensemble free energy (kcal/mol)         fc.pf()[1]
- * stats[1] ensemble defect of `structure`, / n      fc.ensemble_defect(fold)
+ * stats[1] ensemble defect of `structure`, / n      fc.ensemble_defect(fold)   (2.4.14 leaves position n out of the sum)
  * stats[2] probability of `structure`               fc.pr_structure(fold)   (needs its energy: e_dcal)
  * stats[3] mean base-pair distance                  fc.mean_bp_distance()
  * stats[4] distance of the centroid to the ensemble fc.centroid()[1]
@@ -99,7 +99,7 @@ int orc_fold_batch(const orc_params *P, const char *seqs, const int *off, int B,
 #define ORC_PF_NSTATS 5
 int orc_pf(const orc_params *P, const char *seq, int n, const char *structure, int e_dcal, int smooth, double *stats,
            char *centroid, double *bpp);
-/* RNA.dist_mountain(a, b): L1 distance of the mountain functions; weighted != 0: a pair (i, j) raises by 1 / (j - i). */
+/* RNA.dist_mountain(a, b) as ViennaRNA 2.4.14 computes it (see rnafold_pf.c); weighted must be non-zero for parity. */
 double orc_dist_mountain(const char *a, const char *b, int n, int weighted);
 /* Batched (OpenMP): stats_out[B][ORC_PF_NSTATS]; structures / e_dcal as returned by orc_fold_batch. */
 int orc_pf_batch(const orc_params *P, const char *seqs, const int *off, int B, const char *structures, const int *e_dcal,

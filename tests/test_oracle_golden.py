@@ -119,3 +119,79 @@ def test_hd_unpinned_rows_fixture(golden_rows, golden_folds, oracle_params):
             assert (s, e) == (v["structure"], v["dcal"])
         assert not any(v["hd"] == r["hd"] and v["fe_matches"] for v in r["per_set"].values())
     assert sum(not r["per_set"][r["params"]]["target_is_cooptimal"] for r in rows) == 22
+
+
+def test_logged_ensemble_defect_and_mountain_distance(golden_rows, golden_folds, oracle_params):
+    """Row N3 (Solution.compute_statistics, rlif/rna/solution.py:221-238): the `ed` and `md` columns of the reference's
+    logs (rlif/utils/comparison.py:225-233, '{:.3f}') against the partition-function oracle.  Every row whose HD reproduces
+    (1,697 of 1,726; the others carry an HD from another evaluation, see test_hd_unpinned_rows_fixture) matches to 5e-4
+    on both columns, 12..451 nt, both parameter sets."""
+    import oracle
+    checked = 0
+    for name in ("turner2004", "turner1999"):
+        P = oracle_params(name)
+        idx = [k for k, r in enumerate(golden_rows) if r["params"] == name
+               and sum(a != b for a, b in zip(golden_folds[k][0], r["target"])) == r["hd"]]
+        seqs = [golden_rows[k]["seq"] for k in idx]
+        buf = np.frombuffer("".join(seqs).encode(), dtype=np.uint8)
+        dbs = np.frombuffer("".join(golden_folds[k][0] for k in idx).encode(), dtype=np.uint8)
+        off = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int32)
+        mfe = np.array([golden_folds[k][1] for k in idx], dtype=np.int32)
+        stats = P.pf_batch(buf, off, dbs, mfe, smooth=True, nthreads=0)
+        for n_, k in enumerate(idx):
+            r = golden_rows[k]
+            assert abs(stats[n_][1] - float(r["ed"])) <= 0.00051, (r["file"], r["line"], r["ed"], stats[n_][1])
+            md = oracle.dist_mountain(r["target"], golden_folds[k][0])
+            assert abs(md - float(r["md"])) <= 0.00051, (r["file"], r["line"], r["md"], md)
+            assert stats[n_][0] <= mfe[n_] / 100.0 + 1e-9 and 0 < stats[n_][2] <= 1.0 + 1e-9     # F <= MFE, 0 < p(mfe) <= 1
+            checked += 1
+    assert checked == 1697
+
+
+def test_partition_function_against_enumeration(oracle_params):
+    """Z and every base-pair probability against an explicit sum over all structures (n <= 15), on the integer energies of
+    the independent loop evaluator (smooth=False: the same energy model as the MFE recursions)."""
+    import math
+    P = oracle_params("turner2004")
+    kT = (37 + 273.15) * 1.98717
+    pairs = {"AU", "UA", "CG", "GC", "GU", "UG"}
+
+    def structures(n):
+        out, cur, stack = [], [], []
+
+        def rec(i):
+            if i == n:
+                if not stack:
+                    out.append("".join(cur))
+                return
+            cur.append("."); rec(i + 1); cur.pop()
+            cur.append("("); stack.append(i); rec(i + 1); stack.pop(); cur.pop()
+            if stack and i - stack[-1] > 3:
+                o = stack.pop(); cur.append(")"); rec(i + 1); cur.pop(); stack.append(o)
+        rec(0)
+        return out
+    rng = np.random.default_rng(11)
+    for trial in range(8):
+        n = int(rng.integers(10, 16))
+        seq = "".join(rng.choice(list("ACGU" if trial % 2 else "GCGCAU"), n))
+        Z, pij = 0.0, np.zeros((n, n))
+        for st in structures(n):
+            stack, pl, ok = [], [], True
+            for k, ch in enumerate(st):
+                if ch == "(":
+                    stack.append(k)
+                elif ch == ")":
+                    o = stack.pop()
+                    ok = ok and (seq[o] + seq[k]) in pairs
+                    pl.append((o, k))
+            if not ok:
+                continue
+            w = math.exp(-P.eval_structure(seq, st) * 10 / kT)
+            Z += w
+            for o, k in pl:
+                pij[o, k] += w
+        s, e = P.fold_dcal(seq)
+        r = P.pf(seq, s, e, smooth=False, bpp=True)
+        assert abs(r["ensemble_energy"] + kT * math.log(Z) / 1000) < 1e-9
+        assert np.abs(r["bpp"] - pij / Z).max() < 1e-12
+        assert abs(r["probability"] - math.exp(-e * 10 / kT) / Z) < 1e-12
