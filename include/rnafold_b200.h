@@ -190,6 +190,23 @@ uint64_t rnafold_permute_draw(uint64_t seed, int32_t index, int32_t step, int32_
 int rnafold_env_config_permute(int32_t handle, int32_t enabled, int32_t budget, int32_t radius, int32_t threshold,
                                double mutation_probability, int32_t allow_gu);
 
+/* ---- Ensemble statistics: Solution.compute_statistics (rlif/rna/solution.py:221-238; printed by rlif/CLI.py:42-49, logged
+ * as the `md` / `ed` columns by rlif/utils/comparison.py:225-233) for a batch: McCaskill partition function and base-pair
+ * probabilities of the same loop model (dangles=2), fp64 on the GPU.  `structure` / `e_dcal` are the fold and energy of every
+ * sequence (what rnafold_fold_batch returns: fc.mfe()); `target` (may be NULL) the dot-bracket targets for the mountain
+ * distance.  stats_out[B][6] = { ensemble free energy kcal/mol (fc.pf()[1]), ensemble defect of `structure`
+ * (fc.ensemble_defect(fold)), its probability (fc.pr_structure(fold)), mean base-pair distance (fc.mean_bp_distance()),
+ * distance of the centroid to the ensemble (fc.centroid()[1]), mountain distance RNA.dist_mountain(target, fold) }.
+ * Optional: centroid_out (CSR bytes like seq: pairs with p > 0.5, fc.centroid()[0]); pos_out[total][3] = P(paired with a
+ * base downstream), P(paired upstream), positional entropy in bits (fc.positional_entropy(); the first two give the pair
+ * propensity string of fc.pf()[0]); bpp_out (single-sequence calls only: n x n row-major, upper triangle).
+ * off must be a host array; the other buffers may be host or device pointers.  Synchronous.  MEA structures and
+ * eval_structure of the centroid (solution.py:231-233) are not part of this entry point. */
+#define RNAFOLD_ENSEMBLE_MAX_LEN 1000
+int rnafold_ensemble_batch(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *structure,
+                           const int32_t *e_dcal, const uint8_t *target, double *stats_out, uint8_t *centroid_out,
+                           double *pos_out, double *bpp_out);
+
 /* Measurement helper (bench.py): on-box peaks of the two on-chip resources that bound the fold DP,
  * whole device: conflict-free 4-byte shared-memory loads per second and integer add+min
  * (min-plus candidate) updates per second. */

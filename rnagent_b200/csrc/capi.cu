@@ -742,6 +742,18 @@ void fold_dyn_plan_free(void *plan) { delete (DynPlanImpl *)plan; }
 // device address of the sticky status word (env.cu reads it with its end-of-step copies)
 const int32_t *status_word() { return g_ctx ? g_ctx->d_status : nullptr; }
 
+int ctx_view(CtxView *out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g_ctx) return -1;
+  out->device = g_ctx->device;
+  out->num_sms = g_ctx->num_sms;
+  out->stream = g_ctx->stream;
+  out->hp = &g_ctx->hp;
+  out->d_params = g_ctx->d_params;
+  out->params_epoch = g_ctx->params_epoch;
+  return 0;
+}
+
 // error channel shared with env.cu
 int set_error(int code, const char *msg) {
   g_err = msg ? msg : "";

@@ -76,6 +76,16 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
 void fold_dyn_plan_free(void *plan);
 const int32_t *status_word();
 
+// capi.cu: what other translation units need from the per-process context (ensemble.cu)
+struct CtxView {
+  int device, num_sms;
+  cudaStream_t stream;
+  const HostParams *hp;        // live parameter set (host copy)
+  const FoldParams *d_params;  // ... and its device copy
+  uint64_t params_epoch;       // changes with every parameter upload
+};
+int ctx_view(CtxView *out);    // 0, or non-zero before rnafold_init
+
 // capi.cu: records the message returned by rnafold_last_error() and passes `code` through
 int set_error(int code, const char *msg);
 

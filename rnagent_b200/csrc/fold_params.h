@@ -62,6 +62,10 @@ struct HostParams {
   char tetra[kMaxSpecial][8];
   char tri[kMaxSpecial][8];
   char hexa[kMaxSpecial][12];
+  // dangle / multiloop- and exterior-mismatch tables as read from the file, before the <= 0 clamp of the MFE model
+  // (the partition function passes them through ViennaRNA's SMOOTH() instead, csrc/ensemble.cu)
+  int32_t raw_mmM[8][5][5], raw_mmExt[8][5][5], raw_dangle5[8][5], raw_dangle3[8][5];
+  int32_t raw_valid;
 };
 
 // params_io.cpp

@@ -148,6 +148,11 @@ void complete_int22(int32_t a[8][8][5][5][5][5]) {
 
 void finalize_params(HostParams *hp) {
   SmallParams &s = hp->dev.s;
+  std::memcpy(hp->raw_mmM, s.mmM, sizeof(s.mmM));
+  std::memcpy(hp->raw_mmExt, s.mmExt, sizeof(s.mmExt));
+  std::memcpy(hp->raw_dangle5, s.dangle5, sizeof(s.dangle5));
+  std::memcpy(hp->raw_dangle3, s.dangle3, sizeof(s.dangle3));
+  hp->raw_valid = 1;
   for (int p = 0; p < 8; ++p)
     for (int a = 0; a < 5; ++a) {
       if (s.dangle5[p][a] > 0) s.dangle5[p][a] = 0;
@@ -177,6 +182,12 @@ int parse_parameter_text(const char *text, size_t len, HostParams *hp, char *err
   }
   FoldParams &d = hp->dev;
   SmallParams &s = d.s;
+  if (hp->raw_valid) {  // sections absent from this file keep the live values: un-clamp them first
+    std::memcpy(s.mmM, hp->raw_mmM, sizeof(s.mmM));
+    std::memcpy(s.mmExt, hp->raw_mmExt, sizeof(s.mmExt));
+    std::memcpy(s.dangle5, hp->raw_dangle5, sizeof(s.dangle5));
+    std::memcpy(s.dangle3, hp->raw_dangle3, sizeof(s.dangle3));
+  }
   const std::vector<int> i_mm = idx_pairs_bases(2), i_dg = idx_pairs_bases(1);
   std::vector<int> i_stack;
   for (int p = 1; p <= 7; ++p)

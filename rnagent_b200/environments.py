@@ -207,7 +207,8 @@ class RnaDesignBatch(object):
         if name == 'boosting' and value:
             raise NotImplementedError("boosting=True is not on the batched path")
         if name == 'testing_mode' and value:
-            raise NotImplementedError("testing_mode=True (partition-function statistics) is not on the batched path")
+            raise NotImplementedError("testing_mode=True computes the ensemble statistics of every terminal solution inside step(); "
+                                      "call rnagent_b200.ensemble_batch on env.get_attr('prev_solution') instead")
         setattr(self, name, value)
         if name in ('randomize', 'auto_reset', 'seed', 'permute', 'config'):
             self._configure()

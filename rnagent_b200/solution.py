@@ -60,12 +60,13 @@ class Solution(object):
         self.kernel_size = self.config.get('kernel_size', 25)
         self.index = 0
         self.permute_seed = int(self.config.get('permute_seed', 0))
+        self.init_vars()
         self.create_encoding()
         if self.config_check('boosting'):
             raise NotImplementedError("boosting (forgi graph heuristics) is not part of this path")
         if string is not None:
             self.str = [x for x in string]
-            self.evaluate(string, permute=False, compute_statistics=False)
+            self.evaluate(string, permute=False, compute_statistics=True)   # as the reference (solution.py:44-46)
         if time is None:
             self.start = t.time()
 
@@ -115,8 +116,6 @@ class Solution(object):
     def evaluate(self, string=None, permute=False, compute_statistics=False, boost=False, reward=False, verbose=False):
         if boost:
             raise NotImplementedError("boosting is not part of this path")
-        if compute_statistics:
-            raise NotImplementedError("ensemble statistics (partition function) are not part of this path")
         if string is None:
             string = self.string
         tgt = self.target.seq
@@ -132,6 +131,8 @@ class Solution(object):
         else:
             structs, mfe, hd, mism, _ = fold_hamming_batch([string], [tgt], reward_exp=self.reward_exp)
             self.folded_structure, self.fe, self.hd, self.mismatch_indices = structs[0], float(mfe[0]), int(hd[0]), mism[0]
+        if compute_statistics:
+            self.compute_statistics()
         if reward:
             self.r = (1 - float(self.hd) / float(self.target.len)) ** self.reward_exp
             gcau = self.gcau_content()
@@ -151,6 +152,25 @@ class Solution(object):
         if res.hd[0] == 0 and res.rounds[0] > 0:
             self.source = 'rlif*'
         return list(res.sequences[0]), int(res.hd[0])
+
+    # ---- solution.py:221-238 (and init_vars, :240-255)
+    def init_vars(self):
+        for name in ('probability', 'positional_entropy', 'partition_prob', 'partition_fn', 'centroid_structure', 'centroid_dist',
+                     'centroid_en', 'MEA_structure', 'MEA', 'MEA_en', 'ensemble_diversity', 'ensemble_defect'):
+            setattr(self, name, None)
+
+    def compute_statistics(self):
+        """Partition function, centroid, ensemble defect / diversity, mountain distance of the current string on the GPU
+        (rnafold_ensemble_batch).  centroid_en and the MEA_* attributes stay None (not built)."""
+        from .ensemble import ensemble_batch
+        res = ensemble_batch([self.string], targets=[self.target.seq])
+        self.partition_prob, self.partition_fn = res.propensity[0], float(res.ensemble_energy[0])
+        self.positional_entropy = res.positional_entropy[0]
+        self.centroid_structure, self.centroid_dist = res.centroid_structure[0], float(res.centroid_dist[0])
+        self.probability = float(res.probability[0])
+        self.ensemble_diversity = float(res.ensemble_diversity[0])
+        self.ensemble_defect = float(res.ensemble_defect[0])
+        self.md = float(res.md[0])
 
     def gcau_content(self):
         return gcau_content(self.str)

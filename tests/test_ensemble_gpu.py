@@ -1,0 +1,81 @@
+"""GPU: ensemble statistics (Solution.compute_statistics, rlif/rna/solution.py:221-238) through rnafold_ensemble_batch against
+the reference's logged `ed` / `md` columns and against the CPU oracle (oracle/rnafold_pf.c).  Floating point: fp64 on both
+sides, different summation orders -> relative tolerance 1e-9 against the oracle, 5e-4 (the logs' three decimals) against the logs."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-9
+
+
+def test_logged_ed_and_md_columns(golden_rows):
+    """All logged rows whose HD reproduces (1,697): ensemble defect and mountain distance to 5e-4, 12..451 nt, both sets."""
+    import rnagent_b200 as rb
+    checked = 0
+    for setno, name in ((1, "turner2004"), (2, "turner1999")):
+        rb.set_vienna_params(setno)
+        rows = [r for r in golden_rows if r["params"] == name]
+        res = rb.ensemble_batch([r["seq"] for r in rows], targets=[r["target"] for r in rows])
+        for k, r in enumerate(rows):
+            if rb.hamming_distance(r["target"], res.structures[k])[0] != r["hd"]:
+                continue
+            assert abs(res.ensemble_defect[k] - float(r["ed"])) <= 0.00051, (r["file"], r["line"], r["ed"], res.ensemble_defect[k])
+            assert abs(res.md[k] - float(r["md"])) <= 0.00051, (r["file"], r["line"], r["md"], res.md[k])
+            checked += 1
+    rb.set_vienna_params(1)
+    assert checked == 1697
+
+
+@pytest.mark.parametrize("setno,name", [(1, "turner2004"), (2, "turner1999"), (3, "andronescu2007")])
+def test_against_the_oracle(oracle_params, setno, name):
+    import oracle
+    import rnagent_b200 as rb
+    rb.set_vienna_params(setno)
+    P = oracle_params(name)
+    rng = np.random.default_rng(40 + setno)
+    lens = [0, 1, 4, 5, 8, 12] + [int(v) for v in rng.integers(13, 140, 90)] + [200, 257, 330]
+    seqs = ["".join(rng.choice(list("ACGU"), n)) for n in lens]
+    seqs[7] = "GGGGAAAACCCC".lower().replace("u", "t")            # case / T handling as the fold
+    seqs[8] = "GCGCNNNNGCGC"                                       # unknown letters never pair
+    from rnagent_b200 import synth
+    targets = [synth.random_structure(len(s), rng).tobytes().decode() if len(s) else "" for s in seqs]
+    res = rb.ensemble_batch(seqs, targets=targets)
+    for k, s in enumerate(seqs):
+        st, e = P.fold_dcal(s)
+        assert (res.structures[k], int(res.mfe[k])) == (st, e)
+        if not s:
+            continue
+        want = P.pf(s, st, e, smooth=True, bpp=True)
+        for key in ("ensemble_energy", "ensemble_defect", "probability", "ensemble_diversity", "centroid_dist"):
+            got = getattr(res, key)[k]
+            assert abs(got - want[key]) <= RTOL * max(1.0, abs(want[key])), (k, len(s), key, got, want[key])
+        assert res.centroid_structure[k] == want["centroid_structure"]
+        assert abs(res.md[k] - oracle.dist_mountain(targets[k], st)) < 1e-12
+        full = want["bpp"] + want["bpp"].T
+        down = np.triu(want["bpp"]).sum(axis=1)
+        assert res.propensity[k] == rb.ensemble.propensity_string(down, full.sum(axis=1) - down)
+        pu = 1.0 - full.sum(axis=1)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            ent = -(np.where(full > 0, full * np.log(full), 0.0).sum(axis=1) + np.where(pu > 0, pu * np.log(pu), 0.0)) / np.log(2.0)
+        assert np.abs(res.positional_entropy[k] - ent).max() < 1e-9
+    one = rb.ensemble_batch([seqs[40]], bpp=True)
+    s40, e40 = P.fold_dcal(seqs[40])
+    assert np.abs(one.bpp - P.pf(seqs[40], s40, e40, bpp=True)["bpp"]).max() < 1e-12 and np.isnan(one.md[0])
+    rb.set_vienna_params(1)
+
+
+def test_solution_compute_statistics_and_limits():
+    import rnagent_b200 as rb
+    from rnagent_b200 import _lib
+    rb.set_vienna_params(1)
+    cfg = dict(kernel_size=25, reward_exp=9, use_nucleotides=True, encoding_type=2)
+    sol = rb.Solution(target="(((((......)))))", config=cfg, string="UGUUGAAGGCCUAACA")   # first row of rlif/logs/eterna/solutions.csv
+    assert (sol.hd, sol.fe) == (0, float(np.float32(-0.8)))
+    assert round(sol.ensemble_defect, 3) == 0.121 and sol.md == 0.0                          # ... and its logged ed / md
+    assert sol.centroid_structure == ".((((......))))." and 0.4 < sol.probability < 0.5      # p(1,16) = 0.47: not in the centroid
+    assert len(sol.partition_prob) == 16 and sol.partition_fn < -0.8 and len(sol.positional_entropy) == 16
+    assert sol.MEA_structure is None and sol.centroid_en is None
+    with pytest.raises(ValueError):
+        rb.ensemble_batch(["A" * 1001])
+    assert len(rb.ensemble_batch([])) == 0
