@@ -79,3 +79,40 @@ def test_solution_compute_statistics_and_limits():
     with pytest.raises(ValueError):
         rb.ensemble_batch(["A" * 1001])
     assert len(rb.ensemble_batch([])) == 0
+
+
+def test_comparison_writer_regenerates_the_reference_log(tmp_path):
+    """Row N4: `solutions.csv` / `<n>.log` of rlif/utils/comparison.py:150-255 from GPU results, against the first block of the
+    reference's own rlif/logs/eterna/solutions.csv (tests/golden/eterna_solutions_head.csv).  The committed log went through a
+    spreadsheet (trailing zeros and the log-name field stripped, padding commas and a per-method tally appended): the block's
+    fields are compared one by one -- strings exactly, numbers as the values our '{:.3f}' text denotes."""
+    import os
+    import rnagent_b200 as rb
+    from conftest import GOLDEN
+    from rnagent_b200 import comparison
+    rb.set_vienna_params(1)
+    ref = [l.rstrip("\n").split(",") for l in open(os.path.join(GOLDEN, "eterna_solutions_head.csv"))]
+    target, limit, length = ref[0][0], ref[0][1], ref[0][2]
+    rows = [r for r in ref[2:] if r[0] and set(r[0]) <= set("ACGU")]
+    assert (target, limit, length) == ("(((((......)))))", "60", "16") and len(rows) == 8 and ref[1][:8] == comparison.COLUMNS
+    logged_t = {r[1]: float(r[2]) for r in rows}
+    t = [0.0]
+
+    def make(seq_out, name):
+        def fn(seq, time_limit=10):
+            t[0] += logged_t[name]       # the method's run time is the logged one (a fake clock): everything else is computed
+            return seq_out
+        return fn
+    names = [r[1] for r in rows]
+    out, log = tmp_path / "solutions.csv", tmp_path / "1.log"
+    solved, times = comparison.mass_fold(target, [make(r[0], r[1]) for r in rows], names, time_limit=int(limit), file=str(out),
+                                         log=str(log), clock=lambda: t[0])
+    assert solved.tolist() == [1.0] * 8
+    got = [l.rstrip("\n").split(",") for l in open(out)]
+    assert got[0] == [target, limit, length, "1"] and got[1] == comparison.COLUMNS and got[-1] == [""]
+    for g, r in zip(got[2:], rows):
+        assert g[0] == r[0] and g[1] == r[1] and g[3] == r[3] and g[7] == r[7]                   # seq, source, hd, attempts
+        assert all(len(g[c].split(".")[1]) == 3 for c in (2, 4, 5, 6))                           # '{:.3f}'
+        assert [float(g[c]) for c in (2, 4, 5, 6)] == [float(r[c]) for c in (2, 4, 5, 6)], (g, r)   # t, md, fe, ed
+    assert [l.split() for l in open(log)] == [[r[0], "%.3f" % float(r[2]), r[1]] for r in rows]
+    assert comparison.timeout_row("NUPACK", 60.0) == "---, NUPACK, 60.000\n"
