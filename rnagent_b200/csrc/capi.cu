@@ -103,7 +103,7 @@ struct Context {
   // model details (RNA.cvar)
   double md_temperature = 37.0, md_dangles = 2, md_noGU = 0, md_no_closingGU = 0, md_uniq_ML = 0;
   // device staging for host-side callers
-  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws, d_redo, d_dyn;
+  DevBuf d_seq, d_off, d_order, d_target, d_db, d_mfe, d_hd, d_reward, d_mismatch, d_ctl, d_ws, d_ws2, d_redo, d_dyn;
   PinBuf h_in, h_out, h_off;
   std::vector<int32_t> off_host, order_host;
   int32_t last_launches = 0, last_routed[3] = {0, 0, 0};
@@ -233,7 +233,8 @@ int cached_occ(Context *c, int family, int nmax, int esz, int threads) {
 // Issue the kernels of one launch record.  `count` is the number of sequences of the launch when the host knows
 // it, otherwise (a.dyn != nullptr: the count lives on the device) an upper bound that sizes grids and workspaces.
 // q: two queue counters (main kernel, range-check re-run).
-int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, BatchArgs a, int32_t *q, cudaStream_t st) {
+int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, BatchArgs a, int32_t *q, cudaStream_t st,
+                 bool with_rerun = true) {
   auto legacy = [&](BatchArgs la, bool smem_tables, int32_t *queue) -> int {
     const int occ = std::max(1, cached_occ(c, 2, L.nmax, smem_tables ? 1 : 0, kCtaThreads));
     const int grid = std::min(count, c->num_sms * occ);
@@ -262,7 +263,7 @@ int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, Batc
     CUDA_TRY(launch_fold_wave(c->d_params, a, L.nmax, lim.wave_esz, grid, threads, q, st));
     c->last_launches++;
     c->last_routed[0] += count;
-    if (lim.wave_esz == 2) {
+    if (lim.wave_esz == 2 && with_rerun) {
       // sequences whose values left the int16 range (flagged on the device) are re-run in int32
       a.redo_filter = 1;
       return legacy(a, L.nmax <= kLegacySmemLimit, q + 1);
@@ -276,6 +277,7 @@ int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, Batc
     CUDA_TRY(launch_f5_backtrack(c->d_params, a, L.nmax, count, cbg, fg, st));
     c->last_launches += 2;
     c->last_routed[1] += count;
+    if (!with_rerun) return RNAFOLD_OK;
     a.redo_filter = 1;  // int16 range violations -> int32 kernel with global tables
     return legacy(a, false, q + 1);
   } else {
@@ -561,12 +563,20 @@ struct RouteTable {
 
 __global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__ count_ptr, const int32_t *__restrict__ total_ptr,
                                                      int32_t *off, int cap, RouteTable rt, int32_t *__restrict__ order,
-                                                     int32_t *__restrict__ dyn) {
+                                                     int32_t *__restrict__ dyn, int32_t *__restrict__ ctl, int nctl,
+                                                     int32_t *__restrict__ redo) {
   __shared__ int cnt[kMaxDynLaunches], beg[kMaxDynLaunches], fill[kMaxDynLaunches];
   const int tid = threadIdx.x;
   const int count = min(max(*count_ptr, 0), cap);
   const int total = total_ptr ? *total_ptr : 0;
   if (tid < kMaxDynLaunches) cnt[tid] = fill[tid] = 0;
+  // queue counters of every launch and this batch's range-check flags start at zero (no separate memsets)
+  for (int k = tid; k < nctl; k += blockDim.x) ctl[k] = 0;
+  for (int s = tid; s < count; s += blockDim.x) redo[s] = 0;
+  if (tid == 0) {   // entry rt.nl: the whole batch (the single int32 re-run launch walks all of it)
+    dyn[2 * rt.nl] = count;
+    dyn[2 * rt.nl + 1] = 0;
+  }
   __syncthreads();
   const bool merge = rt.merged >= 0 && count <= rt.num_sms;
   auto cls_of = [&](int s) -> int {
@@ -605,7 +615,7 @@ __global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__
 
 struct DynPlanImpl {
   uint64_t epoch = ~0ull;
-  int cap = 0;
+  int cap = 0, lmax = 0;
   Limits lim;
   std::vector<Launch> launches;
   RouteTable rt;
@@ -618,6 +628,7 @@ int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen,
   const Limits &lim = p->lim;
   int lmax = 0;
   for (int k = 0; k < nlen; ++k) lmax = std::max(lmax, lengths[k]);
+  p->lmax = lmax;
   auto any_in = [&](int lo, int hi) {  // a possible length in (lo, hi]
     for (int k = 0; k < nlen; ++k)
       if (lengths[k] > lo && lengths[k] <= hi) return true;
@@ -706,12 +717,11 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
   if (rc) return rc;
   const int nl = p->rt.nl;
   CUDA_TRY(c->d_order.reserve(sizeof(int32_t) * (2 * (size_t)cap + 2)));
-  CUDA_TRY(c->d_dyn.reserve(sizeof(int32_t) * 2 * kMaxDynLaunches));
-  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(2 * nl)));
-  CUDA_TRY(cudaMemsetAsync(c->d_ctl.p, 0, sizeof(int32_t) * (size_t)(2 * nl), st));
+  CUDA_TRY(c->d_dyn.reserve(sizeof(int32_t) * 2 * (kMaxDynLaunches + 1)));
+  CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(2 * nl + 2)));
   CUDA_TRY(c->d_redo.reserve(sizeof(int32_t) * (size_t)cap));
-  CUDA_TRY(cudaMemsetAsync(c->d_redo.p, 0, sizeof(int32_t) * (size_t)cap, st));
-  route_kernel<<<1, 1024, 0, st>>>(count_ptr, total_ptr, off, cap, p->rt, (int32_t *)c->d_order.p, (int32_t *)c->d_dyn.p);
+  route_kernel<<<1, 1024, 0, st>>>(count_ptr, total_ptr, off, cap, p->rt, (int32_t *)c->d_order.p, (int32_t *)c->d_dyn.p,
+                                   (int32_t *)c->d_ctl.p, 2 * nl + 2, (int32_t *)c->d_redo.p);
   CUDA_TRY(cudaGetLastError());
   c->last_launches++;
   for (int li = 0; li < nl; ++li) {
@@ -732,8 +742,27 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
     a.redo = (int32_t *)c->d_redo.p;
     a.redo_filter = 0;
     a.dyn = (const int32_t *)c->d_dyn.p + 2 * li;
-    rc = issue_launch(c, p->lim, L, L.end - L.begin, a, (int32_t *)c->d_ctl.p + 2 * li, st);
+    rc = issue_launch(c, p->lim, L, L.end - L.begin, a, (int32_t *)c->d_ctl.p + 2 * li, st, false);
     if (rc) return rc;
+    if (li + 1 == nl && p->lim.wave_esz == 2) {
+      // ONE int32 re-run for the sequences any class flagged (values beyond the int16 tables' range): it walks the
+      // whole batch in routed order with the longest possible length's layout
+      a.redo_filter = 1;
+      a.dyn = (const int32_t *)c->d_dyn.p + 2 * nl;
+      const bool smem_tables = p->lmax <= kLegacySmemLimit;
+      const int occ = std::max(1, cached_occ(c, 2, std::max(p->lmax, 8), smem_tables ? 1 : 0, kCtaThreads));
+      const int grid = std::min(cap, c->num_sms * occ);
+      int *wsp = nullptr;
+      long long stride = 0;
+      if (!smem_tables) {
+        // the cluster launches' tables are dead by now (stream order); the re-run's own tables go behind them
+        stride = 2LL * table_cells(p->lmax);
+        CUDA_TRY(c->d_ws2.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
+        wsp = (int *)c->d_ws2.p;
+      }
+      CUDA_TRY(launch_fold_cta(c->d_params, a, std::max(p->lmax, 8), smem_tables, grid, wsp, stride, (int32_t *)c->d_ctl.p + 2 * nl, st));
+      c->last_launches++;
+    }
   }
   return leave_call(c, st);
 }
@@ -826,7 +855,7 @@ void rnafold_shutdown(void) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   for (DevBuf *b : {&c->d_seq, &c->d_off, &c->d_order, &c->d_target, &c->d_db, &c->d_mfe, &c->d_hd,
-                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws, &c->d_redo, &c->d_dyn})
+                    &c->d_reward, &c->d_mismatch, &c->d_ctl, &c->d_ws, &c->d_ws2, &c->d_redo, &c->d_dyn})
     b->release();
   for (PinBuf *b : {&c->h_in, &c->h_out, &c->h_off}) b->release();
   cudaFree(c->d_params);

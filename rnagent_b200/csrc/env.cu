@@ -58,7 +58,7 @@ struct Env {
   uint8_t *d_seq = nullptr, *d_mask = nullptr, *d_done = nullptr;
   double *d_reward = nullptr;
   // terminal batch
-  int32_t *d_list = nullptr, *d_off = nullptr, *d_hd = nullptr, *d_mfe = nullptr;
+  int32_t *d_list = nullptr, *d_off = nullptr, *d_hd = nullptr, *d_mfe = nullptr, *d_slot = nullptr;
   uint8_t *d_bseq = nullptr, *d_btgt = nullptr, *d_bdb = nullptr;
   double *d_brw = nullptr;
   int32_t *h_off = nullptr;  // pinned: [0] = total length, [1] = count, [2..] offsets (host-routed path: local search)
@@ -155,7 +155,7 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
                                 const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
                                 const int16_t *__restrict__ pair, int32_t *idx, uint8_t *seq, uint8_t *mask,
                                 uint8_t *done, double *reward, unsigned long long *istat, unsigned long long *packed,
-                                int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt) {
+                                int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt, int32_t *slot_of) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_envs) return;
   const int t = cur[e];
@@ -185,6 +185,7 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
     const unsigned long long old = atomicAdd(packed, (1ull << 32) | (unsigned long long)n);
     const int slot = (int)(old >> 32), o0 = (int)(old & 0xffffffffull);
     list[slot] = e;
+    slot_of[e] = slot;
     boff[slot] = o0;
     for (int q = 0; q < n; ++q) {
       bseq[o0 + q] = s[q];
@@ -192,57 +193,6 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
     }
   }
   atomicAdd(&istat[3], 1ull);
-}
-
-// scatter fold results back to their environments and update the rollout statistics
-__global__ void env_scatter_kernel(const int32_t *__restrict__ count_ptr, int n_envs, int lmax, const int32_t *__restrict__ list, const int32_t *__restrict__ off,
-                                   const double *__restrict__ brw, const int32_t *__restrict__ bhd,
-                                   const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb,
-                                   const uint8_t *__restrict__ bseq, const int32_t *__restrict__ cur,
-                                   const int32_t *__restrict__ toff, double *reward,
-                                   uint8_t *last_db, uint8_t *last_seq, int32_t *last_hd, int32_t *last_mfe,
-                                   int32_t *last_t, unsigned long long *istat, double *fstat, int gc_penalty) {
-  __shared__ int n_u;
-  const int count = min(*count_ptr, n_envs);
-  for (int s = blockIdx.x; s < count; s += gridDim.x) {
-    const int e = list[s];
-    const int o0 = off[s], len = toff[cur[e] + 1] - toff[cur[e]];
-    if (gc_penalty) {
-      if (threadIdx.x == 0) n_u = 0;
-      __syncthreads();
-    }
-    int my_u = 0;
-    for (int q = threadIdx.x; q < len; q += blockDim.x) {
-      const uint8_t ch = bseq[o0 + q];
-      last_db[(size_t)e * lmax + q] = bdb[o0 + q];
-      last_seq[(size_t)e * lmax + q] = ch;
-      my_u += ch == 'U';
-    }
-    double rw = brw[s];
-    if (gc_penalty) {
-      if (my_u) atomicAdd(&n_u, my_u);
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        // r * 0.85 + clip(gcau['U'], 0, .15); gcau['U'] accumulates one increment per U like gcau_content (solution.py:257-268)
-        const double inc = 1.0 / (double)len;
-        double u = 0.0;
-        for (int k = 0; k < n_u; ++k) u += inc;
-        rw = rw * 0.85 + fmin(fmax(u, 0.0), 0.15);
-      }
-      __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-      reward[e] = rw;
-      last_hd[e] = bhd[s];
-      last_mfe[e] = bmfe[s];
-      last_t[e] = cur[e];
-      atomicAdd(&istat[0], 1ull);
-      if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
-      atomicAdd(&istat[2], (unsigned long long)bhd[s]);
-      atomicAdd(&fstat[0], rw);
-      atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
-    }
-  }
 }
 
 // observation window encoding[:, i:i+2k] of the zero-padded [10, len+2k] encoding (solution.py:62-75,116-123)
@@ -262,6 +212,89 @@ __global__ void env_obs_kernel(int n_envs, int lmax, int k, const int32_t *__res
   };
   // kRows * w = 20 k bytes per environment: a multiple of 4, so every thread emits one 32-bit word when the
   // destination is word-aligned
+  uint8_t *dst = obs + (size_t)e * kRows * w;
+  if ((reinterpret_cast<uintptr_t>(obs) & 3u) == 0) {
+    for (int q = 4 * threadIdx.x; q < kRows * w; q += 4 * blockDim.x)
+      *reinterpret_cast<unsigned *>(dst + q) = cell(q) | (cell(q + 1) << 8) | (cell(q + 2) << 16) | (cell(q + 3) << 24);
+  } else {
+    for (int q = threadIdx.x; q < kRows * w; q += blockDim.x) dst[q] = (uint8_t)cell(q);
+  }
+}
+
+// End of a step, one block per environment: a terminal environment takes its fold results (reward, last solution,
+// rollout counters), is re-armed with its next target when auto_reset is on, and every environment emits its observation
+// window -- the three former kernels in one launch (an environment's observation only depends on its own state).
+__global__ void env_finish_kernel(int n_envs, int n_targets, int lmax, int k, int auto_reset, int randomize, unsigned long long seed,
+                                  int gc_penalty, const uint8_t *__restrict__ done, const int32_t *__restrict__ slot_of,
+                                  const int32_t *__restrict__ off, const double *__restrict__ brw, const int32_t *__restrict__ bhd,
+                                  const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb, const uint8_t *__restrict__ bseq,
+                                  const int32_t *__restrict__ toff, const uint8_t *__restrict__ mot, int32_t *cur, int32_t *idx,
+                                  int32_t *ep, uint8_t *seq, uint8_t *mask, double *reward, uint8_t *last_db, uint8_t *last_seq,
+                                  int32_t *last_hd, int32_t *last_mfe, int32_t *last_t, unsigned long long *istat, double *fstat,
+                                  uint8_t *obs, unsigned long long *packed) {
+  __shared__ int n_u;
+  const int e = blockIdx.x;
+  if (e >= n_envs) return;
+  if (e == 0 && threadIdx.x == 0) *packed = 0ull;  // nobody reads the terminal counter any more: the next step starts empty
+  if (done[e]) {
+    const int s = slot_of[e];
+    const int t0 = cur[e];
+    const int o0 = off[s], len = toff[t0 + 1] - toff[t0];
+    if (threadIdx.x == 0) n_u = 0;
+    __syncthreads();
+    int my_u = 0;
+    for (int q = threadIdx.x; q < len; q += blockDim.x) {
+      const uint8_t ch = bseq[o0 + q];
+      last_db[(size_t)e * lmax + q] = bdb[o0 + q];
+      last_seq[(size_t)e * lmax + q] = ch;
+      my_u += ch == 'U';
+    }
+    if (gc_penalty && my_u) atomicAdd(&n_u, my_u);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double rw = brw[s];
+      if (gc_penalty) {
+        // r * 0.85 + clip(gcau['U'], 0, .15); gcau['U'] accumulates one increment per U like gcau_content (solution.py:257-268)
+        const double inc = 1.0 / (double)len;
+        double u = 0.0;
+        for (int q = 0; q < n_u; ++q) u += inc;
+        rw = rw * 0.85 + fmin(fmax(u, 0.0), 0.15);
+      }
+      reward[e] = rw;
+      last_hd[e] = bhd[s];
+      last_mfe[e] = bmfe[s];
+      last_t[e] = t0;
+      atomicAdd(&istat[0], 1ull);
+      if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
+      atomicAdd(&istat[2], (unsigned long long)bhd[s]);
+      atomicAdd(&fstat[0], rw);
+      atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
+      if (auto_reset) {   // RnaDesign.reset: next target, empty solution
+        const int epn = ep[e] + 1;
+        int t;
+        if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
+        else t = (t0 + 1) % n_targets;
+        cur[e] = t;
+        idx[e] = 0;
+        ep[e] = epn;
+      }
+    }
+    if (auto_reset)
+      for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
+        seq[(size_t)e * lmax + q] = '-';
+        mask[(size_t)e * lmax + q] = 0;
+      }
+    __syncthreads();
+  }
+  const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
+  const int w = 2 * k;
+  auto cell = [&](int q) -> unsigned {
+    const int row = q / w, col = q - row * w;
+    const int pos = i - k + col;
+    unsigned v = 0;
+    if (pos >= 0 && pos < n) v = row < 6 ? (mot[base + pos] == row) : ((mask[(size_t)e * lmax + pos] >> (row - 6)) & 1);
+    return v;
+  };
   uint8_t *dst = obs + (size_t)e * kRows * w;
   if ((reinterpret_cast<uintptr_t>(obs) & 3u) == 0) {
     for (int q = 4 * threadIdx.x; q < kRows * w; q += 4 * blockDim.x)
@@ -300,7 +333,7 @@ static cudaError_t copy_out(void *user, const void *dev, size_t bytes, cudaStrea
 
 static void env_free(Env *e) {
   void *ptrs[] = {e->d_tgt, e->d_mot, e->d_pair, e->d_toff, e->d_cur, e->d_idx, e->d_ep, e->d_act, e->d_seq, e->d_mask,
-                  e->d_done, e->d_reward, e->d_list, e->d_off, e->d_hd, e->d_mfe, e->d_bseq, e->d_btgt, e->d_bdb,
+                  e->d_done, e->d_reward, e->d_list, e->d_off, e->d_hd, e->d_mfe, e->d_slot, e->d_bseq, e->d_btgt, e->d_bdb,
                   e->d_brw, e->d_istat, e->d_fstat, e->d_obs, e->d_last_db, e->d_last_seq, e->d_last_hd,
                   e->d_last_mfe, e->d_last_t};
   for (void *p : ptrs)
@@ -331,6 +364,7 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_done, N));
   ENV_TRY(dalloc(&e->d_reward, N));
   ENV_TRY(dalloc(&e->d_list, N));
+  ENV_TRY(dalloc(&e->d_slot, N));
   ENV_TRY(dalloc(&e->d_off, N + 4));
   ENV_TRY(cudaMemset(e->d_off, 0, (N + 4) * sizeof(int32_t)));
   ENV_TRY(dalloc(&e->d_hd, N));
@@ -497,6 +531,7 @@ int rnafold_env_reset(int32_t h, uint8_t *obs_out) {
   env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
                                                      nullptr, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
   ENV_TRY(cudaGetLastError());
+  ENV_TRY(cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), e->stream));
   int rc = env_emit_obs(e, obs_out);
   if (rc) return rc;
   ENV_TRY(cudaStreamSynchronize(e->stream));
@@ -525,11 +560,11 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
     d_act = e->d_act;
   }
   // d_off: [0] total length, [1] count (one 64-bit word advanced atomically by the terminal environments), [2..] offsets
-  ENV_TRY(cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st));  // this step's terminal batch starts empty
+  // (the terminal counter is zero here: cleared by the last kernel of the previous step, by reset(), and on error returns)
   env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
                                                    e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
                                                    reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
-                                                   e->d_bseq, e->d_btgt);
+                                                   e->d_bseq, e->d_btgt, e->d_slot);
   ENV_TRY(cudaGetLastError());
   int rc = RNAFOLD_OK;
   if (e->permute) {
@@ -550,27 +585,32 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
       rc = rnafold_permute_batch(e->d_bseq, boff, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
                                  e->pm_allow_gu, e->seed + 0x632be59bd9b4e019ull * ++e->pm_calls, reward_exp, e->d_bdb, e->d_mfe,
                                  e->d_hd, e->d_brw, nullptr, nullptr);
-      if (rc) return rc;
+      if (rc) {
+        cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st);
+        return rc;
+      }
     }
   } else {
     rc = rnafold::fold_hamming_dyn_enqueue(&e->plan, e->lens.data(), (int)e->lens.size(), N, e->d_bseq, e->d_off + 2,
                                            e->d_off + 1, e->d_off, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
                                            reward_exp, (void *)st);
-    if (rc) return rc;
+    if (rc) {
+      cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st);
+      return rc;
+    }
   }
-  const int tail_grid = N < 592 ? N : 592;  // grid-stride over the terminal list (its length lives on the device)
-  env_scatter_kernel<<<tail_grid, 64, 0, st>>>(e->d_off + 1, N, e->lmax, e->d_list, e->d_off + 2, e->d_brw, e->d_hd, e->d_mfe,
-                                               e->d_bdb, e->d_bseq, e->d_cur, e->d_toff, e->d_reward, e->d_last_db,
-                                               e->d_last_seq, e->d_last_hd, e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat,
-                                               e->gc_penalty ? 1 : 0);
-  ENV_TRY(cudaGetLastError());
-  if (e->auto_reset) {
-    env_reset_kernel<<<tail_grid, 64, 0, st>>>(N, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, e->d_list, e->d_off + 1,
-                                               e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
+  {
+    // scatter + auto-reset + observation in one launch; a device destination is written by the kernel itself
+    const bool direct = obs_out && env_is_device_ptr(obs_out);
+    env_finish_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, e->auto_reset ? 1 : 0, e->randomize ? 1 : 0, e->seed,
+                                         e->gc_penalty ? 1 : 0, e->d_done, e->d_slot, e->d_off + 2, e->d_brw, e->d_hd, e->d_mfe,
+                                         e->d_bdb, e->d_bseq, e->d_toff, e->d_mot, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask,
+                                         e->d_reward, e->d_last_db, e->d_last_seq, e->d_last_hd, e->d_last_mfe, e->d_last_t,
+                                         e->d_istat, e->d_fstat, direct ? obs_out : e->d_obs,
+                                         reinterpret_cast<unsigned long long *>(e->d_off));
     ENV_TRY(cudaGetLastError());
+    if (!direct) ENV_TRY(copy_out(obs_out, e->d_obs, (size_t)N * kRows * 2 * e->k, st));
   }
-  rc = env_emit_obs(e, obs_out);
-  if (rc) return rc;
   ENV_TRY(copy_out(reward_out, e->d_reward, sizeof(double) * (size_t)N, st));
   ENV_TRY(copy_out(done_out, e->d_done, (size_t)N, st));
   const bool host_out = (obs_out && !env_is_device_ptr(obs_out)) || (reward_out && !env_is_device_ptr(reward_out)) ||
