@@ -19,6 +19,11 @@ namespace cg = cooperative_groups;
 
 constexpr int kClusterThreads = 512;
 
+// Split cluster barrier (barrier.cluster.arrive / .wait): a CTA announces the end of its phase without blocking and
+// only waits -- right before the items that consume the row its peer pushed -- for the peer's announcement.
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
 struct ClusterSmem {
   // common
   int misc_off, ptab_off, S_off;
@@ -149,6 +154,10 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
       for (int k = 0; k < kGenIters; ++k) gterm[k] = goff[k] = 0;
     }
 
+    // Protocol per phase: [items that only read this CTA's tables] -> wait for the peer's previous phase -> [items that
+    // read the row the peer pushed: Fp / Fm] -> __syncthreads -> arrive.  The rows are double / triple buffered, and a row
+    // is only overwritten by an item that runs behind a wait, i.e. after its consumer's phase has been announced.
+    cluster_arrive_release();
     for (int d = kTurn + 1; d <= n + 1; ++d) {
 #ifdef WAVE_PHASE_CLK
       const long long clk_p0 = clock64();
@@ -170,8 +179,66 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
 #pragma unroll
         for (int r = 0; r < kEParts; ++r) neparts += (epart_beg(r) <= lmax) ? 1 : 0;
         const int nI = nbI * neparts, nT = (lmax >= 0) ? nbI : 0, nF = nb_1;
-        const int total = nI + nT + nF + nP;
+        const int total = nI + nT + nP + nF;
+        auto finalise_pairs = [&](int kf) {
+          // ---- Fp(b): finalise c of diagonal d1 (needs the DML row the multiloop CTA pushed in its previous phase),
+          // push c + E_MLstem to the multiloop CTA; lookups up front and unconditional, masked afterwards
+          {
+            const int x = kf * 32 + lane;
+            const bool live = x < cells_1;
+            const int xs = live ? x : 0;
+            const int i = xs + 1, j = i + d1;
+            const int type = PT(S[i], S[j]);
+            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
+            const int rt = rtype_of(type);
+            const int v_mmh = __ldg(&sp.mmH[type][si1][sj1]);
+            const int v_mlc = e_mlstem(sp, rt, sj1, si1);
+            const int v_mmii = __ldg(&sp.mmI[rt][sjp1][sim1]);
+            const int v_mm1i = __ldg(&sp.mm1nI[rt][sjp1][sim1]);
+            const int v_mls = e_mlstem(sp, type, sim1, sjp1);
+            const int hbase = (d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1]);
+            const int v_mmio = __ldg(&sp.mmI[type][si1][sj1]);
+            const ST *src = part + (par1 * kWSlots) * np + xs;
+            const int s_g = (int)src[0], s_t = (int)src[np];
+            int s_e = kInfS;
+#pragma unroll
+            for (int r = 0; r < kEParts; ++r) s_e = (d1 - 6 >= epart_beg(r)) ? min(s_e, (int)src[(2 + r) * np]) : s_e;
+            const int v_dml = dml[((d1 - 2) % 3) * np + xs + 1];
+            int cij = hbase + v_mmh;
+            if (d1 == 4 || d1 == 5 || d1 == 7) cij = type ? e_hairpin(sp, gp, S, i, j, type) : cij;
+            cij = (d1 >= 12) ? min(cij, s_g + v_mmio) : cij;
+            cij = (d1 >= 6) ? min(cij, s_t) : cij;
+            cij = (d1 >= 8) ? min(cij, s_e) : cij;
+            cij = (d1 >= 2 * kTurn + 4) ? min(cij, v_dml + v_mlc + cW.MLclosing) : cij;
+            if (live) {
+              const int wrow = (d1 & (kWin - 1)) * rs + x;
+              int stem = kInf;
+              ST cb = (ST)kInfS;
+              if (type) {
+                cb = put<ST>(cij + (type > 2 ? tau : 0), flag);
+                wI[wrow] = put<ST>(cij + v_mmii, flag);
+                w1[wrow] = put<ST>(cij + v_mm1i, flag);
+                stem = cij + v_mls;
+              } else {
+                wI[wrow] = (ST)kInfS;
+                w1[wrow] = (ST)kInfS;
+              }
+              wB[wrow] = cb;
+              cbg[tri(n, d1) + x] = cb;
+              peer_cst[(d1 & 1) * np + x] = stem;
+            }
+          }
+        };
+        bool waited = false;
         for (int k = warp; k < total; k += NW) {
+          if (k >= nI + nT + nP) {
+            if (!waited) {
+              cluster_wait_acquire();   // the multiloop CTA's previous phase (its DML push) is complete
+              waited = true;
+            }
+            finalise_pairs(k - nI - nT - nP);
+            continue;
+          }
           if (k < nI) {
             // ---- E(b,r): bulges and 1xn loops of the loop sizes in part r, lanes across pairable cells
             const int r = div_small(k, nbI, kEParts), blk = k - r * nbI;
@@ -214,52 +281,6 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
                 best = (n1 + n2 <= d - 6 && t2 != 0) ? min(best, e) : best;
               }
               part[(par * kWSlots + 1) * np + x] = (ST)min(best, kInfS);
-            }
-          } else if (k < nI + nT + nF) {
-            // ---- Fp(b): finalise c of diagonal d1, push c + E_MLstem to the multiloop CTA
-            // all lookups up front and unconditional, masked afterwards (see fold_wave_kernel's F item)
-            const int x = (k - nI - nT) * 32 + lane;
-            const bool live = x < cells_1;
-            const int xs = live ? x : 0;
-            const int i = xs + 1, j = i + d1;
-            const int type = PT(S[i], S[j]);
-            const int si1 = S[i + 1], sj1 = S[j - 1], sim1 = S[i - 1], sjp1 = S[j + 1];
-            const int rt = rtype_of(type);
-            const int v_mmh = __ldg(&sp.mmH[type][si1][sj1]);
-            const int v_mlc = e_mlstem(sp, rt, sj1, si1);
-            const int v_mmii = __ldg(&sp.mmI[rt][sjp1][sim1]);
-            const int v_mm1i = __ldg(&sp.mm1nI[rt][sjp1][sim1]);
-            const int v_mls = e_mlstem(sp, type, sim1, sjp1);
-            const int hbase = (d1 - 1 <= 30) ? sp.hairpin[d1 - 1] : __ldg(&gp->hairpin_len[d1 - 1]);
-            const int v_mmio = __ldg(&sp.mmI[type][si1][sj1]);
-            const ST *src = part + (par1 * kWSlots) * np + xs;
-            const int s_g = (int)src[0], s_t = (int)src[np];
-            int s_e = kInfS;
-#pragma unroll
-            for (int r = 0; r < kEParts; ++r) s_e = (d1 - 6 >= epart_beg(r)) ? min(s_e, (int)src[(2 + r) * np]) : s_e;
-            const int v_dml = dml[((d1 - 2) % 3) * np + xs + 1];
-            int cij = hbase + v_mmh;
-            if (d1 == 4 || d1 == 5 || d1 == 7) cij = type ? e_hairpin(sp, gp, S, i, j, type) : cij;
-            cij = (d1 >= 12) ? min(cij, s_g + v_mmio) : cij;
-            cij = (d1 >= 6) ? min(cij, s_t) : cij;
-            cij = (d1 >= 8) ? min(cij, s_e) : cij;
-            cij = (d1 >= 2 * kTurn + 4) ? min(cij, v_dml + v_mlc + cW.MLclosing) : cij;
-            if (live) {
-              const int wrow = (d1 & (kWin - 1)) * rs + x;
-              int stem = kInf;
-              ST cb = (ST)kInfS;
-              if (type) {
-                cb = put<ST>(cij + (type > 2 ? tau : 0), flag);
-                wI[wrow] = put<ST>(cij + v_mmii, flag);
-                w1[wrow] = put<ST>(cij + v_mm1i, flag);
-                stem = cij + v_mls;
-              } else {
-                wI[wrow] = (ST)kInfS;
-                w1[wrow] = (ST)kInfS;
-              }
-              wB[wrow] = cb;
-              cbg[tri(n, d1) + x] = cb;
-              peer_cst[(d1 & 1) * np + x] = stem;
             }
           } else {
             // ---- P: list of the pairable cells of diagonal d+1 (used by the next phase)
@@ -313,6 +334,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
           const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
           goff[k] = (u >= bb + (int)wI_sa) ? u : t;
         }
+        if (!waited) cluster_wait_acquire();
       } else {
         // ================= multiloop CTA
         // split range t = 4 .. d-5 cut into enough chunks that every warp of this CTA gets work even on the
@@ -329,18 +351,25 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
         const int cells_2 = (d2 >= kTurn + 1 && d2 < n) ? n - d2 : 0;
         const int nb_2 = (cells_2 + 31) >> 5;
         const int nM = nb_d * nch;
-        const int total = nM + nb_2;
-        for (int k = warp; k < total; k += NW) {
-          if (k < nM) {
-            // ---- M(b,m)
-            const int m = k / nb_d, blk = k - m * nb_d;
-            const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
-            const int t0 = kTurn + 1 + m * chunk, t1 = min(d - kTurn - 1, t0 + chunk);
-            const int best = split_scan<ST>(F, rs, d, xc, t0, t1);
-            if (x < cells_d) atomicMin(&mlp[(d % 3) * mlparts * np + x], best);
-          } else {
+        bool waited = false;
+        for (int k = warp; k < nM; k += NW) {
+          // ---- M(b,m)
+          const int m = k / nb_d, blk = k - m * nb_d;
+          const int x = blk * 32 + lane, xc = min(x, cells_d - 1);
+          const int t0 = kTurn + 1 + m * chunk, t1 = min(d - kTurn - 1, t0 + chunk);
+          const int best = split_scan<ST>(F, rs, d, xc, t0, t1);
+          if (x < cells_d) atomicMin(&mlp[(d % 3) * mlparts * np + x], best);
+        }
+        {
+          int f0 = warp - (nM % NW);
+          if (f0 < 0) f0 += NW;
+          for (int kf = f0; kf < nb_2; kf += NW) {
+            if (!waited) {
+              cluster_wait_acquire();   // the pair CTA's previous phase (its stem-row push) is complete
+              waited = true;
+            }
             // ---- Fm(b): finalise fML of diagonal d2, push DML to the pair CTA
-            const int x = (k - nM) * 32 + lane;
+            const int x = kf * 32 + lane;
             if (x < cells_2) {
               int e = kInf;
               if (d2 > kTurn + 1) {
@@ -357,16 +386,19 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
             }
           }
         }
+        if (!waited) cluster_wait_acquire();
       }
 #ifdef WAVE_PHASE_CLK
       __syncthreads();
       if (tid == 0) atomicAdd(&g_phase_clk[(rank ? 64 : 0) + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
 #endif
-      cluster.sync();
+      __syncthreads();            // this CTA's tables of the phase are complete ...
+      cluster_arrive_release();   // ... and so are its pushes: announce the phase, do not wait here
 #ifdef WAVE_PHASE_CLK
       if (tid == 0 && rank == 0) atomicAdd(&g_phase_clk[128 + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
 #endif
     }
+    cluster_wait_acquire();       // drain the last announcement (pairs with the arrive above)
     if (Store<ST>::kChecked && flag && a.redo) a.redo[b] = 1;
   }
 }
