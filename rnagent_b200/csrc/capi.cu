@@ -368,7 +368,21 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     int k = 0;
     while (k < B && len_at(k) > cluster_limit) ++k;
     if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal, false});
-    // 2-CTA cluster kernel (tables split over DSMEM) for lengths above the single-CTA kernel's reach
+    // 2-CTA cluster kernel (tables split over DSMEM) for lengths above the single-CTA kernel's reach.
+    // Few of them (no more than the clusters the device holds at once): ONE launch of the longest one's class, so that
+    // the call costs one long-fold latency instead of one per length class.
+    {
+      int e_all = k;
+      while (e_all < B && len_at(e_all) > wave_limit) ++e_all;
+      if (e_all > k && !getenv("RNAFOLD_NO_MERGE")) {
+        int q0 = 0;
+        while (q0 < kNumClusterClasses && kClusterClasses[q0] < len_at(k)) ++q0;
+        if (q0 < kNumClusterClasses && e_all - k <= cached_occ(c, 1, kClusterClasses[q0], 2, 0)) {
+          launches.push_back(Launch{k, e_all, kClusterClasses[q0], kKindCluster, false});
+          k = e_all;
+        }
+      }
+    }
     for (int q = kNumClusterClasses - 1; q >= 0 && k < B; --q) {
       if (kClusterClasses[q] > cluster_limit) continue;
       const int lo = q > 0 ? std::max(kClusterClasses[q - 1], wave_limit) : wave_limit;
@@ -558,6 +572,9 @@ struct RouteTable {
   int merged;                     // index of the latency launch that takes a batch of <= num_sms sequences whole, or -1
   int num_sms;
   int first_class;                // first class launch (the classes follow in ASCENDING order of `upper`)
+  int wfirst, wlast;              // wave class launches [wfirst, wlast] (-1: none)
+  int cfirst, clast, cmax;        // cluster class launches [cfirst, clast]; cmax: clusters resident at once in clast's class
+                                  // (a batch with <= cmax cluster-length sequences sends them all to launch clast)
   int upper[kMaxDynLaunches];     // class launches: longest sequence routed to launch k
 };
 
@@ -578,36 +595,51 @@ __global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__
     dyn[2 * rt.nl + 1] = 0;
   }
   __syncthreads();
-  const bool merge = rt.merged >= 0 && count <= rt.num_sms;
   auto cls_of = [&](int s) -> int {
     const int n = ((s + 1 == count && total_ptr) ? total : off[s + 1]) - off[s];
     int k = rt.first_class;
     while (k + 1 < rt.nl && n > rt.upper[k]) ++k;
     return k;
   };
-  if (merge) {
-    for (int s = tid; s < count; s += blockDim.x) order[s] = s;
-    if (tid < rt.nl) {
-      dyn[2 * tid] = tid == rt.merged ? count : 0;
-      dyn[2 * tid + 1] = 0;
-    }
-  } else {
-    for (int s = tid; s < count; s += blockDim.x) atomicAdd(&cnt[cls_of(s)], 1);
-    __syncthreads();
-    if (tid == 0) {
-      int o = 0;
-      for (int k = 0; k < rt.nl; ++k) {
-        beg[k] = o;
-        o += cnt[k];
-        dyn[2 * k] = cnt[k];
-        dyn[2 * k + 1] = beg[k];
+  __shared__ int merge_w, merge_c;
+  for (int s = tid; s < count; s += blockDim.x) atomicAdd(&cnt[cls_of(s)], 1);
+  __syncthreads();
+  if (tid == 0) {
+    // Few sequences of a kernel family (no more than the device runs at once): ONE launch of the family's longest class,
+    // so that the call costs one fold latency per family instead of one per length class.
+    merge_w = merge_c = 0;
+    if (rt.merged >= 0 && rt.wfirst >= 0) {
+      int nw = 0;
+      for (int k = rt.wfirst; k <= rt.wlast; ++k) nw += cnt[k];
+      if (nw <= rt.num_sms) {
+        merge_w = 1;
+        for (int k = rt.wfirst; k <= rt.wlast; ++k) cnt[k] = 0;
+        cnt[rt.merged] = nw;
       }
     }
-    __syncthreads();
-    for (int s = tid; s < count; s += blockDim.x) {
-      const int k = cls_of(s);
-      order[beg[k] + atomicAdd(&fill[k], 1)] = s;
+    if (rt.cfirst >= 0 && rt.clast > rt.cfirst) {
+      int nc = 0;
+      for (int k = rt.cfirst; k <= rt.clast; ++k) nc += cnt[k];
+      if (nc <= rt.cmax) {
+        merge_c = 1;
+        for (int k = rt.cfirst; k < rt.clast; ++k) cnt[k] = 0;
+        cnt[rt.clast] = nc;
+      }
     }
+    int o = 0;
+    for (int k = 0; k < rt.nl; ++k) {
+      beg[k] = o;
+      o += cnt[k];
+      dyn[2 * k] = cnt[k];
+      dyn[2 * k + 1] = beg[k];
+    }
+  }
+  __syncthreads();
+  for (int s = tid; s < count; s += blockDim.x) {
+    int k = cls_of(s);
+    if (merge_w && k >= rt.wfirst && k <= rt.wlast) k = rt.merged;
+    else if (merge_c && k >= rt.cfirst && k < rt.clast) k = rt.clast;
+    order[beg[k] + atomicAdd(&fill[k], 1)] = s;
   }
   __syncthreads();
   if (tid == 0 && total_ptr) off[count] = total;  // closes the CSR (the producers wrote off[0..count-1])
@@ -643,11 +675,17 @@ int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen,
   RouteTable &rt = p->rt;
   std::memset(&rt, 0, sizeof(rt));
   rt.merged = -1;
+  rt.cfirst = rt.clast = rt.wfirst = rt.wlast = -1;
   rt.num_sms = c->num_sms;
-  // the latency launch: everything in one wide-CTA launch of the longest possible class
-  if (lmax <= lim.wave_limit) {
-    rt.merged = 0;
-    p->launches.push_back(Launch{0, std::min(cap, c->num_sms), std::max(lmax, 8), kKindWave, true});
+  // the latency launch: the sequences of the single-CTA kernel's reach in one wide-CTA launch of their longest class
+  {
+    int wmax = 0;
+    for (int k = 0; k < nlen; ++k)
+      if (lengths[k] <= lim.wave_limit) wmax = std::max(wmax, lengths[k]);
+    if (any_in(-1, lim.wave_limit)) {
+      rt.merged = 0;
+      p->launches.push_back(Launch{0, std::min(cap, c->num_sms), std::max(wmax, 8), kKindWave, true});
+    }
   }
   rt.first_class = (int)p->launches.size();
   // class launches in ascending order of their upper bound (the routing kernel walks them upwards)
@@ -657,6 +695,8 @@ int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen,
     if (any_in(lo, kWaveClasses[cls]) && (int)p->launches.size() < kMaxDynLaunches) {
       p->launches.push_back(Launch{0, cap, top_in(lo, kWaveClasses[cls]), kKindWave, false});
       rt.upper[p->launches.size() - 1] = kWaveClasses[cls];
+      if (rt.wfirst < 0) rt.wfirst = (int)p->launches.size() - 1;
+      rt.wlast = (int)p->launches.size() - 1;
     }
     lo = kWaveClasses[cls];
   }
@@ -668,6 +708,9 @@ int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen,
       if (per_seq * (size_t)cap > kClusterWorkspaceCap) return fail(RNAFOLD_EINVAL, "device-routed batch too large for the cluster workspace");
       p->launches.push_back(Launch{0, cap, kClusterClasses[q], kKindCluster, false});
       rt.upper[p->launches.size() - 1] = kClusterClasses[q];
+      if (rt.cfirst < 0) rt.cfirst = (int)p->launches.size() - 1;
+      rt.clast = (int)p->launches.size() - 1;
+      rt.cmax = cached_occ(c, 1, kClusterClasses[q], 2, 0);
     }
     lo = kClusterClasses[q];
   }

@@ -59,6 +59,7 @@ struct Env {
   double *d_reward = nullptr;
   // terminal batch
   int32_t *d_list = nullptr, *d_off = nullptr, *d_hd = nullptr, *d_mfe = nullptr, *d_slot = nullptr;
+  unsigned long long *d_keys = nullptr;
   uint8_t *d_bseq = nullptr, *d_btgt = nullptr, *d_bdb = nullptr;
   double *d_brw = nullptr;
   int32_t *h_off = nullptr;  // pinned: [0] = total length, [1] = count, [2..] offsets (host-routed path: local search)
@@ -155,7 +156,8 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
                                 const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
                                 const int16_t *__restrict__ pair, int32_t *idx, uint8_t *seq, uint8_t *mask,
                                 uint8_t *done, double *reward, unsigned long long *istat, unsigned long long *packed,
-                                int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt, int32_t *slot_of) {
+                                int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt, int32_t *slot_of,
+                                const int32_t *__restrict__ ep, unsigned long long *keys) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_envs) return;
   const int t = cur[e];
@@ -186,6 +188,7 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
     const int slot = (int)(old >> 32), o0 = (int)(old & 0xffffffffull);
     list[slot] = e;
     slot_of[e] = slot;
+    keys[slot] = ((unsigned long long)(unsigned)e << 32) | (unsigned long long)(unsigned)ep[e];  // what the local search's draws are keyed on
     boff[slot] = o0;
     for (int q = 0; q < n; ++q) {
       bseq[o0 + q] = s[q];
@@ -333,7 +336,7 @@ static cudaError_t copy_out(void *user, const void *dev, size_t bytes, cudaStrea
 
 static void env_free(Env *e) {
   void *ptrs[] = {e->d_tgt, e->d_mot, e->d_pair, e->d_toff, e->d_cur, e->d_idx, e->d_ep, e->d_act, e->d_seq, e->d_mask,
-                  e->d_done, e->d_reward, e->d_list, e->d_off, e->d_hd, e->d_mfe, e->d_slot, e->d_bseq, e->d_btgt, e->d_bdb,
+                  e->d_done, e->d_reward, e->d_list, e->d_off, e->d_hd, e->d_mfe, e->d_slot, e->d_keys, e->d_bseq, e->d_btgt, e->d_bdb,
                   e->d_brw, e->d_istat, e->d_fstat, e->d_obs, e->d_last_db, e->d_last_seq, e->d_last_hd,
                   e->d_last_mfe, e->d_last_t};
   for (void *p : ptrs)
@@ -365,6 +368,7 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_reward, N));
   ENV_TRY(dalloc(&e->d_list, N));
   ENV_TRY(dalloc(&e->d_slot, N));
+  ENV_TRY(dalloc(&e->d_keys, N));
   ENV_TRY(dalloc(&e->d_off, N + 4));
   ENV_TRY(cudaMemset(e->d_off, 0, (N + 4) * sizeof(int32_t)));
   ENV_TRY(dalloc(&e->d_hd, N));
@@ -564,7 +568,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
                                                    e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
                                                    reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
-                                                   e->d_bseq, e->d_btgt, e->d_slot);
+                                                   e->d_bseq, e->d_btgt, e->d_slot, e->d_ep, e->d_keys);
   ENV_TRY(cudaGetLastError());
   int rc = RNAFOLD_OK;
   if (e->permute) {
@@ -582,9 +586,10 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
       }
       int32_t *boff = e->h_off + 2;   // CSR offsets of the terminal batch (slot order = arrival order)
       boff[count] = e->h_off[0];
-      rc = rnafold_permute_batch(e->d_bseq, boff, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
-                                 e->pm_allow_gu, e->seed + 0x632be59bd9b4e019ull * ++e->pm_calls, reward_exp, e->d_bdb, e->d_mfe,
-                                 e->d_hd, e->d_brw, nullptr, nullptr);
+      // draws keyed on (environment, episode): reproducible from the seed whatever else finishes in the same step
+      rc = rnafold::permute_batch_keyed(e->d_bseq, boff, count, e->d_btgt, e->pm_budget, e->pm_radius, e->pm_threshold, e->pm_p,
+                                        e->pm_allow_gu, e->seed, reward_exp, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw, nullptr,
+                                        nullptr, e->d_keys);
       if (rc) {
         cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st);
         return rc;

@@ -76,6 +76,12 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
 void fold_dyn_plan_free(void *plan);
 const int32_t *status_word();
 
+// permute.cu: rnafold_permute_batch with the draws of sequence b keyed on d_keys[b] (device array; nullptr: on b)
+int permute_batch_keyed(uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, int32_t budget, int32_t radius,
+                        int32_t threshold, double mutation_probability, int32_t allow_gu, uint64_t seed, double reward_exp,
+                        uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out, double *reward_out, int32_t *rounds_out,
+                        int32_t *folds_out, const unsigned long long *d_keys);
+
 // capi.cu: what other translation units need from the per-process context (ensemble.cu)
 struct CtxView {
   int device, num_sms;

@@ -61,6 +61,7 @@ struct PermuteCfg {
   int budget, radius, threshold, allow_gu;
   double p;
   unsigned long long seed;
+  const unsigned long long *keys;  // per sequence: what the draws are keyed on instead of the batch index (device; may be null)
   int order;  // candidate visiting order: 0 CPython >= 3.7 set, 1 CPython 3.6 set (the reference's pinned interpreter), 2 ascending
 };
 int g_pm_order = 0;
@@ -208,7 +209,7 @@ __global__ void pm_mutate_kernel(int count, int step, const int32_t *__restrict_
   }
   __syncthreads();
   if (threadIdx.x != 0) return;
-  const unsigned long long key = pm_mix64(cfg.seed + (unsigned long long)b);
+  const unsigned long long key = pm_mix64(cfg.seed + (cfg.keys ? cfg.keys[b] : (unsigned long long)b));
   const int nc = ncand[b];
   for (int c = 0; c < nc; ++c) {
     const int m = cand[o + c];
@@ -344,6 +345,18 @@ int rnafold_permute_batch(uint8_t *seq, const int32_t *off, int32_t B, const uin
                           int32_t radius, int32_t threshold, double mutation_probability, int32_t allow_gu,
                           uint64_t seed, double reward_exp, uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
                           double *reward_out, int32_t *rounds_out, int32_t *folds_out) {
+  return rnafold::permute_batch_keyed(seq, off, B, target, budget, radius, threshold, mutation_probability, allow_gu, seed,
+                                      reward_exp, db_out, mfe_dcal_out, hd_out, reward_out, rounds_out, folds_out, nullptr);
+}
+
+}  // extern "C"
+
+// The same with the draws of sequence b keyed on d_keys[b] (device array) instead of b: the batched environment passes
+// (environment index, episode), so a search does not depend on which other environments finished in the same step.
+int rnafold::permute_batch_keyed(uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *target, int32_t budget,
+                                 int32_t radius, int32_t threshold, double mutation_probability, int32_t allow_gu,
+                                 uint64_t seed, double reward_exp, uint8_t *db_out, int32_t *mfe_dcal_out, int32_t *hd_out,
+                                 double *reward_out, int32_t *rounds_out, int32_t *folds_out, const unsigned long long *d_keys) {
   std::lock_guard<std::mutex> lk(g_pm_mu);
   if (B < 0 || !off || (B > 0 && (!seq || !target))) return set_error(RNAFOLD_EINVAL, "null seq/off/target or negative batch size");
   if (pm_is_device_ptr(off)) return set_error(RNAFOLD_EINVAL, "permute: the CSR offsets must be a host array");
@@ -358,7 +371,7 @@ int rnafold_permute_batch(uint8_t *seq, const int32_t *off, int32_t B, const uin
   for (int b = 0; b < B; ++b)
     if (off[b + 1] < off[b] || off[b + 1] - off[b] > RNAFOLD_MAX_LEN) return set_error(RNAFOLD_EINVAL, "bad sequence length");
   const size_t total = (size_t)off[B], NB = (size_t)B;
-  const PermuteCfg cfg{budget, radius, threshold, allow_gu ? 1 : 0, mutation_probability, (unsigned long long)seed, g_pm_order};
+  const PermuteCfg cfg{budget, radius, threshold, allow_gu ? 1 : 0, mutation_probability, (unsigned long long)seed, d_keys, g_pm_order};
 
   Scratch &S = g_scratch;
   PM_TRY(S.reserve(total, NB));
@@ -431,5 +444,3 @@ int rnafold_permute_batch(uint8_t *seq, const int32_t *off, int32_t B, const uin
   if (folds_out) *folds_out = folds;
   return RNAFOLD_OK;
 }
-
-}  // extern "C"

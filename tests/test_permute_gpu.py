@@ -136,3 +136,28 @@ def test_environment_with_permute():
         assert abs(r1[e] - b.r) < 1e-12 and abs(r0[e] - a.r) < 1e-12
         better += b.hd < a.hd
     assert better > 10
+
+
+def test_environment_search_is_keyed_on_environment_and_episode():
+    """The local search of an environment draws from (seed, environment index, episode): it does not depend on which other
+    environments finish in the same step.  The first 40 environments of an 80-environment batch (round-robin targets,
+    the same actions) end with exactly the solutions they reach in a 40-environment batch."""
+    import rnagent_b200 as rb
+    from rnagent_b200 import synth
+    rb.set_vienna_params(1)
+    seq, off = synth.random_sequences(5, 36, 77)
+    structs, _ = rb.fold_batch([seq[off[k]:off[k + 1]].tobytes().decode() for k in range(5)])
+    cfg = dict(kernel_size=25, reward_exp=9, encoding_type=2, use_nucleotides=True, permute=True, permutation_budget=15,
+               permutation_radius=5, permutation_threshold=15, allow_gu_permutations=True, mutation_probability=0.5)
+    acts = np.random.default_rng(8).integers(0, 4, (120, 80)).astype(np.int32)
+    out = {}
+    for N in (40, 80):
+        env = rb.RnaDesignBatch(cfg, N, targets=structs, auto_reset=True, seed=11)
+        env.reset()
+        for t in range(120):                      # several episodes each: the episode counter enters the key
+            env.step(np.ascontiguousarray(acts[t, :N]))
+        out[N] = [(p.string, p.folded_structure, p.hd) for p in env.get_attr("prev_solution")]
+        assert env.stats().episodes >= 2 * N
+        env.close()
+    assert out[80][:40] == out[40]
+    assert len({s for s, _, _ in out[80]}) > 40   # ... and the environments are not all alike
