@@ -94,6 +94,10 @@ struct Context {
   // ev_done: end of the last fold call's device work (the next call, on whatever stream, waits for it before it
   // touches the shared scratch); ev_staged: the last call's H2D copies out of the pinned staging blocks
   cudaEvent_t ev_done = nullptr, ev_staged = nullptr;
+  // device-routed calls run their two kernel families side by side: the wavefront launches go to stream2 between a fork
+  // and a join event (few sequences per family: they occupy disjoint SMs)
+  cudaStream_t stream2 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool have_done = false, have_staged = false;
   int32_t *d_status = nullptr;   // sticky: set by a kernel whose backtrack found no decomposition
   uint64_t params_epoch = 0;     // bumped by every parameter upload (device-routed plans are rebuilt)
@@ -767,6 +771,14 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
                                    (int32_t *)c->d_ctl.p, 2 * nl + 2, (int32_t *)c->d_redo.p);
   CUDA_TRY(cudaGetLastError());
   c->last_launches++;
+  // both kernel families present: the wavefront launches run on stream2 beside the cluster / global-table launches
+  const bool two = p->rt.wfirst >= 0 && (p->rt.cfirst >= 0 || p->launches.back().kind == kKindLegacySmem ||
+                                         p->launches.back().kind == kKindLegacyGlobal);
+  if (two) {
+    CUDA_TRY(cudaEventRecord(c->ev_fork, st));
+    CUDA_TRY(cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+  }
+  bool joined = !two;
   for (int li = 0; li < nl; ++li) {
     const Launch &L = p->launches[li];
     BatchArgs a;
@@ -785,8 +797,14 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
     a.redo = (int32_t *)c->d_redo.p;
     a.redo_filter = 0;
     a.dyn = (const int32_t *)c->d_dyn.p + 2 * li;
-    rc = issue_launch(c, p->lim, L, L.end - L.begin, a, (int32_t *)c->d_ctl.p + 2 * li, st, false);
+    rc = issue_launch(c, p->lim, L, L.end - L.begin, a, (int32_t *)c->d_ctl.p + 2 * li,
+                      (two && L.kind == kKindWave) ? c->stream2 : st, false);
     if (rc) return rc;
+    if (li + 1 == nl && !joined) {
+      CUDA_TRY(cudaEventRecord(c->ev_join, c->stream2));
+      CUDA_TRY(cudaStreamWaitEvent(st, c->ev_join, 0));
+      joined = true;
+    }
     if (li + 1 == nl && p->lim.wave_esz == 2) {
       // ONE int32 re-run for the sequences any class flagged (values beyond the int16 tables' range): it walks the
       // whole batch in routed order with the longest possible length's layout
@@ -865,6 +883,9 @@ int rnafold_init(int device) {
   CUDA_TRY(cudaEventCreate(&c->ev1));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_staged, cudaEventDisableTiming));
+  CUDA_TRY(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   CUDA_TRY(cudaMalloc((void **)&c->d_status, sizeof(int32_t)));
   CUDA_TRY(cudaMemset(c->d_status, 0, sizeof(int32_t)));
   CUDA_TRY(cudaMalloc((void **)&c->d_params, sizeof(FoldParams)));
@@ -907,6 +928,9 @@ void rnafold_shutdown(void) {
   cudaEventDestroy(c->ev1);
   cudaEventDestroy(c->ev_done);
   cudaEventDestroy(c->ev_staged);
+  cudaEventDestroy(c->ev_fork);
+  cudaEventDestroy(c->ev_join);
+  cudaStreamDestroy(c->stream2);
   cudaStreamDestroy(c->stream);
   delete c;
   g_ctx = nullptr;
