@@ -96,8 +96,8 @@ struct Context {
   cudaEvent_t ev_done = nullptr, ev_staged = nullptr;
   // device-routed calls run their two kernel families side by side: the wavefront launches go to stream2 between a fork
   // and a join event (few sequences per family: they occupy disjoint SMs)
-  cudaStream_t stream2 = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaStream_t stream2 = nullptr, stream3 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join3 = nullptr;
   bool have_done = false, have_staged = false;
   int32_t *d_status = nullptr;   // sticky: set by a kernel whose backtrack found no decomposition
   uint64_t params_epoch = 0;     // bumped by every parameter upload (device-routed plans are rebuilt)
@@ -238,7 +238,8 @@ int cached_occ(Context *c, int family, int nmax, int esz, int threads) {
 // it, otherwise (a.dyn != nullptr: the count lives on the device) an upper bound that sizes grids and workspaces.
 // q: two queue counters (main kernel, range-check re-run).
 int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, BatchArgs a, int32_t *q, cudaStream_t st,
-                 bool with_rerun = true) {
+                 bool with_rerun = true, DevBuf *wsbuf = nullptr) {
+  DevBuf &ws_buf = wsbuf ? *wsbuf : c->d_ws;   // global tables of this launch (launches that overlap need their own)
   auto legacy = [&](BatchArgs la, bool smem_tables, int32_t *queue) -> int {
     const int occ = std::max(1, cached_occ(c, 2, L.nmax, smem_tables ? 1 : 0, kCtaThreads));
     const int grid = std::min(count, c->num_sms * occ);
@@ -246,8 +247,8 @@ int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, Batc
     long long stride = 0;
     if (!smem_tables) {
       stride = 2LL * table_cells(L.nmax);
-      CUDA_TRY(c->d_ws.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
-      ws = (int *)c->d_ws.p;
+      CUDA_TRY(ws_buf.reserve(sizeof(int32_t) * (size_t)stride * (size_t)grid));
+      ws = (int *)ws_buf.p;
     }
     CUDA_TRY(launch_fold_cta(c->d_params, la, L.nmax, smem_tables, grid, ws, stride, queue, st));
     c->last_launches++;
@@ -274,8 +275,8 @@ int issue_launch(Context *c, const Limits &lim, const Launch &L, int count, Batc
     }
   } else if (L.kind == kKindCluster) {
     const size_t stride = cluster_table_stride(L.nmax);
-    CUDA_TRY(c->d_ws.reserve(2 * stride * sizeof(int16_t) * (size_t)count));
-    int16_t *cbg = (int16_t *)c->d_ws.p, *fg = cbg + stride * (size_t)count;
+    CUDA_TRY(ws_buf.reserve(2 * stride * sizeof(int16_t) * (size_t)count));
+    int16_t *cbg = (int16_t *)ws_buf.p, *fg = cbg + stride * (size_t)count;
     const int ncl = std::max(1, std::min(count, cached_occ(c, 1, L.nmax, 2, 0)));
     CUDA_TRY(launch_fold_cluster(c->d_params, a, L.nmax, ncl, q, cbg, fg, st));
     CUDA_TRY(launch_f5_backtrack(c->d_params, a, L.nmax, count, cbg, fg, st));
@@ -488,6 +489,21 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
   CUDA_TRY(cudaMemsetAsync(c->d_redo.p, 0, sizeof(int32_t) * (size_t)B, st));
 
   if (c->timed) CUDA_TRY(cudaEventRecord(c->ev0, st));
+  // Length classes overlap: the wavefront launches go to an auxiliary stream beside the cluster /
+  // global-table launches on the caller's stream, so that the tail of one persistent launch is filled by the next
+  // (RNAFOLD_OVERLAP=0 serialises them on one stream; 3: two auxiliary streams -- measured on C5: 237.8 k folds/s serial,
+  // 252.8 k with one auxiliary stream (the default), 250.7 k with two)
+  static const int overlap_env = getenv("RNAFOLD_OVERLAP") ? atoi(getenv("RNAFOLD_OVERLAP")) : 2;
+  int n_w = 0, n_o = 0;
+  for (const Launch &L : launches) (L.kind == kKindWave ? n_w : n_o)++;
+  const bool two = overlap_env != 0 && n_w > 0 && (n_o > 0 || n_w > 1);
+  const bool three = two && overlap_env >= 3 && n_w > 1;
+  if (two) {
+    CUDA_TRY(cudaEventRecord(c->ev_fork, st));
+    CUDA_TRY(cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+    if (three) CUDA_TRY(cudaStreamWaitEvent(c->stream3, c->ev_fork, 0));
+  }
+  int wave_no = 0;
   for (int li = 0; li < nl; ++li) {
     const Launch &L = launches[li];
     BatchArgs a;
@@ -506,8 +522,19 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     a.redo = (int32_t *)c->d_redo.p;
     a.redo_filter = 0;
     a.dyn = nullptr;
-    int rc = issue_launch(c, lim, L, a.B, a, d_ctl + 2 * li, st);
+    const bool on2 = two && L.kind == kKindWave;
+    cudaStream_t ls = !on2 ? st : (three && (wave_no++ & 1)) ? c->stream3 : c->stream2;
+    // (only the 256-nt class re-runs with global tables: one user of d_ws2 at a time)
+    int rc = issue_launch(c, lim, L, a.B, a, d_ctl + 2 * li, ls, true, on2 ? &c->d_ws2 : nullptr);
     if (rc) return rc;
+  }
+  if (two) {
+    CUDA_TRY(cudaEventRecord(c->ev_join, c->stream2));
+    CUDA_TRY(cudaStreamWaitEvent(st, c->ev_join, 0));
+    if (three) {
+      CUDA_TRY(cudaEventRecord(c->ev_join3, c->stream3));
+      CUDA_TRY(cudaStreamWaitEvent(st, c->ev_join3, 0));
+    }
   }
   if (c->timed) CUDA_TRY(cudaEventRecord(c->ev1, st));
 
@@ -884,6 +911,8 @@ int rnafold_init(int device) {
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_staged, cudaEventDisableTiming));
   CUDA_TRY(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+  CUDA_TRY(cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_join3, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   CUDA_TRY(cudaMalloc((void **)&c->d_status, sizeof(int32_t)));
@@ -931,6 +960,8 @@ void rnafold_shutdown(void) {
   cudaEventDestroy(c->ev_fork);
   cudaEventDestroy(c->ev_join);
   cudaStreamDestroy(c->stream2);
+  cudaStreamDestroy(c->stream3);
+  cudaEventDestroy(c->ev_join3);
   cudaStreamDestroy(c->stream);
   delete c;
   g_ctx = nullptr;
