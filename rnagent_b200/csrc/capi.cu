@@ -373,30 +373,21 @@ int run_batch(Context *c, const uint8_t *seq, const int32_t *off, int32_t B, con
     int k = 0;
     while (k < B && len_at(k) > cluster_limit) ++k;
     if (k > 0) launches.push_back(Launch{0, k, len_at(0), len_at(0) <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal, false});
-    // 2-CTA cluster kernel (tables split over DSMEM) for lengths above the single-CTA kernel's reach.
-    // Few of them (no more than the clusters the device holds at once): ONE launch of the longest one's class, so that
-    // the call costs one long-fold latency instead of one per length class.
+    // 2-CTA cluster kernel (tables split over DSMEM) for lengths above the single-CTA kernel's reach: ONE launch of the
+    // longest one's class for all of them (the kernel runs one CTA per SM whatever the class, so separate classes would
+    // buy no occupancy, only one launch tail each; the queue is sorted longest first), cut only by the workspace cap.
     {
       int e_all = k;
       while (e_all < B && len_at(e_all) > wave_limit) ++e_all;
-      if (e_all > k && !getenv("RNAFOLD_NO_MERGE")) {
+      if (e_all > k) {
         int q0 = 0;
-        while (q0 < kNumClusterClasses && kClusterClasses[q0] < len_at(k)) ++q0;
-        if (q0 < kNumClusterClasses && e_all - k <= cached_occ(c, 1, kClusterClasses[q0], 2, 0)) {
-          launches.push_back(Launch{k, e_all, kClusterClasses[q0], kKindCluster, false});
-          k = e_all;
-        }
+        while (q0 + 1 < kNumClusterClasses && kClusterClasses[q0] < len_at(k)) ++q0;
+        const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q0]) * sizeof(int16_t);
+        const int chunk = (int)std::max<size_t>(1, kClusterWorkspaceCap / per_seq);
+        for (int s0 = k; s0 < e_all; s0 += chunk)
+          launches.push_back(Launch{s0, std::min(e_all, s0 + chunk), kClusterClasses[q0], kKindCluster, false});
+        k = e_all;
       }
-    }
-    for (int q = kNumClusterClasses - 1; q >= 0 && k < B; --q) {
-      if (kClusterClasses[q] > cluster_limit) continue;
-      const int lo = q > 0 ? std::max(kClusterClasses[q - 1], wave_limit) : wave_limit;
-      int e = k;
-      while (e < B && len_at(e) > lo) ++e;
-      const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q]) * sizeof(int16_t);
-      const int chunk = (int)std::max<size_t>(1, kClusterWorkspaceCap / per_seq);
-      for (int s0 = k; s0 < e; s0 += chunk) launches.push_back(Launch{s0, std::min(e, s0 + chunk), kClusterClasses[q], kKindCluster, false});
-      k = e;
     }
     if (k < B && B - k <= c->num_sms && !getenv("RNAFOLD_NO_MERGE")) {
       // fewer sequences than SMs: one launch of the longest sequence's class (every CTA has an SM to itself,
@@ -731,19 +722,21 @@ int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen,
     }
     lo = kWaveClasses[cls];
   }
-  lo = lim.wave_limit;
-  for (int q = 0; q < kNumClusterClasses; ++q) {
-    if (kClusterClasses[q] > lim.cluster_limit || kClusterClasses[q] <= lim.wave_limit) continue;
-    if (any_in(lo, kClusterClasses[q]) && (int)p->launches.size() < kMaxDynLaunches) {
-      const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q]) * sizeof(int16_t);
+  {
+    // one cluster launch, of the class of the longest cluster-length target (see run_batch)
+    int cmaxlen = 0;
+    for (int k = 0; k < nlen; ++k)
+      if (lengths[k] > lim.wave_limit && lengths[k] <= lim.cluster_limit) cmaxlen = std::max(cmaxlen, lengths[k]);
+    if (cmaxlen > 0 && (int)p->launches.size() < kMaxDynLaunches) {
+      int q0 = 0;
+      while (q0 + 1 < kNumClusterClasses && kClusterClasses[q0] < cmaxlen) ++q0;
+      const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q0]) * sizeof(int16_t);
       if (per_seq * (size_t)cap > kClusterWorkspaceCap) return fail(RNAFOLD_EINVAL, "device-routed batch too large for the cluster workspace");
-      p->launches.push_back(Launch{0, cap, kClusterClasses[q], kKindCluster, false});
-      rt.upper[p->launches.size() - 1] = kClusterClasses[q];
-      if (rt.cfirst < 0) rt.cfirst = (int)p->launches.size() - 1;
-      rt.clast = (int)p->launches.size() - 1;
-      rt.cmax = cached_occ(c, 1, kClusterClasses[q], 2, 0);
+      p->launches.push_back(Launch{0, cap, kClusterClasses[q0], kKindCluster, false});
+      rt.upper[p->launches.size() - 1] = lim.cluster_limit;
+      rt.cfirst = rt.clast = (int)p->launches.size() - 1;
+      rt.cmax = cached_occ(c, 1, kClusterClasses[q0], 2, 0);
     }
-    lo = kClusterClasses[q];
   }
   if (lmax > lim.cluster_limit && (int)p->launches.size() < kMaxDynLaunches) {
     p->launches.push_back(Launch{0, cap, lmax, lmax <= kLegacySmemLimit ? kKindLegacySmem : kKindLegacyGlobal, false});
