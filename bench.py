@@ -520,13 +520,21 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
     for k in range(steps):
         env.step_device(acts[settle + k], d_obs, d_r, d_done)
     torch.cuda.synchronize()
-    secs = max_over_ranks(time.perf_counter() - t0)
+    my_secs = time.perf_counter() - t0
+    secs = max_over_ranks(my_secs)
+    rank_us = [1e6 * my_secs / steps]
+    if world > 1:                                        # per-rank step times: is the maximum one slow rank or all of them?
+        g_ = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(g_, torch.tensor([rank_us[0]], dtype=torch.float64, device=dev))
+        rank_us = [float(t.item()) for t in g_]
+    my_episodes = env.stats().episodes
     stats = env.stats().all_reduce(device=dev)          # the path's only collective: rollout statistics over NCCL
     env.close()
     out["env"] = {"metric": "rl_env_steps_per_sec", "value": stats.steps / secs, "unit": "env steps/s",
                   "per_gpu": stats.steps / secs / world, "us_per_vector_step": 1e6 * secs / steps,
                   "episodes_per_s": stats.episodes / secs, "envs_per_gpu": N, "steps_timed": steps,
-                  "host_syncs_per_step": 0,
+                  "host_syncs_per_step": 0, "per_rank_us_per_vector_step": [round(v, 1) for v in rank_us],
+                  "sum_of_rank_rates": sum(N * 1e6 / v for v in rank_us),
                   "roofline": roof(stats.episodes / secs / world * synth.work_candidates(100),
                                    "terminal folds only (one per episode); the step is bound by ONE fold's latency, not by throughput"),
                   "workload": "4096 RnaDesign envs per GPU, n=100 targets (folds of random sequences), uniform random actions, "
