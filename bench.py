@@ -199,6 +199,11 @@ def measured_traffic(kernel_key):
         return None, None
 
 
+def arm_config(desc, folds_per_gpu, world):
+    return {"workload": desc, "folds_per_gpu_per_step": int(folds_per_gpu), "l2": "flushed between timed steps (256 MiB memset)",
+            "parallelism": f"dp{world} (independent shards, no data-path collective)"}
+
+
 def run_reference(args):
     """`--impl reference`: CPU path on all host threads, rank 0 only; same metric/unit/config."""
     rank = int(os.environ.get("RANK", "0"))
@@ -219,7 +224,9 @@ def run_reference(args):
         "impl": "reference", "metric": f"mfe_folds_per_sec_n{n_label}", "value": value, "unit": "folds/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": desc, "sample_per_step": sample, "us_per_fold_per_thread": 1e6 * cores / value},
+        # the same `config` as the GPU arm (it names the workload); what this arm folded per step is stated beside it
+        "config": arm_config(desc, len(off) - 1, args.gpus),
+        "sample_per_step": sample, "us_per_fold_per_thread": 1e6 * cores / value,
         "cpu_baseline": {"value": value, "unit": "folds/s", "cores": cores, "kind": "port",
                          "sample": f"first {sample} sequences of the workload per step, OpenMP over {cores} host threads; "
                                    "oracle port of ViennaRNA 2.4.14 RNA.fold (ViennaRNA itself is not in the "
@@ -390,8 +397,7 @@ def run_ours(args):
         "unit": "folds/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": resident_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int16 tables / int32 arithmetic (int32 re-run of sequences that leave the int16 range)", "data": "synthetic",
-        "config": {"workload": desc, "folds_per_gpu_per_step": B, "l2": "flushed between timed steps (256 MiB memset)",
-                   "parallelism": f"dp{world} (independent shards, no data-path collective)"},
+        "config": arm_config(desc, B, world),
         "e2e": {"value": world * B * args.steps / e2e_s, "unit": "folds/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h},
         "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
