@@ -194,18 +194,30 @@ int rnafold_env_config_permute(int32_t handle, int32_t enabled, int32_t budget, 
  * as the `md` / `ed` columns by rlif/utils/comparison.py:225-233) for a batch: McCaskill partition function and base-pair
  * probabilities of the same loop model (dangles=2), fp64 on the GPU.  `structure` / `e_dcal` are the fold and energy of every
  * sequence (what rnafold_fold_batch returns: fc.mfe()); `target` (may be NULL) the dot-bracket targets for the mountain
- * distance.  stats_out[B][6] = { ensemble free energy kcal/mol (fc.pf()[1]), ensemble defect of `structure`
- * (fc.ensemble_defect(fold)), its probability (fc.pr_structure(fold)), mean base-pair distance (fc.mean_bp_distance()),
- * distance of the centroid to the ensemble (fc.centroid()[1]), mountain distance RNA.dist_mountain(target, fold) }.
+ * distance.  stats_out[B][RNAFOLD_ENSEMBLE_STATS] = { ensemble free energy kcal/mol (fc.pf()[1]), ensemble defect of
+ * `structure` (fc.ensemble_defect(fold)), its probability (fc.pr_structure(fold)), mean base-pair distance
+ * (fc.mean_bp_distance()), distance of the centroid to the ensemble (fc.centroid()[1]), mountain distance
+ * RNA.dist_mountain(target, fold), expected accuracy of the MEA structure (fc.MEA()[1]), energy of the centroid
+ * (fc.eval_structure(centroid), kcal/mol), energy of the MEA structure (solution.py:232-234) }.
  * Optional: centroid_out (CSR bytes like seq: pairs with p > 0.5, fc.centroid()[0]); pos_out[total][3] = P(paired with a
  * base downstream), P(paired upstream), positional entropy in bits (fc.positional_entropy(); the first two give the pair
- * propensity string of fc.pf()[0]); bpp_out (single-sequence calls only: n x n row-major, upper triangle).
- * off must be a host array; the other buffers may be host or device pointers.  Synchronous.  MEA structures and
- * eval_structure of the centroid (solution.py:231-233) are not part of this entry point. */
+ * propensity string of fc.pf()[0]); bpp_out (single-sequence calls only: n x n row-major, upper triangle); mea_out (CSR
+ * bytes: the maximum-expected-accuracy structure fc.MEA()[0] for pair weight mea_gamma > 0; the reference uses the default 1).
+ * off must be a host array; the other buffers may be host or device pointers.  Synchronous. */
 #define RNAFOLD_ENSEMBLE_MAX_LEN 1000
+#define RNAFOLD_ENSEMBLE_STATS 9
 int rnafold_ensemble_batch(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *structure,
                            const int32_t *e_dcal, const uint8_t *target, double *stats_out, uint8_t *centroid_out,
-                           double *pos_out, double *bpp_out);
+                           double *pos_out, double *bpp_out, double mea_gamma, uint8_t *mea_out);
+
+/* Free energy of GIVEN structures (fc.eval_structure(structure) of ViennaRNA 2.4.14 on the reference's model, dangles=2;
+ * rlif/rna/solution.py:232,234) for a batch: one CTA per sequence, the loops of a structure spread over its threads.
+ * structure: dot-bracket bytes, CSR like seq.  e_dcal_out[B]: energies in dcal/mol (x / 100 = kcal/mol), loops of any size
+ * (interior loops above 30 unpaired bases take the lxc * log(u / 30) extrapolation).  err_out[B] (may be NULL): 0, 1 = a
+ * bracket pair that cannot pair or a hairpin of fewer than 3 bases, 3 = unbalanced brackets (energy 0 then).
+ * off must be a host array; the other buffers may be host or device pointers.  Synchronous. */
+int rnafold_eval_structure_batch(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *structure,
+                                 int32_t *e_dcal_out, int32_t *err_out);
 
 /* Measurement helper (bench.py): on-box peaks of the two on-chip resources that bound the fold DP,
  * whole device: conflict-free 4-byte shared-memory loads per second and integer add+min

@@ -49,6 +49,7 @@ def lib():
                              ctypes.c_void_p, ctypes.c_char_p, ctypes.c_void_p]
         L.orc_dist_mountain.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_int]
         L.orc_dist_mountain.restype = ctypes.c_double
+        L.orc_mea.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_char_p, ctypes.c_void_p]
         L.orc_pf_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                    ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
         _lib = L
@@ -119,6 +120,16 @@ class Params:
             out["bpp"] = mat
         return out
 
+    def statistics(self, seq, structure, e_dcal, gamma=1.0):
+        """Everything Solution.compute_statistics sets (rlif/rna/solution.py:221-238): pf() plus the centroid's energy, the
+        MEA structure (fc.MEA(), gamma = 1), its expected accuracy and its energy (kcal/mol as fc.eval_structure returns)."""
+        out = self.pf(seq, structure, e_dcal, bpp=True)
+        s, v = mea(out["bpp"], gamma)
+        out["MEA_structure"], out["MEA"] = s, v
+        out["centroid_en"] = self.eval_structure(seq, out["centroid_structure"]) / 100.0
+        out["MEA_en"] = self.eval_structure(seq, s) / 100.0
+        return out
+
     def pf_batch(self, seqs_u8, off, structs_u8, mfe_dcal, smooth=True, nthreads=0):
         B = len(off) - 1
         out = np.zeros((B, 5), dtype=np.float64)
@@ -168,6 +179,18 @@ def hamming_distance(a, b):
     """rlif/rna/utils.py:67-75 restated: zip-truncating; returns (hd, mismatch indices)."""
     m = [x != y for x, y in zip(a, b)]
     return sum(m), np.where(m)[0]
+
+
+def mea(bpp, gamma=1.0):
+    """fc.MEA(gamma) from a base-pair probability matrix (n x n, upper triangle) -> (structure, expected accuracy)."""
+    mat = np.ascontiguousarray(bpp, dtype=np.float64)
+    n = mat.shape[0]
+    buf = ctypes.create_string_buffer(n + 1)
+    val = np.zeros(1, dtype=np.float64)
+    rc = lib().orc_mea(mat.ctypes.data, n, float(gamma), buf, val.ctypes.data)
+    if rc:
+        raise RuntimeError("orc_mea: backtracking failed")
+    return buf.value.decode(), float(val[0])
 
 
 def dist_mountain(a, b, weighted=True):

@@ -643,7 +643,7 @@ static int eval_loop(const orc_params *P, const char *seq, const short *S, const
   if (nb == 1) {
     int t2 = PAIR[S[p1]][S[q1]];
     if (!t2) { *err = 1; return 0; }
-    if ((p1 - i - 1) + (j - q1 - 1) > MAXLOOP) { *err = 2; return 0; }
+    /* any loop size: fc.eval_structure extrapolates above MAXLOOP (the folding recursions never build such a loop) */
     return e_intloop(P, p1 - i - 1, j - q1 - 1, type, RTYPE[t2], S[i + 1], S[j - 1], S[p1 - 1], S[q1 + 1]) +
            eval_loop(P, seq, S, pt, n, p1, q1, err);
   }

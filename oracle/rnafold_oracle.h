@@ -101,6 +101,9 @@ int orc_pf(const orc_params *P, const char *seq, int n, const char *structure, i
            char *centroid, double *bpp);
 /* RNA.dist_mountain(a, b) as ViennaRNA 2.4.14 computes it (see rnafold_pf.c); weighted must be non-zero for parity. */
 double orc_dist_mountain(const char *a, const char *b, int n, int weighted);
+/* fc.MEA() (gamma = 1 in the reference): maximum expected accuracy structure from orc_pf's base-pair probability matrix
+ * (n x n row-major upper triangle); structure holds n + 1 chars.  Returns 0, or -1 if backtracking failed. */
+int orc_mea(const double *bpp, int n, double gamma, char *structure, double *mea_out);
 /* Batched (OpenMP): stats_out[B][ORC_PF_NSTATS]; structures / e_dcal as returned by orc_fold_batch. */
 int orc_pf_batch(const orc_params *P, const char *seqs, const int *off, int B, const char *structures, const int *e_dcal,
                  int smooth, double *stats_out, int nthreads);

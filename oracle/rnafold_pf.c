@@ -390,3 +390,107 @@ int orc_pf_batch(const orc_params *P, const char *seqs, const int *off, int B, c
   }
   return rc;
 }
+
+/* ------------------------------------------------------------------ maximum expected accuracy structure
+ * fc.MEA() of ViennaRNA 2.4.14 (rlif/rna/solution.py:233; gamma = 1): restated from the published algorithm of MEA.c --
+ *   pu[i] = 1 - sum of the listed pair probabilities of i, the list holding pairs with p >= 1e-4 / (1 + gamma);
+ *   a pair is a candidate when 2 gamma p > pu[i] + pu[j];
+ *   M(i,j) = max( M(i,j-1) + pu[j],  max_k M(i,k-1) + A(k,j) ),  A(k,j) = 2 gamma p(k,j) + M(k+1,j-1),
+ *   rows i = n .. 1 kept two at a time, A(k,j) remembered in a per-j list only where the pair strictly improved M(k,j);
+ *   backtracking re-derives a row per enclosed interval and accepts equality within DBL_EPSILON * M.
+ * PARITY UNPINNED: the reference logs no MEA column and the library is absent, so this is checked against the definition
+ * only (enumeration over all structures, tests/test_oracle_golden.py); the value does not depend on tie-breaking, the
+ * structure could where two optima tie exactly.
+ * bpp: n x n row-major upper triangle (orc_pf's bpp_out).  structure: n + 1 chars. */
+typedef struct { int i; double A; } mea_item;
+typedef struct { mea_item *v; int n, cap; } mea_list;
+
+static void mea_push(mea_list *L, int i, double A) {
+  if (L->n == L->cap) {
+    L->cap = L->cap ? 2 * L->cap : 4;
+    L->v = (mea_item *)realloc(L->v, sizeof(mea_item) * (size_t)L->cap);
+  }
+  L->v[L->n].i = i;
+  L->v[L->n].A = A;
+  L->n++;
+}
+
+static void mea_row(const mea_list *C, const double *pu, double *Mi, int i, int j) {
+  /* Mi[i-1 .. j] of the interval that starts at i, from the remembered candidates */
+  Mi[i - 1] = 0.;
+  Mi[i] = pu[i];
+  for (int k = i + 1; k <= j; k++) {
+    Mi[k] = Mi[k - 1] + pu[k];
+    for (int t = 0; t < C[k].n && C[k].v[t].i >= i; t++) {
+      const double EA = C[k].v[t].A + Mi[C[k].v[t].i - 1];
+      if (EA > Mi[k]) Mi[k] = EA;
+    }
+  }
+}
+
+static int mea_backtrack(const mea_list *C, const double *pu, double *Mi, char *structure, int i, int j, int pair) {
+  if (pair) {
+    structure[i - 1] = '(';
+    structure[j - 1] = ')';
+    i++;
+    j--;
+    if (j < i) return 0;
+    mea_row(C, pu, Mi, i, j);
+  }
+  const double prec = 2.220446049250313e-16 * Mi[j];
+  while (j > i && Mi[j] <= Mi[j - 1] + pu[j] + prec) j--;
+  if (j <= i) return 0;
+  for (int t = 0; t < C[j].n && C[j].v[t].i >= i; t++) {
+    const int k = C[j].v[t].i;
+    if (Mi[j] <= C[j].v[t].A + Mi[k - 1] + prec) {
+      if (k > i + 3) {
+        /* the left part keeps the row of i: the recursion below only reads entries <= k-1 */
+        if (mea_backtrack(C, pu, Mi, structure, i, k - 1, 0)) return -1;
+      }
+      return mea_backtrack(C, pu, Mi, structure, k, j, 1);
+    }
+  }
+  return -1;
+}
+
+int orc_mea(const double *bpp, int n, double gamma, char *structure, double *mea_out) {
+  for (int k = 0; k < n; k++) structure[k] = '.';
+  structure[n > 0 ? n : 0] = 0;
+  *mea_out = 0.;
+  if (n <= 0) return 0;
+  const double cut = 1e-4 / (1. + gamma);
+  double *pu = (double *)malloc(sizeof(double) * (size_t)(n + 2));
+  double *Mi = (double *)calloc((size_t)n + 2, sizeof(double)), *Mi1 = (double *)calloc((size_t)n + 2, sizeof(double));
+  mea_list *C = (mea_list *)calloc((size_t)n + 2, sizeof(mea_list));
+  for (int i = 0; i <= n + 1; i++) pu[i] = 1.;
+  for (int i = 1; i <= n; i++)
+    for (int j = i + 1; j <= n; j++) {
+      const double p = bpp[(size_t)(i - 1) * n + (j - 1)];
+      if (p >= cut) { pu[i] -= p; pu[j] -= p; }
+    }
+  for (int i = n; i > 0; i--) {
+    Mi[i] = pu[i];
+    for (int j = i + 1; j <= n; j++) {
+      Mi[j] = Mi[j - 1] + pu[j];
+      for (int t = 0; t < C[j].n; t++) {
+        const double EA = C[j].v[t].A + Mi[C[j].v[t].i - 1];
+        if (EA > Mi[j]) Mi[j] = EA;
+      }
+      const double p = bpp[(size_t)(i - 1) * n + (j - 1)];
+      if (p >= cut && p * 2. * gamma > pu[i] + pu[j]) {
+        const double EA = 2. * gamma * p + Mi1[j - 1];
+        if (Mi[j] < EA) {
+          Mi[j] = EA;
+          mea_push(&C[j], i, EA);
+        }
+      }
+    }
+    double *t = Mi1; Mi1 = Mi; Mi = t;
+  }
+  *mea_out = Mi1[n];
+  /* the row of i = 1 is in Mi1 */
+  int rc = mea_backtrack(C, pu, Mi1, structure, 1, n, 0);
+  for (int k = 0; k <= n + 1; k++) free(C[k].v);
+  free(C); free(Mi); free(Mi1); free(pu);
+  return rc;
+}

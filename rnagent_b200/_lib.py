@@ -20,7 +20,7 @@ EXPORTS = [
     "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes", "rnafold_current_device",
     "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_config_reward", "rnafold_env_set_current", "rnafold_env_set_targets", "rnafold_env_reset",
     "rnafold_env_step", "rnafold_env_stats", "rnafold_env_snapshot", "rnafold_parse_target",
-    "rnafold_ensemble_batch", "rnafold_permute_batch", "rnafold_permute_draw", "rnafold_permute_set_order", "rnafold_permute_candidate_order", "rnafold_env_config_permute",
+    "rnafold_ensemble_batch", "rnafold_eval_structure_batch", "rnafold_permute_batch", "rnafold_permute_draw", "rnafold_permute_set_order", "rnafold_permute_candidate_order", "rnafold_env_config_permute",
 ]
 
 _lock = threading.Lock()
@@ -77,7 +77,8 @@ def load_library():
         L.rnafold_parse_target.argtypes = [vp, ci, vp, vp]
         L.rnafold_permute_batch.argtypes = [vp, vp, ci, vp, ci, ci, ci, cd, ci, u64, cd, vp, vp, vp, vp, vp, i32p]
         L.rnafold_permute_draw.argtypes = [u64, ci, ci, ci, ci]
-        L.rnafold_ensemble_batch.argtypes = [vp, vp, ci, vp, vp, vp, vp, vp, vp, vp]
+        L.rnafold_ensemble_batch.argtypes = [vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, ctypes.c_double, vp]
+        L.rnafold_eval_structure_batch.argtypes = [vp, vp, ci, vp, vp, vp]
         L.rnafold_permute_draw.restype = u64
         L.rnafold_permute_set_order.argtypes = [ci]
         L.rnafold_permute_candidate_order.argtypes = [vp, ci, ci, ci, vp]

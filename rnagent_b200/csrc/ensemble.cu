@@ -31,6 +31,7 @@
 
 #include "../../include/rnafold_b200.h"
 #include "energy.cuh"
+#include "evaluate.cuh"
 #include "fold_kernels.h"
 
 namespace rnafold {
@@ -177,7 +178,8 @@ __device__ __forceinline__ double warp_sum(double v) {
 constexpr int kEnsThreads = 256;
 constexpr int kEnsWarps = kEnsThreads / 32;
 constexpr int kEnsTables = 10;
-constexpr int kEnsStats = 6;  // F, ensemble defect, p(structure), mean bp distance, centroid distance, mountain distance
+// F, ensemble defect, p(structure), mean bp distance, centroid distance, mountain distance, MEA, centroid energy, MEA energy
+constexpr int kEnsStats = RNAFOLD_ENSEMBLE_STATS;
 
 struct EnsArgs {
   const uint8_t *seq;
@@ -190,6 +192,8 @@ struct EnsArgs {
   uint8_t *centroid;       // CSR like seq, or nullptr
   double *pos;             // [total][3]: P(paired with a downstream base), P(paired upstream), positional entropy (bits); or nullptr
   double *bpp;             // single-sequence calls only: n * n row-major upper triangle, or nullptr
+  uint8_t *mea;            // maximum-expected-accuracy structure, CSR like seq, or nullptr
+  double gamma;            // its pair weight (fc.MEA() default 1)
 };
 
 __global__ void __launch_bounds__(kEnsThreads)
@@ -202,8 +206,10 @@ ensemble_kernel(const ExpParams *__restrict__ E, const FoldParams *__restrict__ 
   double *red = bpow + np;                       // [8] block-level accumulators
   int *pt = reinterpret_cast<int *>(red + 8);    // pair table of the reported structure
   int *pt2 = pt + np;                            // pair table of the target / stack scratch
-  int *misc = pt2 + np;
-  unsigned char *S = reinterpret_cast<unsigned char *>(misc + 4);
+  int *ptc = pt2 + np;                           // pair table of the centroid
+  int *ptm = ptc + np;                           // pair table of the MEA structure
+  int *misc = ptm + np;
+  unsigned char *S = reinterpret_cast<unsigned char *>(misc + 8);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double *base = ws + (long long)blockIdx.x * ws_stride;
 
@@ -383,9 +389,13 @@ ensemble_kernel(const ExpParams *__restrict__ E, const FoldParams *__restrict__ 
     }
     __syncthreads();
     double mbd = 0., cdist = 0., ed = 0.;
+    const double mea_cut = 1e-4 / (1. + a.gamma);   // fc.MEA() lists the pairs with p >= 1e-4 / (1 + gamma)
+    double *pu_mea = scale;                         // the scaling powers are not needed any more
     for (int i = 1 + tid; i <= n; i += kEnsThreads) {
       double up = 0., down = 0., ent = 0.;   // paired with a downstream base (j > i) / an upstream one
+      double listed = 0.;
       char cen = '.';
+      int cpart = 0;
       for (int j = 1; j <= n; ++j) {
         if (j == i) continue;
         const int lo = min(i, j), hi = max(i, j);
@@ -398,9 +408,16 @@ ensemble_kernel(const ExpParams *__restrict__ E, const FoldParams *__restrict__ 
           cdist += (p > 0.5) ? 1. - p : p;
           if (a.bpp) a.bpp[(size_t)(i - 1) * n + (j - 1)] = p;
         } else up += p;
-        if (p > 0.5) cen = (j > i) ? '(' : ')';
+        if (p > 0.5) {
+          cen = (j > i) ? '(' : ')';
+          cpart = j;
+        }
+        if (p >= mea_cut) listed += p;
         ent -= p * log(p);
       }
+      ptc[i] = cpart;
+      ptm[i] = 0;
+      pu_mea[i] = 1. - listed;
       const double pu = 1. - up - down;
       if (pu > 0.) ent -= pu * log(pu);
       if (a.pos) {
@@ -451,13 +468,94 @@ ensemble_kernel(const ExpParams *__restrict__ E, const FoldParams *__restrict__ 
       }
       st[5] = md;
     }
+    // ---------------- fc.MEA(gamma): maximum expected accuracy structure (rlif/rna/solution.py:233)
+    //   M(i,j) = max( M(i,j-1) + pu[j],  max_{i<k} M(i,k-1) + A(k,j),  A(i,j) ),   A(i,j) = 2 gamma P(i,j) + M(i+1,j-1)
+    // over the listed pairs with 2 gamma P > pu[i] + pu[j]; as the library does, a pair's A is remembered only where it
+    // strictly improved M(i,j).  The library rolls two rows and re-derives rows while backtracking; here the whole table is
+    // filled by anti-diagonals (a warp per cell, lanes across k), M in the W table, A transposed in XT (0 = no candidate).
+    {
+      double *M = W, *AT = XT;
+      const double g2 = 2. * a.gamma;
+      __syncthreads();
+      for (size_t k = tid; k < NN; k += kEnsThreads) AT[k] = 0.;
+      for (int i = 1 + tid; i <= n + 1; i += kEnsThreads) {
+        M[IX(i, i - 1)] = 0.;
+        if (i <= n) M[IX(i, i)] = pu_mea[i];
+      }
+      __syncthreads();
+      for (int d = 1; d < n; ++d) {
+        for (int i = 1 + warp; i + d <= n; i += kEnsWarps) {
+          const int j = i + d;
+          double best = M[IX(i, j - 1)] + pu_mea[j];
+          for (int k = i + 1 + lane; k <= j - kTurn - 1; k += 32) {
+            const double A = AT[IX(j, k)];
+            if (A > 0.) best = fmax(best, A + M[IX(i, k - 1)]);
+          }
+          for (int o = 16; o; o >>= 1) best = fmax(best, __shfl_xor_sync(0xffffffffu, best, o));
+          if (lane == 0) {
+            if (d > kTurn) {
+              const double p = po[IX(i, j)] * qb[IX(i, j)];
+              if (p >= mea_cut && p * g2 > pu_mea[i] + pu_mea[j]) {
+                const double EA = g2 * p + M[IX(i + 1, j - 1)];
+                if (best < EA) {
+                  best = EA;
+                  AT[IX(j, i)] = EA;
+                }
+              }
+            }
+            M[IX(i, j)] = best;
+          }
+        }
+        __syncthreads();
+      }
+      if (tid == 0) {   // backtracking: intervals on a stack (the YT table is free), accepting equality within DBL_EPSILON * M
+        int *stk = reinterpret_cast<int *>(YT);
+        int top = 0;
+        stk[top++] = 1;
+        stk[top++] = n;
+        while (top > 0) {
+          int j = stk[--top];
+          const int i = stk[--top];
+          if (j <= i) continue;
+          const double prec = 2.220446049250313e-16 * M[IX(i, j)];
+          while (j > i && M[IX(i, j)] <= M[IX(i, j - 1)] + pu_mea[j] + prec) --j;
+          if (j <= i) continue;
+          for (int k = j - kTurn - 1; k >= i; --k) {
+            const double A = AT[IX(j, k)];
+            if (A > 0. && M[IX(i, j)] <= A + M[IX(i, k - 1)] + prec) {
+              ptm[k] = j;
+              ptm[j] = k;
+              if (k > i + 3) {
+                stk[top++] = i;
+                stk[top++] = k - 1;
+              }
+              stk[top++] = k + 1;
+              stk[top++] = j - 1;
+              break;
+            }
+          }
+        }
+        st[6] = M[IX(1, n)];
+      }
+      __syncthreads();
+      if (a.mea)
+        for (int i = 1 + tid; i <= n; i += kEnsThreads) a.mea[beg + i - 1] = (uint8_t)(ptm[i] == 0 ? '.' : ptm[i] > i ? '(' : ')');
+      // fc.eval_structure of the centroid and of the MEA structure (solution.py:232,234), kcal/mol
+      int err = 0;
+      const int e_cen = eval_structure_cta(gp->s, gp, S, ptc, n, misc + 2, &err);
+      const int e_mea = eval_structure_cta(gp->s, gp, S, ptm, n, misc + 2, &err);
+      if (tid == 0) {
+        st[7] = e_cen / 100.;
+        st[8] = e_mea / 100.;
+      }
+    }
 #undef IX
   }
 }
 
 size_t ens_smem_bytes(int nmax) {
   const int np = (nmax + 4 + 3) & ~3;
-  return (size_t)np * 16 + 64 + (size_t)np * 8 + 16 + (size_t)np + 16;
+  return (size_t)np * 16 + 64 + (size_t)np * 16 + 32 + (size_t)np + 16;
 }
 
 struct EnsContext {
@@ -489,7 +587,8 @@ using namespace rnafold;
 
 extern "C" int rnafold_ensemble_batch(const uint8_t *seq, const int32_t *off, int32_t B, const uint8_t *structure,
                                       const int32_t *e_dcal, const uint8_t *target, double *stats_out,
-                                      uint8_t *centroid_out, double *pos_out, double *bpp_out) {
+                                      uint8_t *centroid_out, double *pos_out, double *bpp_out, double mea_gamma,
+                                      uint8_t *mea_out) {
   std::lock_guard<std::mutex> lk(g_ens_mu);
   std::vector<void *> tmp;
   CtxView cv;
@@ -497,6 +596,7 @@ extern "C" int rnafold_ensemble_batch(const uint8_t *seq, const int32_t *off, in
   if (B < 0 || !off || (B > 0 && (!seq || !structure || !e_dcal || !stats_out)))
     return set_error(RNAFOLD_EINVAL, "ensemble: null seq / off / structure / energies / stats or negative batch size");
   if (B == 0) return RNAFOLD_OK;
+  if (!(mea_gamma > 0.)) return set_error(RNAFOLD_EINVAL, "ensemble: the MEA pair weight gamma must be positive");
   if (bpp_out && B != 1) return set_error(RNAFOLD_EINVAL, "ensemble: the base-pair probability matrix is returned for single-sequence calls only");
   if (off[0] != 0) return set_error(RNAFOLD_EINVAL, "off[0] must be 0");
   int nmax = 0;
@@ -544,6 +644,8 @@ extern "C" int rnafold_ensemble_batch(const uint8_t *seq, const int32_t *off, in
     a.bpp = (double *)p;
     ENS_TRY(cudaMemsetAsync(p, 0, sizeof(double) * (size_t)nmax * nmax, st));
   }
+  if (mea_out) { ENS_TRY(stage(nullptr, total, &p)); a.mea = (uint8_t *)p; }
+  a.gamma = mea_gamma;
   a.B = B;
   const long long stride = (long long)kEnsTables * (nmax + 2) * (nmax + 2);
   int grid = std::min(B, cv.num_sms);
@@ -566,6 +668,7 @@ extern "C" int rnafold_ensemble_batch(const uint8_t *seq, const int32_t *off, in
   if (centroid_out) ENS_TRY(cudaMemcpyAsync(centroid_out, a.centroid, total, cudaMemcpyDefault, st));
   if (pos_out) ENS_TRY(cudaMemcpyAsync(pos_out, a.pos, sizeof(double) * 3 * total, cudaMemcpyDefault, st));
   if (bpp_out) ENS_TRY(cudaMemcpyAsync(bpp_out, a.bpp, sizeof(double) * (size_t)nmax * nmax, cudaMemcpyDefault, st));
+  if (mea_out) ENS_TRY(cudaMemcpyAsync(mea_out, a.mea, total, cudaMemcpyDefault, st));
   ENS_TRY(cudaStreamSynchronize(st));
   for (void *q : tmp) cudaFree(q);
   return RNAFOLD_OK;

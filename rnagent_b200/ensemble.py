@@ -10,14 +10,18 @@ reference derives from them.
     ensemble_diversity = fc.mean_bp_distance()             ensemble_diversity[k]
     ensemble_defect = fc.ensemble_defect(fold)             ensemble_defect[k]   (the `ed` column of rlif/logs/*)
     md = RNA.dist_mountain(target.seq, fold)               md[k]                (the `md` column)
-    centroid_en, MEA_structure, MEA, MEA_en                not built (None)
+    centroid_en = fc.eval_structure(centroid)              centroid_en[k]       (kcal/mol)
+    MEA_structure, MEA = fc.MEA()                          MEA_structure[k], MEA[k]   (gamma = 1; parity unpinned: no logged column)
+    MEA_en = fc.eval_structure(MEA_structure)              MEA_en[k]
+
+`eval_structure_batch` is fc.eval_structure for any batch of (sequence, structure) pairs (rnafold_eval_structure_batch).
 """
 import numpy as np
 
 from . import _lib
 from .vienna import pack, unpack
 
-STATS = ("ensemble_energy", "ensemble_defect", "probability", "ensemble_diversity", "centroid_dist", "md")
+STATS = ("ensemble_energy", "ensemble_defect", "probability", "ensemble_diversity", "centroid_dist", "md", "MEA", "centroid_en", "MEA_en")
 
 
 def propensity_string(down, up):
@@ -42,11 +46,12 @@ def propensity_string(down, up):
 
 
 class EnsembleResult(object):
-    def __init__(self, seqs, structures, mfe, stats, centroids, pos, off, bpp=None):
+    def __init__(self, seqs, structures, mfe, stats, centroids, pos, off, bpp=None, mea=None):
         self.sequences, self.structures, self.mfe = seqs, structures, mfe
         for k, name in enumerate(STATS):
             setattr(self, name, stats[:, k].copy())
         self.centroid_structure = centroids
+        self.MEA_structure = mea
         self.positional_entropy = [pos[off[k]:off[k + 1], 2].copy() for k in range(len(seqs))]
         self.propensity = [propensity_string(pos[off[k]:off[k + 1], 0], pos[off[k]:off[k + 1], 1]) for k in range(len(seqs))]
         self.bpp = bpp
@@ -55,9 +60,9 @@ class EnsembleResult(object):
         return len(self.sequences)
 
 
-def ensemble_batch(seqs, targets=None, structures=None, mfe_dcal=None, bpp=False):
+def ensemble_batch(seqs, targets=None, structures=None, mfe_dcal=None, bpp=False, gamma=1.0):
     """Statistics of every sequence's ensemble.  `structures` / `mfe_dcal` default to the sequences' own folds (fc.mfe());
-    `targets` (dot-bracket strings) are only needed for the mountain distance."""
+    `targets` (dot-bracket strings) are only needed for the mountain distance; `gamma` is fc.MEA()'s pair weight."""
     L = _lib.lib()
     seqs = list(seqs)
     B = len(seqs)
@@ -81,6 +86,7 @@ def ensemble_batch(seqs, targets=None, structures=None, mfe_dcal=None, bpp=False
         tgt = np.frombuffer(''.join(targets).encode(), dtype=np.uint8).copy()
     stats = np.zeros((B, len(STATS)), dtype=np.float64)
     cen = np.zeros_like(buf)
+    mea = np.zeros_like(buf)
     pos = np.zeros((len(buf), 3), dtype=np.float64)
     mat = None
     if bpp:
@@ -88,7 +94,30 @@ def ensemble_batch(seqs, targets=None, structures=None, mfe_dcal=None, bpp=False
             raise ValueError("bpp=True needs a single sequence")
         mat = np.zeros((len(seqs[0]), len(seqs[0])), dtype=np.float64)
     _lib.check(L.rnafold_ensemble_batch(_lib._ptr(buf), _lib._ptr(off), B, _lib._ptr(db), _lib._ptr(mfe), _lib._ptr(tgt),
-                                        _lib._ptr(stats), _lib._ptr(cen), _lib._ptr(pos), _lib._ptr(mat)))
+                                        _lib._ptr(stats), _lib._ptr(cen), _lib._ptr(pos), _lib._ptr(mat),
+                                        float(gamma), _lib._ptr(mea)))
     if targets is None:
         stats[:, 5] = np.nan
-    return EnsembleResult(seqs, structures, mfe, stats, unpack(cen, off), pos, off, mat)
+    return EnsembleResult(seqs, structures, mfe, stats, unpack(cen, off), pos, off, mat, unpack(mea, off))
+
+
+def eval_structure_batch(seqs, structures, strict=True):
+    """fc.eval_structure(structure) for every (sequence, structure) pair -> int32 energies in dcal/mol (x / 100 = kcal/mol)
+    on the GPU.  strict: raise ValueError on unbalanced brackets, bracket pairs that cannot pair or hairpins under 3 bases;
+    otherwise return (energies, codes)."""
+    L = _lib.lib()
+    seqs, structures = list(seqs), list(structures)
+    if [len(s) for s in structures] != [len(s) for s in seqs]:
+        raise ValueError("structures and sequences differ in length")
+    B = len(seqs)
+    buf, off = pack(seqs)
+    db = np.frombuffer(''.join(structures).encode(), dtype=np.uint8).copy()
+    e = np.zeros(B, dtype=np.int32)
+    codes = np.zeros(B, dtype=np.int32)
+    _lib.check(L.rnafold_eval_structure_batch(_lib._ptr(buf), _lib._ptr(off), B, _lib._ptr(db), _lib._ptr(e), _lib._ptr(codes)))
+    if strict:
+        bad = np.flatnonzero(codes)
+        if len(bad):
+            raise ValueError("eval_structure: structure %d is invalid (code %d)" % (int(bad[0]), int(codes[bad[0]])))
+        return e
+    return e, codes

@@ -161,13 +161,15 @@ class Solution(object):
 
     def compute_statistics(self):
         """Partition function, centroid, ensemble defect / diversity, mountain distance of the current string on the GPU
-        (rnafold_ensemble_batch).  centroid_en and the MEA_* attributes stay None (not built)."""
+        (rnafold_ensemble_batch), with the centroid's and the MEA structure's energies (fc.eval_structure) in kcal/mol."""
         from .ensemble import ensemble_batch
         res = ensemble_batch([self.string], targets=[self.target.seq])
         self.partition_prob, self.partition_fn = res.propensity[0], float(res.ensemble_energy[0])
         self.positional_entropy = res.positional_entropy[0]
         self.centroid_structure, self.centroid_dist = res.centroid_structure[0], float(res.centroid_dist[0])
         self.probability = float(res.probability[0])
+        self.centroid_en = float(res.centroid_en[0])
+        self.MEA_structure, self.MEA, self.MEA_en = res.MEA_structure[0], float(res.MEA[0]), float(res.MEA_en[0])
         self.ensemble_diversity = float(res.ensemble_diversity[0])
         self.ensemble_defect = float(res.ensemble_defect[0])
         self.md = float(res.md[0])

@@ -51,6 +51,12 @@ def test_against_the_oracle(oracle_params, setno, name):
             got = getattr(res, key)[k]
             assert abs(got - want[key]) <= RTOL * max(1.0, abs(want[key])), (k, len(s), key, got, want[key])
         assert res.centroid_structure[k] == want["centroid_structure"]
+        # fc.MEA() and the two fc.eval_structure calls (solution.py:232-234): value to 1e-9, structures and energies exact
+        mea_s, mea_v = oracle.mea(want["bpp"], 1.0)
+        assert abs(res.MEA[k] - mea_v) <= RTOL * max(1.0, mea_v), (k, len(s), res.MEA[k], mea_v)
+        assert res.MEA_structure[k] == mea_s, (k, len(s))
+        assert res.centroid_en[k] == P.eval_structure(s, want["centroid_structure"]) / 100.0
+        assert res.MEA_en[k] == P.eval_structure(s, mea_s) / 100.0
         assert abs(res.md[k] - oracle.dist_mountain(targets[k], st)) < 1e-12
         full = want["bpp"] + want["bpp"].T
         down = np.triu(want["bpp"]).sum(axis=1)
@@ -59,6 +65,11 @@ def test_against_the_oracle(oracle_params, setno, name):
         with np.errstate(divide="ignore", invalid="ignore"):
             ent = -(np.where(full > 0, full * np.log(full), 0.0).sum(axis=1) + np.where(pu > 0, pu * np.log(pu), 0.0)) / np.log(2.0)
         assert np.abs(res.positional_entropy[k] - ent).max() < 1e-9
+    wide = rb.ensemble_batch(seqs[20:40], gamma=3.0)          # a larger pair weight lists and keeps more pairs
+    for k, s in enumerate(seqs[20:40]):
+        st, e = P.fold_dcal(s)
+        mea_s, mea_v = oracle.mea(P.pf(s, st, e, bpp=True)["bpp"], 3.0)
+        assert wide.MEA_structure[k] == mea_s and abs(wide.MEA[k] - mea_v) <= RTOL * mea_v
     one = rb.ensemble_batch([seqs[40]], bpp=True)
     s40, e40 = P.fold_dcal(seqs[40])
     assert np.abs(one.bpp - P.pf(seqs[40], s40, e40, bpp=True)["bpp"]).max() < 1e-12 and np.isnan(one.md[0])
@@ -75,7 +86,11 @@ def test_solution_compute_statistics_and_limits():
     assert round(sol.ensemble_defect, 3) == 0.121 and sol.md == 0.0                          # ... and its logged ed / md
     assert sol.centroid_structure == ".((((......))))." and 0 < sol.probability < 0.5       # p(1,16) = 0.47: not in the centroid
     assert len(sol.partition_prob) == 16 and sol.partition_fn < -0.8 and len(sol.positional_entropy) == 16
-    assert sol.MEA_structure is None and sol.centroid_en is None
+    # 2 p(1,16) = 0.94 < pu(1) + pu(16): the outer pair is no MEA candidate either, the MEA structure is the centroid
+    assert sol.MEA_structure == ".((((......))))." and sol.MEA_en == sol.centroid_en and 8.0 < sol.MEA < 16.0
+    assert sol.centroid_en == rb.eval_structure_batch([sol.string], [sol.centroid_structure])[0] / 100.0
+    with pytest.raises(ValueError):
+        rb.ensemble_batch(["ACGU"], gamma=0.0)
     with pytest.raises(ValueError):
         rb.ensemble_batch(["A" * 1001])
     assert len(rb.ensemble_batch([])) == 0
@@ -116,3 +131,42 @@ def test_comparison_writer_regenerates_the_reference_log(tmp_path):
         assert [float(g[c]) for c in (2, 4, 5, 6)] == [float(r[c]) for c in (2, 4, 5, 6)], (g, r)   # t, md, fe, ed
     assert [l.split() for l in open(log)] == [[r[0], "%.3f" % float(r[2]), r[1]] for r in rows]
     assert comparison.timeout_row("NUPACK", 60.0) == "---, NUPACK, 60.000\n"
+
+
+@pytest.mark.parametrize("setno,name", [(1, "turner2004"), (2, "turner1999"), (3, "andronescu2007")])
+def test_eval_structure_batch(oracle_params, setno, name):
+    """fc.eval_structure (solution.py:232,234) on the GPU against the oracle's independent loop evaluator: MFE folds (energy ==
+    mfe), random structures threaded onto sequences that can form them (every loop kind, loops far above MAXLOOP), and the
+    error codes."""
+    import rnagent_b200 as rb
+    from rnagent_b200 import synth
+    rb.set_vienna_params(setno)
+    P = oracle_params(name)
+    rng = np.random.default_rng(70 + setno)
+    seqs, dbs = [], []
+    for n in [0, 1, 5, 9] + [int(v) for v in rng.integers(10, 400, 300)] + [1000, 2500, 4000]:
+        db = synth.random_structure(n, rng).tobytes().decode() if n else ""
+        s = list(rng.choice(list("ACGU"), n))
+        stack = []
+        for k, ch in enumerate(db):        # make every bracket pair a pairable one (GU pairs included)
+            if ch == "(":
+                stack.append(k)
+            elif ch == ")":
+                o = stack.pop()
+                s[o], s[k] = [("G", "C"), ("C", "G"), ("A", "U"), ("U", "A"), ("G", "U"), ("U", "G")][int(rng.integers(0, 6))]
+        seqs.append("".join(s))
+        dbs.append(db)
+    seqs.append("GGGG" + "A" * 40 + "GGGGAAAACCCC" + "A" * 35 + "CCCC")      # a 75-nt interior loop
+    dbs.append("((((" + "." * 40 + "((((....))))" + "." * 35 + "))))")
+    got = rb.eval_structure_batch(seqs, dbs)
+    for k, (s, d) in enumerate(zip(seqs, dbs)):
+        assert int(got[k]) == P.eval_structure(s, d), (k, len(s))
+    structs, mfes = rb.fold_batch(seqs[4:200])
+    e2 = rb.eval_structure_batch(seqs[4:200], list(structs))
+    assert [int(v) for v in e2] == [int(round(float(m) * 100)) for m in mfes]
+    e, codes = rb.eval_structure_batch(["GGGAAACCC", "GGGAAACCC", "AAAAAAAAA", "GGGAACCC", "GGGAAACCC"],
+                                       ["(((...)))", "((....)))", "(((...)))", "(((..)))", "((.....)."], strict=False)
+    assert list(codes) == [0, 3, 1, 1, 3] and int(e[0]) == P.eval_structure("GGGAAACCC", "(((...)))") and list(e[1:]) == [0, 0, 0, 0]
+    with pytest.raises(ValueError):
+        rb.eval_structure_batch(["GGGAAACCC"], ["(((...))."])
+    rb.set_vienna_params(1)

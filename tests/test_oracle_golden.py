@@ -195,3 +195,64 @@ def test_partition_function_against_enumeration(oracle_params):
         assert abs(r["ensemble_energy"] + kT * math.log(Z) / 1000) < 1e-9
         assert np.abs(r["bpp"] - pij / Z).max() < 1e-12
         assert abs(r["probability"] - math.exp(-e * 10 / kT) / Z) < 1e-12
+
+
+def test_mea_against_its_definition(oracle_params):
+    """fc.MEA() (rlif/rna/solution.py:233) has no logged column to pin it: the restatement is checked against the definition --
+    the structure maximising sum over pairs 2 gamma p(i,j) + sum over unpaired pu(i) -- by enumeration, and the returned
+    structure must reach the returned value; the evaluator takes loops above MAXLOOP (fc.eval_structure extrapolates)."""
+    import math
+    P = oracle_params("turner2004")
+
+    def structures(n):
+        out, cur, stack = [], [], []
+
+        def rec(i):
+            if i == n:
+                if not stack:
+                    out.append("".join(cur))
+                return
+            cur.append("."); rec(i + 1); cur.pop()
+            cur.append("("); stack.append(i); rec(i + 1); stack.pop(); cur.pop()
+            if stack and i - stack[-1] > 3:
+                o = stack.pop(); cur.append(")"); rec(i + 1); cur.pop(); stack.append(o)
+        rec(0)
+        return out
+
+    def accuracy(st, bpp, pu, gamma):
+        stack, acc = [], 0.0
+        for k, ch in enumerate(st):
+            if ch == "(":
+                stack.append(k)
+            elif ch == ")":
+                acc += 2 * gamma * bpp[stack.pop(), k]
+            else:
+                acc += pu[k]
+        return acc
+    rng = np.random.default_rng(5)
+    for trial in range(10):
+        n = int(rng.integers(9, 15))
+        seq = "".join(rng.choice(list("GCGCAU" if trial % 2 else "ACGU"), n))
+        s, e = P.fold_dcal(seq)
+        for gamma in (1.0, 3.0):
+            if trial < 5:
+                bpp = P.pf(seq, s, e, bpp=True)["bpp"]
+            else:   # any consistent matrix will do: random probabilities with row sums below 1
+                bpp = np.triu(rng.random((n, n)) ** 3, 4) / n * 2.5
+            cut = 1e-4 / (1 + gamma)
+            kept = np.where(bpp >= cut, bpp, 0.0)
+            pu = 1.0 - kept.sum(0) - kept.sum(1)
+            best = max(accuracy(st, kept, pu, gamma) for st in structures(n))
+            st, val = oracle.mea(bpp, gamma)
+            assert abs(val - best) < 1e-12
+            assert abs(accuracy(st, kept, pu, gamma) - val) < 1e-12
+    # the evaluator beyond MAXLOOP: one 40-nt bulge costs bulge[30] + (int)(lxc log(40/30)) + the two stacks' helices
+    inner = "GGGGAAAACCCC"
+    seq = "GGGG" + "A" * 40 + inner + "CCCC"
+    st = "((((" + "." * 40 + "((((....))))" + "))))"
+    e_long = P.eval_structure(seq, st)
+    seq30 = "GGGG" + "A" * 30 + inner + "CCCC"
+    st30 = "((((" + "." * 30 + "((((....))))" + "))))"
+    assert e_long - P.eval_structure(seq30, st30) == int(107.856 * math.log(40 / 30.))
+    full = P.statistics("UGUUGAAGGCCUAACA", *P.fold_dcal("UGUUGAAGGCCUAACA"))
+    assert full["MEA_en"] == P.eval_structure("UGUUGAAGGCCUAACA", full["MEA_structure"]) / 100.0 and full["MEA"] > 0
