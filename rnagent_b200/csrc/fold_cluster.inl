@@ -22,6 +22,19 @@ constexpr int kClusterThreads = 512;
 // Split cluster barrier (barrier.cluster.arrive / .wait): a CTA announces the end of its phase without blocking and
 // only waits -- right before the items that consume the row its peer pushed -- for the peer's announcement.
 __device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+// End of a phase, called by every thread right after a __syncthreads: the CTA barrier has ordered every thread's stores
+// (local, DSMEM pushes, global table copies) before warp 0's release, which is cumulative -- so ONE warp pays the fence
+// (MEMBAR.ALL.GPU in SASS) and the others announce without one (the pattern of a grid-wide sync: barrier, then one fence).
+__device__ __forceinline__ void cluster_arrive_phase(int warp) {
+#ifdef CLUSTER_ALL_FENCE   // the round-2 v3 behaviour, kept for A/B runs (tools/var_bench.sh): 64.2 k vs 72.4 k folds/s at n = 400
+  (void)warp;
+  cluster_arrive_release();
+#else
+  if (warp == 0) cluster_arrive_release();
+  else cluster_arrive_relaxed();
+#endif
+}
 __device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
 struct ClusterSmem {
@@ -393,7 +406,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
       if (tid == 0) atomicAdd(&g_phase_clk[(rank ? 64 : 0) + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
 #endif
       __syncthreads();            // this CTA's tables of the phase are complete ...
-      cluster_arrive_release();   // ... and so are its pushes: announce the phase, do not wait here
+      cluster_arrive_phase(warp); // ... and so are its pushes: announce the phase, do not wait here
 #ifdef WAVE_PHASE_CLK
       if (tid == 0 && rank == 0) atomicAdd(&g_phase_clk[128 + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
 #endif
