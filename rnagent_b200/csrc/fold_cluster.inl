@@ -37,6 +37,18 @@ __device__ __forceinline__ void cluster_arrive_phase(int warp) {
 }
 __device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
+#ifdef CLUSTER_TRACE   // debug builds only (tools/cluster_trace.py): per-warp time stamps of every phase of ONE fold
+__device__ unsigned g_cluster_trace[2 * 480 * 16 * 4];
+__device__ unsigned g_cluster_kind[480 * 16];   // [d][kind]: cycles (kinds 0..7) and item counts (8..15), pair CTA
+#define TRACE_AT(slot_) do { if (tracing && lane == 0 && d < 480) g_cluster_trace[((rank * 480 + d) * 16 + warp) * 4 + (slot_)] = (unsigned)(clock64() - trace_t0); } while (0)
+#define KIND_BEGIN() long long kind_t0 = clock64()
+#define KIND_END(kind_) do { if (tracing && lane == 0 && d < 480) { const long long t1_ = clock64(); atomicAdd(&g_cluster_kind[d * 16 + (kind_)], (unsigned)(t1_ - kind_t0)); atomicAdd(&g_cluster_kind[d * 16 + 8 + (kind_)], 1u); kind_t0 = t1_; } } while (0)
+#else
+#define TRACE_AT(slot_) do { } while (0)
+#define KIND_BEGIN() do { } while (0)
+#define KIND_END(kind_) do { } while (0)
+#endif
+
 struct ClusterSmem {
   // common
   int misc_off, ptab_off, S_off;
@@ -171,10 +183,15 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
     // read the row the peer pushed: Fp / Fm] -> __syncthreads -> arrive.  The rows are double / triple buffered, and a row
     // is only overwritten by an item that runs behind a wait, i.e. after its consumer's phase has been announced.
     cluster_arrive_release();
+#ifdef CLUSTER_TRACE
+    const bool tracing = blockIdx.x < 2 && slot < 74;   // cluster 0's first fold
+    const long long trace_t0 = clock64();
+#endif
     for (int d = kTurn + 1; d <= n + 1; ++d) {
 #ifdef WAVE_PHASE_CLK
       const long long clk_p0 = clock64();
 #endif
+      TRACE_AT(0);
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
       const int nb_d = (cells_d + 31) >> 5;
@@ -243,6 +260,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
           }
         };
         bool waited = false;
+        KIND_BEGIN();
         for (int k = warp; k < total; k += NW) {
           if (k >= nI + nT + nP) {
             if (!waited) {
@@ -250,6 +268,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
               waited = true;
             }
             finalise_pairs(k - nI - nT - nP);
+            KIND_END(3);
             continue;
           }
           if (k < nI) {
@@ -269,6 +288,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
               const int e = min(a1 + v_mm1, aB + (type > 2 ? tau : 0));
               part[(par * kWSlots + 2 + r) * np + x] = (ST)min(e, kInfS);
             }
+            KIND_END(0);
           } else if (k < nI + nT) {
             // ---- T(b): tabulated shapes, inner pairs from the cB window
             const int idx = (k - nI) * 32 + lane;
@@ -295,6 +315,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
               }
               part[(par * kWSlots + 1) * np + x] = (ST)min(best, kInfS);
             }
+            KIND_END(1);
           } else {
             // ---- P: list of the pairable cells of diagonal d+1 (used by the next phase)
             const int dn = d + 1, cells_n = n - dn;
@@ -308,6 +329,7 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
               pos += __popc(m);
             }
             if (lane == 0) plc[par1] = pos;
+            KIND_END(2);
           }
         }
         // ---- G(cell): generic interior shapes, lanes across shapes, one pairable cell at a time
@@ -347,7 +369,10 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
           const int t = goff[k] + rs * (int)sizeof(ST), u = t - kWin * rs * (int)sizeof(ST);
           goff[k] = (u >= bb + (int)wI_sa) ? u : t;
         }
+        KIND_END(4);
+        TRACE_AT(1);
         if (!waited) cluster_wait_acquire();
+        TRACE_AT(2);
       } else {
         // ================= multiloop CTA
         // split range t = 4 .. d-5 cut into enough chunks that every warp of this CTA gets work even on the
@@ -399,13 +424,16 @@ fold_cluster_kernel(const FoldParams *__restrict__ gp, BatchArgs a, int nmax, in
             }
           }
         }
+        TRACE_AT(1);
         if (!waited) cluster_wait_acquire();
+        TRACE_AT(2);
       }
 #ifdef WAVE_PHASE_CLK
       __syncthreads();
       if (tid == 0) atomicAdd(&g_phase_clk[(rank ? 64 : 0) + (d >> 4)], (unsigned long long)(clock64() - clk_p0));
 #endif
       __syncthreads();            // this CTA's tables of the phase are complete ...
+      TRACE_AT(3);
       cluster_arrive_phase(warp); // ... and so are its pushes: announce the phase, do not wait here
 #ifdef WAVE_PHASE_CLK
       if (tid == 0 && rank == 0) atomicAdd(&g_phase_clk[128 + (d >> 4)], (unsigned long long)(clock64() - clk_p0));

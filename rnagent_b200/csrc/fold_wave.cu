@@ -1111,6 +1111,16 @@ cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax,
 
 int wave_occupancy(int nmax, int esz, int threads) { return WAVE_DISPATCH(occupancy_t, nmax); }
 
+#ifdef CLUSTER_TRACE
+extern "C" int rnafold_debug_cluster_trace(unsigned *out, int count) {
+  if (count > 2 * 480 * 16 * 4) count = 2 * 480 * 16 * 4;
+  return cudaMemcpyFromSymbol(out, g_cluster_trace, sizeof(unsigned) * count) == cudaSuccess ? 0 : -1;
+}
+extern "C" int rnafold_debug_cluster_kinds(unsigned *out, int count) {
+  if (count > 480 * 16) count = 480 * 16;
+  return cudaMemcpyFromSymbol(out, g_cluster_kind, sizeof(unsigned) * count) == cudaSuccess ? 0 : -1;
+}
+#endif
 #ifdef WAVE_PHASE_CLK
 extern "C" int rnafold_debug_phase_clocks(unsigned long long *out, int count, int reset) {
   if (count > 640) count = 640;
