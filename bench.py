@@ -509,7 +509,10 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
     sseq, soff = synth.random_sequences(256, 100, 4100 + rank)
     targets, _ = rnagent_b200.fold_batch([sseq[soff[k]:soff[k + 1]].tobytes().decode() for k in range(256)])
     cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True)
-    N, steps, settle = 4096, 400, 300   # `settle` untimed steps first: episodes de-synchronise, every step then has terminal folds
+    # `settle` untimed steps first: environments that share a target finish in cohorts until their episode phases have drifted
+    # apart (tools/env_terminal_hist.py: 15-22 % of the steps carry more than 148 terminal folds after 300 steps, none after
+    # 1,500) -- the steady state of a long rollout is what is timed
+    N, steps, settle = 4096, 400, 1500
     env = rnagent_b200.RnaDesignBatch(cfg, N, targets=targets, rank=rank, auto_reset=True, randomize=True, seed=rank)
     g = torch.Generator(device=dev)
     g.manual_seed(rank)
@@ -533,7 +536,6 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
         g_ = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
         dist.all_gather(g_, torch.tensor([rank_us[0]], dtype=torch.float64, device=dev))
         rank_us = [float(t.item()) for t in g_]
-    my_episodes = env.stats().episodes
     stats = env.stats().all_reduce(device=dev)          # the path's only collective: rollout statistics over NCCL
     env.close()
     out["env"] = {"metric": "rl_env_steps_per_sec", "value": stats.steps / secs, "unit": "env steps/s",
@@ -544,7 +546,7 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
                   "roofline": roof(stats.episodes / secs / world * synth.work_candidates(100),
                                    "terminal folds only (one per episode); the step is bound by ONE fold's latency, not by throughput"),
                   "workload": "4096 RnaDesign envs per GPU, n=100 targets (folds of random sequences), uniform random actions, "
-                              "auto-reset, steady state (300 untimed steps first); observations, rewards and dones stay on the device",
+                              "auto-reset, steady state (1,500 untimed steps first); observations, rewards and dones stay on the device",
                   "stats": stats.summary()}
     if cpu_budget > 0 and rank == 0:
         r_steps, r_eps, n_steps = cpu_env_rate(targets, cpu_budget)

@@ -47,7 +47,6 @@ struct Env {
   bool permute = false;
   int pm_budget = 50, pm_radius = 1, pm_threshold = 5, pm_allow_gu = 0;
   double pm_p = 0.5;
-  uint64_t pm_calls = 0;
   cudaStream_t stream = nullptr;
   // data set (device, CSR over targets)
   uint8_t *d_tgt = nullptr, *d_mot = nullptr;
