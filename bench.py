@@ -537,12 +537,35 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
         dist.all_gather(g_, torch.tensor([rank_us[0]], dtype=torch.float64, device=dev))
         rank_us = [float(t.item()) for t in g_]
     stats = env.stats().all_reduce(device=dev)          # the path's only collective: rollout statistics over NCCL
+    # the same steps as a ROLLOUT that keeps one reward row per step (what PPO stores): rewards deferred by up to 32 steps, the
+    # terminal sequences of a window folded by one call (values identical, tests/test_env_gpu.py)
+    d_rT = torch.empty((steps, N), dtype=torch.float64, device=dev)
+    env.set_reward_delay(32)
+    for k in range(64):
+        env.step_device(acts[k], d_obs, d_rT[k], d_done)
+    env.flush()
+    env.stats(clear=True)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(steps):
+        env.step_device(acts[settle + k], d_obs, d_rT[k], d_done)
+    env.flush()
+    torch.cuda.synchronize()
+    dsecs = max_over_ranks(time.perf_counter() - t0)
+    dstats = env.stats().all_reduce(device=dev)
+    env.set_reward_delay(1)
     env.close()
     out["env"] = {"metric": "rl_env_steps_per_sec", "value": stats.steps / secs, "unit": "env steps/s",
                   "per_gpu": stats.steps / secs / world, "us_per_vector_step": 1e6 * secs / steps,
                   "episodes_per_s": stats.episodes / secs, "envs_per_gpu": N, "steps_timed": steps,
                   "host_syncs_per_step": 0, "per_rank_us_per_vector_step": [round(v, 1) for v in rank_us],
                   "sum_of_rank_rates": sum(N * 1e6 / v for v in rank_us),
+                  "rollout_deferred": {"value": dstats.steps / dsecs, "unit": "env steps/s", "per_gpu": dstats.steps / dsecs / world,
+                                       "us_per_vector_step": 1e6 * dsecs / steps, "reward_delay_steps": 32,
+                                       "episodes_per_s": dstats.episodes / dsecs,
+                                       "note": "rnafold_env_config_delay(32): one reward row per step ([T, N] rollout buffer), the terminal folds of 32 steps "
+                                               "in one call; rewards complete at the end of the timed region (19.5 / 66 / 80 / 87 / 92 M steps/s at "
+                                               "delay 1 / 8 / 16 / 32 / 64, tools/env_speed.py)"},
                   "roofline": roof(stats.episodes / secs / world * synth.work_candidates(100),
                                    "terminal folds only (one per episode); the step is bound by ONE fold's latency, not by throughput"),
                   "workload": "4096 RnaDesign envs per GPU, n=100 targets (folds of random sequences), uniform random actions, "
@@ -571,10 +594,23 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
     torch.cuda.synchronize()
     msecs = max_over_ranks(time.perf_counter() - t0)
     mstats = env.stats().all_reduce(device=dev)
+    d_rT = torch.empty((msteps, N), dtype=torch.float64, device=dev)
+    env.set_reward_delay(32)                             # capped by the shortest episode of the data set (12-nt targets: ~8 steps)
+    env.stats(clear=True)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(msteps):
+        env.step_device(macts[msettle + k], d_obs, d_rT[k], d_done)
+    env.flush()
+    torch.cuda.synchronize()
+    mdsecs = max_over_ranks(time.perf_counter() - t0)
+    mdstats = env.stats().all_reduce(device=dev)
     env.close()
     out["env_mixed"] = {"metric": "rl_env_steps_per_sec_mixed_targets", "value": mstats.steps / msecs, "unit": "env steps/s",
                         "per_gpu": mstats.steps / msecs / world, "us_per_vector_step": 1e6 * msecs / msteps,
                         "episodes_per_s": mstats.episodes / msecs, "envs_per_gpu": N, "steps_timed": msteps,
+                        "rollout_deferred": {"value": mdstats.steps / mdsecs, "unit": "env steps/s", "us_per_vector_step": 1e6 * mdsecs / msteps,
+                                             "reward_delay_steps": "32 requested, capped by the shortest episode"},
                         "workload": "4096 RnaDesign envs per GPU, targets = folds of 128 random sequences with the Eterna100 length mix "
                                     "(12-400 nt), uniform random actions, auto-reset, 400 untimed steps first"}
     return out

@@ -156,6 +156,21 @@ int rnafold_env_reset(int32_t handle, uint8_t *obs_out);
 int rnafold_env_step(int32_t handle, const int32_t *actions, double reward_exp, uint8_t *obs_out,
                      double *reward_out, uint8_t *done_out);
 /* istat = {episodes, solved, sum HD, env steps}; fstat = {sum reward, sum MFE kcal/mol}. */
+/* Deferred rewards for rollouts that keep ONE REWARD BUFFER PER STEP (what a PPO rollout stores anyway; the reference's
+ * trainer consumes rewards after n_steps, rlif/learning/trainer.py:307-309): the terminal sequences of up to `steps` (1..64)
+ * consecutive steps are folded by one call -- a step is bound by the latency of a fold, not by its throughput -- and every
+ * reward lands in the reward_out buffer that was passed to the step it belongs to, at the latest when the window closes:
+ * after `steps` steps, on rnafold_env_flush, or before any call that reads or changes the environments' state (stats,
+ * snapshot, reset, set_targets, config_*).  Values are identical to the undeferred step's; observations, dones and
+ * auto-resets are never deferred.  The window is capped by the shortest episode of the data set (no environment finishes
+ * twice within it); steps with a host output buffer or with the local search run undeferred.  steps = 1 (default): every
+ * step folds its own terminals.  No counterpart in the reference (its workers fold synchronously inside step()). */
+/* Enqueue the environments' work on the CALLER's stream from now on (a cudaStream_t, e.g. torch's current stream, so that a
+ * policy network and the step are ordered without host synchronisation); use_own != 0 returns to the environments' own
+ * non-blocking stream, on which device outputs are only ordered against the library's own calls. */
+int rnafold_env_set_stream(int32_t handle, void *stream, int32_t use_own);
+int rnafold_env_config_delay(int32_t handle, int32_t steps);
+int rnafold_env_flush(int32_t handle);
 int rnafold_env_stats(int32_t handle, uint64_t istat[4], double fstat[2], int32_t clear);
 int rnafold_env_snapshot(int32_t handle, uint8_t *seq, int32_t *idx, int32_t *cur, int32_t *ep, uint8_t *last_seq,
                          uint8_t *last_db, int32_t *last_hd, int32_t *last_mfe, int32_t *last_t, int32_t *lmax_out);

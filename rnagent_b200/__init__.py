@@ -7,7 +7,7 @@ signatures.  Import is cheap and GPU-free; the first fold binds the CUDA library
 from .dataset import Dataset
 from .dotbracket import DotBracket
 from .ensemble import EnsembleResult, ensemble_batch, eval_structure_batch
-from .environments import RnaDesignBatch, RolloutStats, create_env, rollout, shard_sequences, shard_targets
+from .environments import RnaDesignBatch, RolloutStats, create_env, rollout, rollout_device, shard_sequences, shard_targets
 from .permute import PermuteResult, permute_batch
 from .solution import Solution
 from .tester import PolicyModel, Tester
@@ -17,5 +17,5 @@ from .vienna import (PARAM_FILES, PARAMETERS, config_vienna, cvar, fold, fold_ba
 
 __all__ = ["fold", "fold_batch", "fold_hamming_batch", "read_parameter_file", "set_vienna_params",
            "config_vienna", "cvar", "hamming_distance", "PARAMETERS", "PARAM_FILES", "DotBracket", "RnaDesignBatch",
-           "RolloutStats", "create_env", "rollout", "shard_targets", "shard_sequences", "permute_batch", "PermuteResult", "Solution",
+           "RolloutStats", "create_env", "rollout", "rollout_device", "shard_targets", "shard_sequences", "permute_batch", "PermuteResult", "Solution",
            "ensemble_batch", "eval_structure_batch", "EnsembleResult", "Dataset", "Tester", "PolicyModel", "load_sequence", "load_dataset", "load_fasta", "write_fasta", "read_fasta_records"]

@@ -20,7 +20,7 @@ EXPORTS = [
     "rnafold_measure_onchip_peaks", "rnafold_device_info", "rnafold_wave_smem_bytes", "rnafold_current_device",
     "rnafold_env_create", "rnafold_env_destroy", "rnafold_env_config", "rnafold_env_config_reward", "rnafold_env_set_current", "rnafold_env_set_targets", "rnafold_env_reset",
     "rnafold_env_step", "rnafold_env_stats", "rnafold_env_snapshot", "rnafold_parse_target",
-    "rnafold_ensemble_batch", "rnafold_eval_structure_batch", "rnafold_permute_batch", "rnafold_permute_draw", "rnafold_permute_set_order", "rnafold_permute_candidate_order", "rnafold_env_config_permute",
+    "rnafold_ensemble_batch", "rnafold_eval_structure_batch", "rnafold_permute_batch", "rnafold_permute_draw", "rnafold_permute_set_order", "rnafold_permute_candidate_order", "rnafold_env_config_permute", "rnafold_env_config_delay", "rnafold_env_flush", "rnafold_env_set_stream",
 ]
 
 _lock = threading.Lock()
@@ -83,6 +83,9 @@ def load_library():
         L.rnafold_permute_set_order.argtypes = [ci]
         L.rnafold_permute_candidate_order.argtypes = [vp, ci, ci, ci, vp]
         L.rnafold_env_config_permute.argtypes = [ci, ci, ci, ci, ci, cd, ci]
+        L.rnafold_env_config_delay.argtypes = [ci, ci]
+        L.rnafold_env_flush.argtypes = [ci]
+        L.rnafold_env_set_stream.argtypes = [ci, vp, ci]
         _cdll = L
         return L
 

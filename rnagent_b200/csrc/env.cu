@@ -36,6 +36,7 @@ using rnafold::set_error;
     }                                                                                   \
   } while (0)
 
+constexpr int kMaxDelay = 64;
 constexpr int kRows = 10;  // 6 structure-motif rows (O C I H M E) + 4 nucleotide rows (A C G U)
 
 struct Env {
@@ -47,7 +48,8 @@ struct Env {
   bool permute = false;
   int pm_budget = 50, pm_radius = 1, pm_threshold = 5, pm_allow_gu = 0;
   double pm_p = 0.5;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;       // where the environments' work is enqueued: own_stream, or the caller's (rnafold_env_set_stream)
+  cudaStream_t own_stream = nullptr;
   // data set (device, CSR over targets)
   uint8_t *d_tgt = nullptr, *d_mot = nullptr;
   int16_t *d_pair = nullptr;
@@ -63,6 +65,13 @@ struct Env {
   double *d_brw = nullptr;
   int32_t *h_off = nullptr;  // pinned: [0] = total length, [1] = count, [2..] offsets (host-routed path: local search)
   int32_t *h_status = nullptr;  // pinned: the library's sticky status word, read with the end-of-step copies
+  // deferred rewards (rnafold_env_config_delay): terminal sequences of up to `delay` consecutive steps are folded together
+  int delay = 1;                // requested window (1 = every step folds its own terminals)
+  int min_episode = 1;          // shortest episode of the data set, in steps: no environment finishes twice within that many
+  int win = 0;                  // steps accumulated in the open window
+  double win_exp = 0.0;         // their reward exponent
+  double *win_r[kMaxDelay] = {};   // the callers' reward buffers of those steps (device pointers or null)
+  int32_t *d_pend = nullptr, *d_pend_t = nullptr;   // per environment: 1 + window step of its pending terminal / its target then
   std::vector<int32_t> lens;    // distinct target lengths (what the device-routed fold must be prepared for)
   void *plan = nullptr;         // launch list of the device-routed fold (capi.cu)
   // statistics: episodes, solved, sum_hd, steps (int64) ; sum_reward, sum_mfe_kcal (double)
@@ -156,7 +165,8 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
                                 const int16_t *__restrict__ pair, int32_t *idx, uint8_t *seq, uint8_t *mask,
                                 uint8_t *done, double *reward, unsigned long long *istat, unsigned long long *packed,
                                 int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt, int32_t *slot_of,
-                                const int32_t *__restrict__ ep, unsigned long long *keys) {
+                                const int32_t *__restrict__ ep, unsigned long long *keys, int32_t *pend, int32_t *pend_t,
+                                int jstep) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_envs) return;
   const int t = cur[e];
@@ -187,6 +197,10 @@ __global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict_
     const int slot = (int)(old >> 32), o0 = (int)(old & 0xffffffffull);
     list[slot] = e;
     slot_of[e] = slot;
+    if (pend) {   // deferred rewards: which step of the window this terminal belongs to, and its target
+      pend[e] = jstep + 1;
+      pend_t[e] = t;
+    }
     keys[slot] = ((unsigned long long)(unsigned)e << 32) | (unsigned long long)(unsigned)ep[e];  // what the local search's draws are keyed on
     boff[slot] = o0;
     for (int q = 0; q < n; ++q) {
@@ -306,6 +320,101 @@ __global__ void env_finish_kernel(int n_envs, int n_targets, int lmax, int k, in
   }
 }
 
+// ---- deferred rewards (window of several steps, one fold): the two halves of env_finish_kernel
+// (a) every step: auto-reset of the environments that just finished + the observation -- nothing here needs the fold
+__global__ void env_resetobs_kernel(int n_envs, int n_targets, int lmax, int k, int auto_reset, int randomize, unsigned long long seed,
+                                    const uint8_t *__restrict__ done, const int32_t *__restrict__ toff,
+                                    const uint8_t *__restrict__ mot, int32_t *cur, int32_t *idx, int32_t *ep, uint8_t *seq,
+                                    uint8_t *mask, uint8_t *obs) {
+  const int e = blockIdx.x;
+  if (e >= n_envs) return;
+  if (done[e] && auto_reset) {
+    if (threadIdx.x == 0) {   // RnaDesign.reset: next target, empty solution
+      const int t0 = cur[e], epn = ep[e] + 1;
+      int t;
+      if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
+      else t = (t0 + 1) % n_targets;
+      cur[e] = t;
+      idx[e] = 0;
+      ep[e] = epn;
+    }
+    for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
+      seq[(size_t)e * lmax + q] = '-';
+      mask[(size_t)e * lmax + q] = 0;
+    }
+    __syncthreads();
+  }
+  const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
+  const int w = 2 * k;
+  auto cell = [&](int q) -> unsigned {
+    const int row = q / w, col = q - row * w;
+    const int pos = i - k + col;
+    unsigned v = 0;
+    if (pos >= 0 && pos < n) v = row < 6 ? (mot[base + pos] == row) : ((mask[(size_t)e * lmax + pos] >> (row - 6)) & 1);
+    return v;
+  };
+  uint8_t *dst = obs + (size_t)e * kRows * w;
+  if ((reinterpret_cast<uintptr_t>(obs) & 3u) == 0) {
+    for (int q = 4 * threadIdx.x; q < kRows * w; q += 4 * blockDim.x)
+      *reinterpret_cast<unsigned *>(dst + q) = cell(q) | (cell(q + 1) << 8) | (cell(q + 2) << 16) | (cell(q + 3) << 24);
+  } else {
+    for (int q = threadIdx.x; q < kRows * w; q += blockDim.x) dst[q] = (uint8_t)cell(q);
+  }
+}
+
+// (b) at the end of a window, after the fold of everything that finished in it: rewards into the reward buffer of the step
+// each environment finished in, last solution, rollout statistics
+struct WindowRewards {
+  double *r[kMaxDelay];
+};
+__global__ void env_rewards_kernel(int n_envs, int lmax, int gc_penalty, int32_t *pend, const int32_t *__restrict__ pend_t,
+                                   const int32_t *__restrict__ slot_of, const int32_t *__restrict__ off,
+                                   const double *__restrict__ brw, const int32_t *__restrict__ bhd,
+                                   const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb,
+                                   const uint8_t *__restrict__ bseq, const int32_t *__restrict__ toff, WindowRewards out,
+                                   uint8_t *last_db, uint8_t *last_seq, int32_t *last_hd, int32_t *last_mfe, int32_t *last_t,
+                                   unsigned long long *istat, double *fstat, unsigned long long *packed) {
+  __shared__ int n_u;
+  const int e = blockIdx.x;
+  if (e >= n_envs) return;
+  if (e == 0 && threadIdx.x == 0) *packed = 0ull;  // the next window starts empty
+  const int j1 = pend[e];
+  if (!j1) return;
+  const int s = slot_of[e], t0 = pend_t[e];
+  const int o0 = off[s], len = toff[t0 + 1] - toff[t0];
+  if (threadIdx.x == 0) n_u = 0;
+  __syncthreads();
+  int my_u = 0;
+  for (int q = threadIdx.x; q < len; q += blockDim.x) {
+    const uint8_t ch = bseq[o0 + q];
+    last_db[(size_t)e * lmax + q] = bdb[o0 + q];
+    last_seq[(size_t)e * lmax + q] = ch;
+    my_u += ch == 'U';
+  }
+  if (gc_penalty && my_u) atomicAdd(&n_u, my_u);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double rw = brw[s];
+    if (gc_penalty) {
+      const double inc = 1.0 / (double)len;
+      double u = 0.0;
+      for (int q = 0; q < n_u; ++q) u += inc;
+      rw = rw * 0.85 + fmin(fmax(u, 0.0), 0.15);
+    }
+    double *dst = out.r[j1 - 1];
+    if (dst) dst[e] = rw;
+    last_hd[e] = bhd[s];
+    last_mfe[e] = bmfe[s];
+    last_t[e] = t0;
+    atomicAdd(&istat[0], 1ull);
+    if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
+    atomicAdd(&istat[2], (unsigned long long)bhd[s]);
+    atomicAdd(&fstat[0], rw);
+    atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
+    pend[e] = 0;
+  }
+}
+
 Env *get_env(int h) {
   if (h < 0 || h >= (int)g_envs.size()) return nullptr;
   return g_envs[h];
@@ -337,17 +446,99 @@ static void env_free(Env *e) {
   void *ptrs[] = {e->d_tgt, e->d_mot, e->d_pair, e->d_toff, e->d_cur, e->d_idx, e->d_ep, e->d_act, e->d_seq, e->d_mask,
                   e->d_done, e->d_reward, e->d_list, e->d_off, e->d_hd, e->d_mfe, e->d_slot, e->d_keys, e->d_bseq, e->d_btgt, e->d_bdb,
                   e->d_brw, e->d_istat, e->d_fstat, e->d_obs, e->d_last_db, e->d_last_seq, e->d_last_hd,
-                  e->d_last_mfe, e->d_last_t};
+                  e->d_last_mfe, e->d_last_t, e->d_pend, e->d_pend_t};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (e->h_off) cudaFreeHost(e->h_off);
   if (e->h_status) cudaFreeHost(e->h_status);
   if (e->plan) rnafold::fold_dyn_plan_free(e->plan);
-  if (e->stream) cudaStreamDestroy(e->stream);
+  if (e->own_stream) cudaStreamDestroy(e->own_stream);
   delete e;
 }
 
+// Close the open window of deferred rewards: ONE device-routed fold of everything that finished in it, then the rewards
+// into the reward buffers of the steps they belong to.  Called with g_env_mu held.
+static int env_window_end(Env *e) {
+  if (e->win == 0) return RNAFOLD_OK;
+  cudaStream_t st = e->stream;
+  const int N = e->n_envs;
+  int rc = rnafold::fold_hamming_dyn_enqueue(&e->plan, e->lens.data(), (int)e->lens.size(), N, e->d_bseq, e->d_off + 2, e->d_off + 1,
+                                             e->d_off, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw, e->win_exp, (void *)st);
+  WindowRewards out{};
+  for (int j = 0; j < e->win; ++j) out.r[j] = e->win_r[j];
+  e->win = 0;
+  if (rc) {
+    cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st);
+    cudaMemsetAsync(e->d_pend, 0, sizeof(int32_t) * (size_t)N, st);
+    return rc;
+  }
+  env_rewards_kernel<<<N, 128, 0, st>>>(N, e->lmax, e->gc_penalty ? 1 : 0, e->d_pend, e->d_pend_t, e->d_slot, e->d_off + 2, e->d_brw,
+                                        e->d_hd, e->d_mfe, e->d_bdb, e->d_bseq, e->d_toff, out, e->d_last_db, e->d_last_seq,
+                                        e->d_last_hd, e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat,
+                                        reinterpret_cast<unsigned long long *>(e->d_off));
+  ENV_TRY(cudaGetLastError());
+  return RNAFOLD_OK;
+}
+
+// episode length (steps) of one target: the cursor walk of env_step_kernel on an empty solution
+static int episode_steps(const std::string &s, const std::vector<int16_t> &pair) {
+  const int n = (int)s.size();
+  std::vector<char> filled((size_t)n, 0);
+  int i = 0, steps = 0;
+  for (;;) {
+    ++steps;
+    filled[i] = 1;
+    if (s[i] == '(' && pair[i] >= 0) filled[pair[i]] = 1;
+    if (i >= n - 1) return steps;
+    int q = i;
+    while (q < n - 1 && filled[q]) ++q;
+    i = q;
+  }
+}
+
 extern "C" {
+
+// Deferred rewards for rollouts that keep one reward buffer per step: the terminal sequences of up to `steps` consecutive
+// steps are folded by ONE call (a step is bound by the latency of a fold, not by its throughput), and every reward lands in
+// the buffer that was passed to the step it belongs to -- at the latest when the window closes: after `steps` steps, on
+// rnafold_env_flush, or before any call that reads or changes the environments' state.  Observations, dones and auto-resets
+// are not deferred.  The window never exceeds the shortest episode of the data set (no environment finishes twice in it);
+// steps with host output buffers or with the local search run undeferred.
+int rnafold_env_config_delay(int32_t h, int32_t steps) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  if (steps < 1) return set_error(RNAFOLD_EINVAL, "reward delay must be at least 1 step");
+  int rc = env_window_end(e);
+  e->delay = steps > kMaxDelay ? kMaxDelay : steps;
+  return rc;
+}
+
+// Enqueue the environments' work on the CALLER's stream from now on (e.g. torch.cuda.current_stream().cuda_stream, so that
+// a policy network and the step are ordered without host synchronisation); use_own != 0 goes back to the environments' own
+// non-blocking stream.  Work already enqueued on the previous stream is waited for on the new one.
+int rnafold_env_set_stream(int32_t h, void *stream, int32_t use_own) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  cudaStream_t next = use_own ? e->own_stream : (cudaStream_t)stream;
+  if (next == e->stream) return RNAFOLD_OK;
+  cudaEvent_t ev;
+  ENV_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  cudaError_t err = cudaEventRecord(ev, e->stream);
+  if (err == cudaSuccess) err = cudaStreamWaitEvent(next, ev, 0);
+  cudaEventDestroy(ev);
+  ENV_TRY(err);
+  e->stream = next;
+  return RNAFOLD_OK;
+}
+
+int rnafold_env_flush(int32_t h) {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  Env *e = get_env(h);
+  if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  return env_window_end(e);
+}
 
 int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   if (n_envs <= 0 || kernel_size <= 0 || kernel_size > 512 || !handle) return set_error(RNAFOLD_EINVAL, "bad env arguments");
@@ -358,7 +549,8 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   e->n_envs = n_envs;
   e->k = kernel_size;
   const size_t N = (size_t)n_envs;
-  ENV_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  ENV_TRY(cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking));
+  e->stream = e->own_stream;
   ENV_TRY(dalloc(&e->d_cur, N));
   ENV_TRY(dalloc(&e->d_idx, N));
   ENV_TRY(dalloc(&e->d_ep, N));
@@ -367,6 +559,9 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_reward, N));
   ENV_TRY(dalloc(&e->d_list, N));
   ENV_TRY(dalloc(&e->d_slot, N));
+  ENV_TRY(dalloc(&e->d_pend, N));
+  ENV_TRY(dalloc(&e->d_pend_t, N));
+  ENV_TRY(cudaMemset(e->d_pend, 0, N * sizeof(int32_t)));
   ENV_TRY(dalloc(&e->d_keys, N));
   ENV_TRY(dalloc(&e->d_off, N + 4));
   ENV_TRY(cudaMemset(e->d_off, 0, (N + 4) * sizeof(int32_t)));
@@ -399,6 +594,7 @@ int rnafold_env_destroy(int32_t h) {
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  env_window_end(e);
   cudaStreamSynchronize(e->stream);
   env_free(e);
   g_envs[h] = nullptr;
@@ -409,6 +605,10 @@ int rnafold_env_config(int32_t h, int32_t auto_reset, int32_t randomize, uint64_
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   e->auto_reset = auto_reset != 0;
   e->randomize = randomize != 0;
   e->seed = seed;
@@ -422,6 +622,10 @@ int rnafold_env_set_current(int32_t h, int32_t value) {
   Env *e = get_env(h);
   if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
   if (value < -1 || value >= e->n_targets) return set_error(RNAFOLD_EINVAL, "current_sequence out of range");
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   std::vector<int32_t> v((size_t)e->n_envs, value);
   ENV_TRY(cudaMemcpyAsync(e->d_cur, v.data(), sizeof(int32_t) * v.size(), cudaMemcpyHostToDevice, e->stream));
   ENV_TRY(cudaStreamSynchronize(e->stream));
@@ -432,6 +636,10 @@ int rnafold_env_config_reward(int32_t h, int32_t gc_penalty) {
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   e->gc_penalty = gc_penalty != 0;
   return RNAFOLD_OK;
 }
@@ -441,6 +649,10 @@ int rnafold_env_config_permute(int32_t h, int32_t enabled, int32_t budget, int32
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   if (enabled && (budget < 0 || radius < 1 || radius > 64 || threshold < 0 || !(mutation_probability >= 0.0 && mutation_probability <= 1.0)))
     return set_error(RNAFOLD_EINVAL, "bad permutation settings");
   e->permute = enabled != 0;
@@ -460,9 +672,14 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e || !bytes || !off || n_targets <= 0) return set_error(RNAFOLD_EINVAL, "bad env targets");
+  {
+    int rc = env_window_end(e);
+    if (rc) return rc;
+    ENV_TRY(cudaStreamSynchronize(e->stream));
+  }
   std::vector<int16_t> pair_all;
   std::vector<uint8_t> mot_all;
-  int lmax = 0;
+  int lmax = 0, min_episode = 1 << 30;
   for (int t = 0; t < n_targets; ++t) {
     const int n = off[t + 1] - off[t];
     if (n <= 0 || n > RNAFOLD_MAX_LEN) return set_error(RNAFOLD_EINVAL, "target length out of range");
@@ -472,6 +689,7 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
     std::vector<int16_t> pr;
     std::vector<uint8_t> mo;
     parse_target(s, pr, mo);
+    min_episode = std::min(min_episode, episode_steps(s, pr));
     pair_all.insert(pair_all.end(), pr.begin(), pr.end());
     mot_all.insert(mot_all.end(), mo.begin(), mo.end());
     lmax = n > lmax ? n : lmax;
@@ -499,6 +717,7 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
   ENV_TRY(cudaMemset(e->d_last_seq, '-', N * lmax));
   e->n_targets = n_targets;
   e->lmax = lmax;
+  e->min_episode = min_episode;
   ENV_TRY(cudaMemset(e->d_cur, 0xff, N * sizeof(int32_t)));
   ENV_TRY(cudaMemset(e->d_ep, 0xff, N * sizeof(int32_t)));  // the constructor's next_target_structure() is not an episode
   e->lens.clear();
@@ -531,6 +750,10 @@ int rnafold_env_reset(int32_t h, uint8_t *obs_out) {
   Env *e = get_env(h);
   if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
   ENV_TRY(cudaSetDevice(rnafold_current_device()));
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
                                                      nullptr, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
   ENV_TRY(cudaGetLastError());
@@ -562,12 +785,42 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
     ENV_TRY(cudaMemcpyAsync(e->d_act, actions, sizeof(int32_t) * (size_t)N, cudaMemcpyHostToDevice, st));
     d_act = e->d_act;
   }
+  {
+    // ---- deferred rewards: device outputs only, no local search
+    const int window = std::min(e->delay, e->min_episode);
+    const bool dev_out = (!obs_out || env_is_device_ptr(obs_out)) && (!reward_out || env_is_device_ptr(reward_out)) &&
+                         (!done_out || env_is_device_ptr(done_out));
+    if (window > 1 && dev_out && !e->permute) {
+      if (e->win > 0 && e->win_exp != reward_exp) {
+        int rc = env_window_end(e);
+        if (rc) return rc;
+      }
+      uint8_t *d_done = done_out ? done_out : e->d_done;
+      double *d_rw = reward_out ? reward_out : e->d_reward;
+      env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
+                                                       e->d_seq, e->d_mask, d_done, d_rw, e->d_istat,
+                                                       reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
+                                                       e->d_bseq, e->d_btgt, e->d_slot, e->d_ep, e->d_keys, e->d_pend, e->d_pend_t,
+                                                       e->win);
+      ENV_TRY(cudaGetLastError());
+      env_resetobs_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, e->auto_reset ? 1 : 0, e->randomize ? 1 : 0, e->seed,
+                                             d_done, e->d_toff, e->d_mot, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask,
+                                             obs_out ? obs_out : e->d_obs);
+      ENV_TRY(cudaGetLastError());
+      e->win_r[e->win] = reward_out;
+      e->win_exp = reward_exp;
+      if (++e->win >= window) return env_window_end(e);
+      return RNAFOLD_OK;
+    }
+    int rc = env_window_end(e);   // an undeferred step closes whatever is open first
+    if (rc) return rc;
+  }
   // d_off: [0] total length, [1] count (one 64-bit word advanced atomically by the terminal environments), [2..] offsets
   // (the terminal counter is zero here: cleared by the last kernel of the previous step, by reset(), and on error returns)
   env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
                                                    e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
                                                    reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
-                                                   e->d_bseq, e->d_btgt, e->d_slot, e->d_ep, e->d_keys);
+                                                   e->d_bseq, e->d_btgt, e->d_slot, e->d_ep, e->d_keys, nullptr, nullptr, 0);
   ENV_TRY(cudaGetLastError());
   int rc = RNAFOLD_OK;
   if (e->permute) {
@@ -639,6 +892,10 @@ int rnafold_env_stats(int32_t h, uint64_t istat[4], double fstat[2], int32_t cle
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e || !istat || !fstat) return set_error(RNAFOLD_EINVAL, "bad env handle");
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   ENV_TRY(cudaMemcpyAsync(istat, e->d_istat, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
   ENV_TRY(cudaMemcpyAsync(fstat, e->d_fstat, 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   if (clear) {
@@ -656,6 +913,10 @@ int rnafold_env_snapshot(int32_t h, uint8_t *seq, int32_t *idx, int32_t *cur, in
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e || !e->n_targets) return set_error(RNAFOLD_EINVAL, "bad env handle or no targets set");
+  {
+    int rc_ = env_window_end(e);   // pending deferred rewards first
+    if (rc_) return rc_;
+  }
   const size_t N = (size_t)e->n_envs, NL = N * (size_t)e->lmax;
   cudaStream_t st = e->stream;
   ENV_TRY(copy_out(seq, e->d_seq, NL, st));

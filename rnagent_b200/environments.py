@@ -93,6 +93,7 @@ class RnaDesignBatch(object):
         self.L = _lib.lib()
         h = ctypes.c_int32(-1)
         _lib.check(self.L.rnafold_env_create(self.n_envs, self.kernel_size, ctypes.byref(h)))
+        self._torch_stream, self._stream = False, None
         self._h = h.value
         self._configure()
         self.observation_shape = (ROWS, 2 * self.kernel_size, 1)
@@ -150,7 +151,32 @@ class RnaDesignBatch(object):
     def step_device(self, actions, obs=None, reward=None, done=None):
         """Same step with torch CUDA tensors (int32 actions; uint8 obs [N,10,2k], float64 reward, uint8 done)."""
         p = lambda t: None if t is None else t.data_ptr()
+        if self._torch_stream:      # order the step against the caller's torch work (policy before, consumers after)
+            import torch
+            s = torch.cuda.current_stream().cuda_stream
+            if s != self._stream:
+                _lib.check(self.L.rnafold_env_set_stream(self._h, s, 0))
+                self._stream = s
         _lib.check(self.L.rnafold_env_step(self._h, actions.data_ptr(), self.reward_exp, p(obs), p(reward), p(done)))
+
+    def use_torch_stream(self, enabled=True):
+        """step_device on torch's current CUDA stream (True: the step is stream-ordered with the tensors' producers and
+        consumers) or on the environments' own non-blocking stream (False, default: synchronise yourself)."""
+        self._torch_stream = bool(enabled)
+        if not enabled and self._stream is not None:
+            _lib.check(self.L.rnafold_env_set_stream(self._h, None, 1))
+            self._stream = None
+
+    def set_reward_delay(self, steps):
+        """Deferred rewards for step_device (rnafold_env_config_delay): the terminal sequences of up to `steps` consecutive
+        steps are folded together, and each reward lands in the `reward` tensor that was passed to ITS step -- at the latest
+        after `steps` steps, on flush(), or before stats() / snapshot() / reset().  Pass a different reward tensor to every
+        step of a window (a [T, N] rollout buffer).  steps=1: every step folds its own terminals (default)."""
+        _lib.check(self.L.rnafold_env_config_delay(self._h, int(steps)))
+
+    def flush(self):
+        """Deliver the rewards that are still deferred (stream-ordered on the environments' stream, no host wait)."""
+        _lib.check(self.L.rnafold_env_flush(self._h))
 
     def stats(self, clear=False):
         """Rollout statistics accumulated on the device since the last clear."""
@@ -290,3 +316,30 @@ def rollout(env, policy, n_steps):
         state, r, done, _ = env.step(actions)
         total_r += float(r.sum())
     return env.stats(), total_r
+
+
+def rollout_device(env, policy, n_steps, reward_delay=8, obs=None):
+    """The vectorised rollout loop with everything on the device (trainer.py:307-309 keeps (state, r, done) per step for PPO):
+    `policy(obs_uint8[N, 10, 2k]) -> int32 actions[N]` on CUDA tensors.  Returns (rewards[T, N] float64, dones[T, N] uint8,
+    last observation, RolloutStats).  Rewards are deferred by up to `reward_delay` steps inside the loop -- the policy never
+    sees them -- and complete when this function returns; values equal those of step-by-step folding."""
+    import torch
+    dev = torch.device("cuda", torch.cuda.current_device())
+    N = env.n_envs
+    if obs is None:
+        obs = torch.empty((N, 10, 2 * env.kernel_size), dtype=torch.uint8, device=dev)
+        obs.copy_(torch.from_numpy(env.reset()).reshape(N, 10, -1))
+    rewards = torch.zeros((n_steps, N), dtype=torch.float64, device=dev)
+    dones = torch.zeros((n_steps, N), dtype=torch.uint8, device=dev)
+    env.set_reward_delay(reward_delay)
+    env.use_torch_stream(True)
+    try:
+        for t in range(n_steps):
+            actions = policy(obs)
+            env.step_device(actions, obs, rewards[t], dones[t])
+        env.flush()
+    finally:
+        env.set_reward_delay(1)
+        torch.cuda.synchronize()
+        env.use_torch_stream(False)
+    return rewards, dones, obs, env.stats()

@@ -202,3 +202,75 @@ def test_create_env_rollout_and_timed_evaluation(tmp_path):
         "Date, Solved, Time(s), Model, Checkpoint, learn_test, taneda, learn_validation, eterna\n"   # first call: header only (quirk)
     env.close()
     w.test_env.close()
+
+
+@pytest.mark.parametrize("gc_penalty", [False, True])
+def test_deferred_rewards_equal_step_by_step(gc_penalty):
+    """rnafold_env_config_delay: folding the terminal sequences of up to 8 steps together changes WHEN a reward is written,
+    never its value or its place -- rewards [T, N], dones, every observation, the rollout statistics and the last solutions
+    equal those of step-by-step folding; short targets cap the window at their episode length; stats() in the middle of a
+    window delivers what is pending."""
+    import torch
+    import rnagent_b200 as rb
+    from rnagent_b200 import synth
+    rb.set_vienna_params(1)
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(3)
+    for lens, delay in (([30, 45, 60, 100], 8), ([12, 14, 40], 16), ([100], 5)):
+        targets = [synth.random_structure(int(n), rng).tobytes().decode() for n in lens for _ in range(3)]
+        cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True, gc_penalty=gc_penalty)
+        N, T = 384, 230
+        envs = [rb.RnaDesignBatch(cfg, N, targets=targets, auto_reset=True, randomize=True, seed=11) for _ in range(2)]
+        g = torch.Generator(device=dev)
+        g.manual_seed(5)
+        acts = torch.randint(0, 4, (T, N), dtype=torch.int32, device=dev, generator=g)
+        out = []
+        for which, env in enumerate(envs):
+            env.reset()
+            env.set_reward_delay(delay if which else 1)
+            obs = torch.zeros((T, N, 10, 50), dtype=torch.uint8, device=dev)
+            rew = torch.full((T, N), -7.0, dtype=torch.float64, device=dev)
+            done = torch.zeros((T, N), dtype=torch.uint8, device=dev)
+            mid = None
+            for t in range(T):
+                env.step_device(acts[t], obs[t], rew[t], done[t])
+                if t == 101:
+                    mid = env.stats()            # closes the open window first
+            env.flush()
+            torch.cuda.synchronize()
+            st, snap = env.stats(), env.snapshot()
+            out.append((obs.cpu().numpy(), rew.cpu().numpy(), done.cpu().numpy(), st.as_vector(), mid.as_vector(), snap))
+            env.close()
+        a, b = out
+        assert (a[2] == b[2]).all() and a[2].sum() > N                 # dones, several episodes per environment
+        assert (a[0] == b[0]).all()                                     # observations
+        assert (a[1] == b[1]).all() and (a[1] != -7.0).all()            # rewards: same values at the same (step, env)
+        assert (a[1][a[2] == 0] == 0.0).all() and (a[1][a[2] == 1] > 0.0).mean() > 0.9
+        assert np.allclose(a[3], b[3]) and np.allclose(a[4], b[4])     # statistics at the end and in the middle
+        for key in ("last_seq", "last_db", "last_hd", "last_mfe", "last_t", "seq", "idx", "cur", "ep"):
+            assert (a[5][key] == b[5][key]).all(), key
+
+
+def test_rollout_device_matches_host_rollout():
+    import torch
+    import rnagent_b200 as rb
+    from rnagent_b200 import synth
+    rb.set_vienna_params(1)
+    rng = np.random.default_rng(8)
+    targets = [synth.random_structure(40, rng).tobytes().decode() for _ in range(5)]
+    cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True)
+    N, T = 64, 120
+
+    def policy_np(state):                    # a deterministic function of the observation
+        return (state.reshape(N, -1).astype(np.int64).sum(axis=1) % 4).astype(np.int32)
+
+    def policy_t(obs):
+        return (obs.reshape(N, -1).to(torch.int64).sum(dim=1) % 4).to(torch.int32)
+    env = rb.RnaDesignBatch(cfg, N, targets=targets, auto_reset=True, randomize=False, seed=0)
+    stats_h, total_h = rb.rollout(env, policy_np, T)
+    env.close()
+    env = rb.RnaDesignBatch(cfg, N, targets=targets, auto_reset=True, randomize=False, seed=0)
+    rew, done, _, stats_d = rb.rollout_device(env, policy_t, T, reward_delay=8)
+    env.close()
+    assert np.allclose(stats_h.as_vector(), stats_d.as_vector()) and stats_d.episodes > N
+    assert abs(float(rew.sum().item()) - total_h) < 1e-9 and int(done.sum().item()) == stats_d.episodes
