@@ -163,7 +163,7 @@ int rnafold_env_step(int32_t handle, const int32_t *actions, double reward_exp, 
  * after `steps` steps, on rnafold_env_flush, or before any call that reads or changes the environments' state (stats,
  * snapshot, reset, set_targets, config_*).  Values are identical to the undeferred step's; observations, dones and
  * auto-resets are never deferred.  The window is capped by the shortest episode of the data set (no environment finishes
- * twice within it); steps with a host output buffer or with the local search run undeferred.  steps = 1 (default): every
+ * twice within it); steps with a host output buffer, with the local search or without auto-reset run undeferred.  steps = 1 (default): every
  * step folds its own terminals.  No counterpart in the reference (its workers fold synchronously inside step()). */
 /* Enqueue the environments' work on the CALLER's stream from now on (a cudaStream_t, e.g. torch's current stream, so that a
  * policy network and the step are ordered without host synchronisation); use_own != 0 returns to the environments' own

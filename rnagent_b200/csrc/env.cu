@@ -790,7 +790,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
     const int window = std::min(e->delay, e->min_episode);
     const bool dev_out = (!obs_out || env_is_device_ptr(obs_out)) && (!reward_out || env_is_device_ptr(reward_out)) &&
                          (!done_out || env_is_device_ptr(done_out));
-    if (window > 1 && dev_out && !e->permute) {
+    if (window > 1 && dev_out && !e->permute && e->auto_reset) {   // (without auto-reset a finished environment finishes again every step)
       if (e->win > 0 && e->win_exp != reward_exp) {
         int rc = env_window_end(e);
         if (rc) return rc;
