@@ -38,6 +38,15 @@ WORKLOADS = {
 PARAM_NAMES = {1: "turner2004", 2: "turner1999"}
 
 
+_JSON_OUT = None
+
+
+def emit_json(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def make_workload(name, rank):
     count, n, seed, setno, desc = WORKLOADS[name]
     if n is None:
@@ -234,7 +243,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "folds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     return 0
 
 
@@ -404,7 +413,7 @@ def run_ours(args):
         "checksum_mfe_dcal": checksum,
     }
     line.update(extra)
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -627,6 +636,12 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the n=400 and env-steps measurements")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON: whatever libraries print there (NCCL's version banner under NCCL_DEBUG=VERSION,
+    # for one) goes to stderr instead
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)
