@@ -166,7 +166,7 @@ int rnafold_env_step(int32_t handle, const int32_t *actions, double reward_exp, 
  * twice within it); steps with a host output buffer, with the local search or without auto-reset run undeferred.  steps = 1 (default): every
  * step folds its own terminals.  No counterpart in the reference (its workers fold synchronously inside step()). */
 /* Enqueue the environments' work on the CALLER's stream from now on (a cudaStream_t, e.g. torch's current stream, so that a
- * policy network and the step are ordered without host synchronisation); use_own != 0 returns to the environments' own
+ * policy network and the step are ordered without host synchronisation; NULL = the legacy default stream); use_own != 0 returns to the environments' own
  * non-blocking stream, on which device outputs are only ordered against the library's own calls. */
 int rnafold_env_set_stream(int32_t handle, void *stream, int32_t use_own);
 int rnafold_env_config_delay(int32_t handle, int32_t steps);

@@ -521,7 +521,9 @@ int rnafold_env_set_stream(int32_t h, void *stream, int32_t use_own) {
   std::lock_guard<std::mutex> lk(g_env_mu);
   Env *e = get_env(h);
   if (!e) return set_error(RNAFOLD_EINVAL, "bad env handle");
-  cudaStream_t next = use_own ? e->own_stream : (cudaStream_t)stream;
+  // a null handle is the legacy default stream (torch's default stream reports 0): named explicitly, because the fold entry
+  // points read a null stream as "the library's own"
+  cudaStream_t next = use_own ? e->own_stream : (stream ? (cudaStream_t)stream : cudaStreamLegacy);
   if (next == e->stream) return RNAFOLD_OK;
   cudaEvent_t ev;
   ENV_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));

@@ -274,3 +274,66 @@ def test_rollout_device_matches_host_rollout():
     env.close()
     assert np.allclose(stats_h.as_vector(), stats_d.as_vector()) and stats_d.episodes > N
     assert abs(float(rew.sum().item()) - total_h) < 1e-9 and int(done.sum().item()) == stats_d.episodes
+
+
+def test_deferred_rewards_interleaved_with_other_calls():
+    """Whatever reads or changes the environments' state closes the open window first: a host step(), a change of the delay,
+    reset(), new targets and a stream switch in the middle of a window leave the same rewards as step-by-step folding."""
+    import torch
+    import rnagent_b200 as rb
+    from rnagent_b200 import synth
+    rb.set_vienna_params(1)
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(17)
+    targets = [synth.random_structure(int(n), rng).tobytes().decode() for n in (24, 33, 47, 60)]
+    targets2 = [synth.random_structure(int(n), rng).tobytes().decode() for n in (18, 52)]
+    cfg = dict(kernel_size=25, reward_exp=9, permute=False, encoding_type=2, use_nucleotides=True)
+    N, T = 96, 150
+    g = torch.Generator(device=dev)
+    g.manual_seed(9)
+    acts = torch.randint(0, 4, (T, N), dtype=torch.int32, device=dev, generator=g)
+    side = torch.cuda.Stream(device=dev)
+    results = []
+    for deferred in (False, True):
+        env = rb.RnaDesignBatch(cfg, N, targets=targets, auto_reset=True, randomize=True, seed=4)
+        env.reset()
+        rew = torch.full((T, N), -3.0, dtype=torch.float64, device=dev)
+        done = torch.zeros((T, N), dtype=torch.uint8, device=dev)
+        obs = torch.zeros((N, 10, 50), dtype=torch.uint8, device=dev)
+        host_r = []
+        torch.cuda.synchronize()
+        if deferred:
+            env.set_reward_delay(12)
+        for t in range(T):
+            if t == 20 or t == 21:                      # a host step in the middle of a window
+                _, r, d, _ = env.step(acts[t].cpu().numpy())
+                host_r.append((r.copy(), d.copy()))
+                rew[t] = torch.from_numpy(r).to(dev)
+                done[t] = torch.from_numpy(d.astype(np.uint8)).to(dev)
+                continue
+            if t == 45 and deferred:
+                env.set_reward_delay(5)                 # closes the window, then a shorter one
+            if t == 70:
+                env.reset()                             # pending rewards are delivered before the reset
+            if t == 100:
+                env.set_data(targets2)                  # ... and before new targets
+                env.reset()
+            if t == 120:
+                env.use_torch_stream(True)
+            if 120 <= t < 135:
+                with torch.cuda.stream(side):           # steps ordered on a torch side stream
+                    side.wait_stream(torch.cuda.current_stream())
+                    env.step_device(acts[t], obs, rew[t], done[t])
+                torch.cuda.current_stream().wait_stream(side)
+            else:
+                env.step_device(acts[t], obs, rew[t], done[t])
+        env.flush()
+        torch.cuda.synchronize()
+        results.append((rew.cpu().numpy(), done.cpu().numpy(), env.stats().as_vector(), host_r))
+        env.close()
+    a, b = results
+    assert (a[1] == b[1]).all() and a[1].sum() > 2 * N
+    assert (a[0] == b[0]).all() and (a[0] != -3.0).all()
+    assert np.allclose(a[2], b[2])
+    for (r0, d0), (r1, d1) in zip(a[3], b[3]):
+        assert (r0 == r1).all() and (d0 == d1).all()
