@@ -215,9 +215,13 @@ Limits make_limits(Context *c) {
   for (int k = 0; k < kNumWaveClasses; ++k)
     if (wave_smem_bytes(kWaveClasses[k], m.wave_esz) + 1024 <= (size_t)c->max_smem_optin) m.wave_limit = kWaveClasses[k];
   m.cluster_limit = m.wave_limit;
+  const int wave_keep = m.wave_limit;
   if (m.wave_esz == 2)
     for (int q = 0; q < kNumClusterClasses; ++q)
       if (cluster_smem_bytes(kClusterClasses[q], 2) + 1024 <= (size_t)c->max_smem_optin) m.cluster_limit = kClusterClasses[q];
+  // experiments only: RNAFOLD_WAVE_LIMIT=<n> sends everything longer than n to the cluster kernel
+  static const int forced_limit = getenv("RNAFOLD_WAVE_LIMIT") ? atoi(getenv("RNAFOLD_WAVE_LIMIT")) : 0;
+  if (forced_limit > 0 && m.cluster_limit > wave_keep) m.wave_limit = std::min(m.wave_limit, forced_limit);
   return m;
 }
 

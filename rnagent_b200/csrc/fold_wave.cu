@@ -56,6 +56,14 @@ __device__ __forceinline__ const SmallParams &small_params(const FoldParams *__r
   else return gp->s;
 }
 
+#ifdef WAVE_TRACE   // debug builds only (tools/wave_trace.py): per-warp time stamps of every phase of one fold (CTA 0, first fold)
+__device__ unsigned g_wave_trace[512 * 16 * 8];
+#define WTRACE(slot_) do { if (wtracing && lane == 0 && d < 512) g_wave_trace[(d * 16 + (warp & 15)) * 8 + (slot_)] = (unsigned)(clock64() - wtrace_t0); } while (0)
+#define WTRACE_VAL(slot_, v_) do { if (wtracing && lane == 0 && d < 512) g_wave_trace[(d * 16 + (warp & 15)) * 8 + (slot_)] = (unsigned)(v_); } while (0)
+#else
+#define WTRACE(slot_) do { } while (0)
+#define WTRACE_VAL(slot_, v_) do { } while (0)
+#endif
 #ifdef WAVE_PHASE_CLK  // debug builds only: cycles per phase, summed over all folds (tools/phase_clocks.py)
 __device__ unsigned long long g_phase_clk[640];
 #ifndef WAVE_SKIP
@@ -726,7 +734,15 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
     // the folded fML layout (fi1), and the latter for d1 - 1 (fi0); the folded layout turns around after row T0
     int tri1 = 0, fi1 = 0, fi0 = 0;
     const int foldT0 = rs / 2 + 2, fold_jump = fold_idx(rs, foldT0 + 1, 0) - fold_idx(rs, foldT0, 0);
+#ifdef WAVE_TRACE
+    __shared__ long long wtrace_base;
+    if (tid == 0) wtrace_base = clock64();
+    __syncthreads();
+    const long long wtrace_t0 = wtrace_base;
+    const bool wtracing = blockIdx.x == 0 && slot < (int)gridDim.x;
+#endif
     for (int d = kTurn + 1; d <= n + 1; ++d) {
+      WTRACE(0);
       const int par = d & 1, par1 = par ^ 1;
       const int cells_d = (d < n) ? n - d : 0;
       const int nb_d = (cells_d + 31) >> 5;
@@ -762,6 +778,8 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
         }
       }
       ITEM_CLK_END(5, d >= 68 ? 1 : 0);
+      WTRACE(1);
+      WTRACE_VAL(4, 0);
       // the block items start with the warp after the last one that took a cell, to even out the phase
       const int nG = nvalid > 0 ? npair : 0;
       int neparts = 0;
@@ -915,7 +933,9 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
           if (lane == 0) f5[j] = min(f5[j - 1], best);
         }
         ITEM_CLK_END(item_kind, d >= 68 ? 1 : 0);
+        WTRACE_VAL(4, 1 + (k < nI ? 0 : k < nI + nT ? 1 : k < nI + nT + nM ? 2 : k < nI + nT + nM + nF ? 3 : 4));   // kind of the last item
       }
+      WTRACE(2);
       // next diagonal: the tabulated shapes' rows shift by one (row r+1 starts n-r cells after row r)
 #pragma unroll
       for (int k = 5; k >= 1; --k) trow[k] = trow[k - 1];
@@ -941,6 +961,7 @@ __global__ void __launch_bounds__(MAXT) __maxnreg__(MAXT == kSmallThreads && siz
         }
       }
       __syncthreads();
+      WTRACE(3);
       PHASE_CLK_END(d);
     }
 
@@ -1111,6 +1132,12 @@ cudaError_t launch_fold_wave(const FoldParams *gp, const BatchArgs &a, int nmax,
 
 int wave_occupancy(int nmax, int esz, int threads) { return WAVE_DISPATCH(occupancy_t, nmax); }
 
+#ifdef WAVE_TRACE
+extern "C" int rnafold_debug_wave_trace(unsigned *out, int count) {
+  if (count > 512 * 16 * 8) count = 512 * 16 * 8;
+  return cudaMemcpyFromSymbol(out, g_wave_trace, sizeof(unsigned) * count) == cudaSuccess ? 0 : -1;
+}
+#endif
 #ifdef CLUSTER_TRACE
 extern "C" int rnafold_debug_cluster_trace(unsigned *out, int count) {
   if (count > 2 * 480 * 16 * 4) count = 2 * 480 * 16 * 4;
