@@ -160,57 +160,6 @@ __global__ void env_reset_kernel(int n_envs, int n_targets, int lmax, int random
 }
 
 // insert_nucleotide + find_next_unfilled (solution.py:84-114) and the terminal test of RnaDesign.step
-__global__ void env_step_kernel(int n_envs, int lmax, const int32_t *__restrict__ act, const int32_t *__restrict__ cur,
-                                const int32_t *__restrict__ toff, const uint8_t *__restrict__ tgt,
-                                const int16_t *__restrict__ pair, int32_t *idx, uint8_t *seq, uint8_t *mask,
-                                uint8_t *done, double *reward, unsigned long long *istat, unsigned long long *packed,
-                                int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt, int32_t *slot_of,
-                                const int32_t *__restrict__ ep, unsigned long long *keys, int32_t *pend, int32_t *pend_t,
-                                int jstep) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n_envs) return;
-  const int t = cur[e];
-  const int base = toff[t], n = toff[t + 1] - base;
-  uint8_t *s = seq + (size_t)e * lmax, *m = mask + (size_t)e * lmax;
-  const int i = idx[e];
-  const int a = act[e] & 3;
-  m[i] |= (uint8_t)(1u << a);
-  s[i] = "ACGU"[a];
-  if (tgt[base + i] == '(') {
-    const int p = pair[base + i];
-    if (p >= 0) {
-      m[p] |= (uint8_t)(1u << (3 - a));  // reverse_action: the Watson-Crick partner
-      s[p] = "UGCA"[a];
-    }
-  }
-  reward[e] = 0.0;  // Solution.r stays 0 until evaluate()
-  if (i < n - 1) {
-    int q = i;
-    while (q < n - 1 && s[q] != '-') ++q;  // stops at n-1 even if that slot is filled (reference quirk)
-    idx[e] = q;
-    done[e] = 0;
-  } else {
-    done[e] = 1;
-    // terminal: claim the next slot of the CSR batch that goes to the fold.  Count and total length advance in ONE
-    // 64-bit atomic, so slot order and offset order agree and the offsets form a proper CSR whatever the arrival order.
-    const unsigned long long old = atomicAdd(packed, (1ull << 32) | (unsigned long long)n);
-    const int slot = (int)(old >> 32), o0 = (int)(old & 0xffffffffull);
-    list[slot] = e;
-    slot_of[e] = slot;
-    if (pend) {   // deferred rewards: which step of the window this terminal belongs to, and its target
-      pend[e] = jstep + 1;
-      pend_t[e] = t;
-    }
-    keys[slot] = ((unsigned long long)(unsigned)e << 32) | (unsigned long long)(unsigned)ep[e];  // what the local search's draws are keyed on
-    boff[slot] = o0;
-    for (int q = 0; q < n; ++q) {
-      bseq[o0 + q] = s[q];
-      btgt[o0 + q] = tgt[base + q];
-    }
-  }
-  atomicAdd(&istat[3], 1ull);
-}
-
 // observation window encoding[:, i:i+2k] of the zero-padded [10, len+2k] encoding (solution.py:62-75,116-123)
 __global__ void env_obs_kernel(int n_envs, int lmax, int k, const int32_t *__restrict__ cur, const int32_t *__restrict__ idx,
                                const int32_t *__restrict__ toff, const uint8_t *__restrict__ mot,
@@ -320,37 +269,96 @@ __global__ void env_finish_kernel(int n_envs, int n_targets, int lmax, int k, in
   }
 }
 
-// ---- deferred rewards (window of several steps, one fold): the two halves of env_finish_kernel
-// (a) every step: auto-reset of the environments that just finished + the observation -- nothing here needs the fold
-__global__ void env_resetobs_kernel(int n_envs, int n_targets, int lmax, int k, int auto_reset, int randomize, unsigned long long seed,
-                                    const uint8_t *__restrict__ done, const int32_t *__restrict__ toff,
-                                    const uint8_t *__restrict__ mot, int32_t *cur, int32_t *idx, int32_t *ep, uint8_t *seq,
-                                    uint8_t *mask, uint8_t *obs) {
+// ---- deferred rewards (window of several steps, one fold)
+// (a) RnaDesign.step for one environment per BLOCK: the cursor update is one thread's work, the copy of a finished sequence into
+// the fold batch is spread over the block.  full != 0 (deferred rewards: ONE launch per step) adds the half of
+// env_finish_kernel that does not need the fold -- auto-reset and observation window -- and marks the environment as pending
+__global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int auto_reset, int randomize, unsigned long long seed,
+                                   const int32_t *__restrict__ act, const int32_t *__restrict__ toff,
+                                   const uint8_t *__restrict__ tgt, const int16_t *__restrict__ pair,
+                                   const uint8_t *__restrict__ mot, int32_t *cur, int32_t *idx, int32_t *ep, uint8_t *seq,
+                                   uint8_t *mask, uint8_t *done, double *reward, unsigned long long *istat,
+                                   unsigned long long *packed, int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt,
+                                   int32_t *slot_of, unsigned long long *keys, int32_t *pend, int32_t *pend_t, int jstep,
+                                   uint8_t *obs, int full) {
+  __shared__ int sh[4];   // done, offset in the batch, target base, length
   const int e = blockIdx.x;
   if (e >= n_envs) return;
-  if (done[e] && auto_reset) {
-    if (threadIdx.x == 0) {   // RnaDesign.reset: next target, empty solution
-      const int t0 = cur[e], epn = ep[e] + 1;
-      int t;
-      if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
-      else t = (t0 + 1) % n_targets;
-      cur[e] = t;
-      idx[e] = 0;
-      ep[e] = epn;
+  uint8_t *s = seq + (size_t)e * lmax, *m = mask + (size_t)e * lmax;
+  if (threadIdx.x == 0) {
+    const int t = cur[e];
+    const int base = toff[t], n = toff[t + 1] - base;
+    const int i = idx[e];
+    const int a = act[e] & 3;
+    m[i] |= (uint8_t)(1u << a);
+    s[i] = "ACGU"[a];
+    if (tgt[base + i] == '(') {
+      const int p = pair[base + i];
+      if (p >= 0) {
+        m[p] |= (uint8_t)(1u << (3 - a));  // reverse_action: the Watson-Crick partner
+        s[p] = "UGCA"[a];
+      }
     }
-    for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
-      seq[(size_t)e * lmax + q] = '-';
-      mask[(size_t)e * lmax + q] = 0;
+    reward[e] = 0.0;
+    int fin = 0, o0 = 0;
+    if (i < n - 1) {
+      int q = i;
+      while (q < n - 1 && s[q] != '-') ++q;  // stops at n-1 even if that slot is filled (reference quirk)
+      idx[e] = q;
+    } else {
+      fin = 1;
+      const unsigned long long old = atomicAdd(packed, (1ull << 32) | (unsigned long long)n);
+      const int slot = (int)(old >> 32);
+      o0 = (int)(old & 0xffffffffull);
+      list[slot] = e;
+      slot_of[e] = slot;
+      keys[slot] = ((unsigned long long)(unsigned)e << 32) | (unsigned long long)(unsigned)ep[e];
+      boff[slot] = o0;
+      if (full) {   // deferred rewards: which step of the window this terminal belongs to, and its target
+        pend[e] = jstep + 1;
+        pend_t[e] = t;
+      }
+    }
+    done[e] = (uint8_t)fin;
+    if (e == 0) atomicAdd(&istat[3], (unsigned long long)n_envs);
+    sh[0] = fin;
+    sh[1] = o0;
+    sh[2] = base;
+    sh[3] = n;
+  }
+  __syncthreads();
+  if (sh[0]) {
+    const int o0 = sh[1], base = sh[2], n = sh[3];
+    for (int q = threadIdx.x; q < n; q += blockDim.x) {
+      bseq[o0 + q] = s[q];
+      btgt[o0 + q] = tgt[base + q];
+    }
+    if (auto_reset && full) {
+      __syncthreads();   // the copy reads the solution that is cleared next
+      if (threadIdx.x == 0) {   // RnaDesign.reset: next target, empty solution
+        const int t0 = cur[e], epn = ep[e] + 1;
+        int t;
+        if (randomize) t = (int)(mix64(seed ^ ((unsigned long long)e << 32) ^ (unsigned long long)epn) % (unsigned long long)n_targets);
+        else t = (t0 + 1) % n_targets;
+        cur[e] = t;
+        idx[e] = 0;
+        ep[e] = epn;
+      }
+      for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
+        s[q] = '-';
+        m[q] = 0;
+      }
     }
     __syncthreads();
   }
+  if (!full) return;   // step-synchronous rewards: env_finish_kernel resets and writes the observation after the fold
   const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
   const int w = 2 * k;
   auto cell = [&](int q) -> unsigned {
     const int row = q / w, col = q - row * w;
     const int pos = i - k + col;
     unsigned v = 0;
-    if (pos >= 0 && pos < n) v = row < 6 ? (mot[base + pos] == row) : ((mask[(size_t)e * lmax + pos] >> (row - 6)) & 1);
+    if (pos >= 0 && pos < n) v = row < 6 ? (mot[base + pos] == row) : ((m[pos] >> (row - 6)) & 1);
     return v;
   };
   uint8_t *dst = obs + (size_t)e * kRows * w;
@@ -799,15 +807,11 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
       }
       uint8_t *d_done = done_out ? done_out : e->d_done;
       double *d_rw = reward_out ? reward_out : e->d_reward;
-      env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
-                                                       e->d_seq, e->d_mask, d_done, d_rw, e->d_istat,
-                                                       reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
-                                                       e->d_bseq, e->d_btgt, e->d_slot, e->d_ep, e->d_keys, e->d_pend, e->d_pend_t,
-                                                       e->win);
-      ENV_TRY(cudaGetLastError());
-      env_resetobs_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, e->auto_reset ? 1 : 0, e->randomize ? 1 : 0, e->seed,
-                                             d_done, e->d_toff, e->d_mot, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask,
-                                             obs_out ? obs_out : e->d_obs);
+      env_step_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, 1, e->randomize ? 1 : 0, e->seed, d_act, e->d_toff, e->d_tgt,
+                                            e->d_pair, e->d_mot, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask, d_done, d_rw,
+                                            e->d_istat, reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
+                                            e->d_bseq, e->d_btgt, e->d_slot, e->d_keys, e->d_pend, e->d_pend_t, e->win,
+                                            obs_out ? obs_out : e->d_obs, 1);
       ENV_TRY(cudaGetLastError());
       e->win_r[e->win] = reward_out;
       e->win_exp = reward_exp;
@@ -819,10 +823,10 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   }
   // d_off: [0] total length, [1] count (one 64-bit word advanced atomically by the terminal environments), [2..] offsets
   // (the terminal counter is zero here: cleared by the last kernel of the previous step, by reset(), and on error returns)
-  env_step_kernel<<<(N + 127) / 128, 128, 0, st>>>(N, e->lmax, d_act, e->d_cur, e->d_toff, e->d_tgt, e->d_pair, e->d_idx,
-                                                   e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
-                                                   reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
-                                                   e->d_bseq, e->d_btgt, e->d_slot, e->d_ep, e->d_keys, nullptr, nullptr, 0);
+  env_step_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, 0, 0, e->seed, d_act, e->d_toff, e->d_tgt, e->d_pair, e->d_mot,
+                                        e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
+                                        reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2, e->d_bseq,
+                                        e->d_btgt, e->d_slot, e->d_keys, nullptr, nullptr, 0, nullptr, 0);
   ENV_TRY(cudaGetLastError());
   int rc = RNAFOLD_OK;
   if (e->permute) {
