@@ -1,7 +1,10 @@
 #!/usr/bin/env python3
 """Per-warp time line of ONE fold in the 512-thread (latency) instance of the wave kernel (library built with -DWAVE_TRACE).
 
-    RNAFOLD_LIB=build_var/wtrace.so python tools/wave_trace.py 100 [d ...]
+    RNAFOLD_LIB=build_var/wtrace.so [TRACE_COUNT=8] python tools/wave_trace.py 100 [d ...]
+
+TRACE_COUNT sequences are folded (8: the latency instance, one fold per SM; >= 740: the 128-thread throughput instance,
+five folds per SM -- the trace is CTA 0's first fold either way).
 
 Stamps per phase and warp (SM cycles): 0 phase start, 1 generic-shape cells done, 2 block items done, 3 after the barrier;
 4 = kind of the warp's last block item (1 E, 2 T, 3 M, 4 F, 5 X; 0 none).
@@ -17,15 +20,18 @@ from rnagent_b200 import _lib, synth  # noqa: E402
 
 n = int(sys.argv[1])
 show = [int(v) for v in sys.argv[2:]]
-seq, off = synth.random_sequences(8, n, seed=5)
+count = int(os.environ.get("TRACE_COUNT", 8))
+seq, off = synth.random_sequences(count, n, seed=5)
 db = np.zeros(len(seq), np.uint8)
-mfe = np.zeros(8, np.int32)
+mfe = np.zeros(count, np.int32)
 L = _lib.lib()
 out = (ctypes.c_uint * (512 * 16 * 8))()
 for _ in range(2):
-    _lib.fold_hamming_raw(seq, off, 8, db=db, mfe=mfe)
+    _lib.fold_hamming_raw(seq, off, count, db=db, mfe=mfe)
 L.rnafold_debug_wave_trace(out, len(out))
 t = np.array(list(out), dtype=np.float64).reshape(512, 16, 8)
+nw = 16 if count <= 148 else 4
+t = t[:, :nw, :]
 print("info", _lib.last_launch_info())
 kinds = ["-", "E", "T", "M", "F", "X"]
 tot = t[n + 1, :, 3].max() - t[5, :, 0].min()
