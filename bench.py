@@ -604,7 +604,7 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
     msecs = max_over_ranks(time.perf_counter() - t0)
     mstats = env.stats().all_reduce(device=dev)
     d_rT = torch.empty((msteps, N), dtype=torch.float64, device=dev)
-    env.set_reward_delay(32)                             # capped by the shortest episode of the data set (12-nt targets: ~8 steps)
+    env.set_reward_delay(32)                             # capped by eight times the shortest episode of the data set
     env.stats(clear=True)
     barrier()
     t0 = time.perf_counter()
@@ -619,7 +619,7 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
                         "per_gpu": mstats.steps / msecs / world, "us_per_vector_step": 1e6 * msecs / msteps,
                         "episodes_per_s": mstats.episodes / msecs, "envs_per_gpu": N, "steps_timed": msteps,
                         "rollout_deferred": {"value": mdstats.steps / mdsecs, "unit": "env steps/s", "us_per_vector_step": 1e6 * mdsecs / msteps,
-                                             "reward_delay_steps": "32 requested, capped by the shortest episode"},
+                                             "reward_delay_steps": "32 requested, capped by 8 x the shortest episode"},
                         "workload": "4096 RnaDesign envs per GPU, targets = folds of 128 random sequences with the Eterna100 length mix "
                                     "(12-400 nt), uniform random actions, auto-reset, 400 untimed steps first"}
     return out

@@ -162,9 +162,9 @@ int rnafold_env_step(int32_t handle, const int32_t *actions, double reward_exp, 
  * reward lands in the reward_out buffer that was passed to the step it belongs to, at the latest when the window closes:
  * after `steps` steps, on rnafold_env_flush, or before any call that reads or changes the environments' state (stats,
  * snapshot, reset, set_targets, config_*).  Values are identical to the undeferred step's; observations, dones and
- * auto-resets are never deferred.  The window is capped by the shortest episode of the data set (no environment finishes
- * twice within it); steps with a host output buffer, with the local search or without auto-reset run undeferred.  steps = 1 (default): every
- * step folds its own terminals.  No counterpart in the reference (its workers fold synchronously inside step()). */
+ * auto-resets are never deferred.  The window is capped by eight times the shortest episode of the data set (an environment
+ * may finish up to eight times within it; every finish gets its own batch entry); steps with a host output buffer, with
+ * the local search or without auto-reset run undeferred.  steps = 1 (default): every step folds its own terminals.  No counterpart in the reference (its workers fold synchronously inside step()). */
 /* Enqueue the environments' work on the CALLER's stream from now on (a cudaStream_t, e.g. torch's current stream, so that a
  * policy network and the step are ordered without host synchronisation; NULL = the legacy default stream); use_own != 0 returns to the environments' own
  * non-blocking stream, on which device outputs are only ordered against the library's own calls. */

@@ -601,13 +601,14 @@ struct RouteTable {
   int wfirst, wlast;              // wave class launches [wfirst, wlast] (-1: none)
   int cfirst, clast, cmax;        // cluster class launches [cfirst, clast]; cmax: clusters resident at once in clast's class
                                   // (a batch with <= cmax cluster-length sequences sends them all to launch clast)
+  int ccap;                       // most cluster-length sequences the caller promised (the cluster workspace is sized for it)
   int upper[kMaxDynLaunches];     // class launches: longest sequence routed to launch k
 };
 
 __global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__ count_ptr, const int32_t *__restrict__ total_ptr,
                                                      int32_t *off, int cap, RouteTable rt, int32_t *__restrict__ order,
                                                      int32_t *__restrict__ dyn, int32_t *__restrict__ ctl, int nctl,
-                                                     int32_t *__restrict__ redo) {
+                                                     int32_t *__restrict__ redo, int32_t *status) {
   __shared__ int cnt[kMaxDynLaunches], beg[kMaxDynLaunches], fill[kMaxDynLaunches];
   const int tid = threadIdx.x;
   const int count = min(max(*count_ptr, 0), cap);
@@ -634,6 +635,16 @@ __global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__
     // Few sequences of a kernel family (no more than the device runs at once): ONE launch of the family's longest class,
     // so that the call costs one fold latency per family instead of one per length class.
     merge_w = merge_c = 0;
+    if (rt.cfirst >= 0) {
+      // more cluster-length sequences than the caller's bound (and the workspace) allows: fold NOTHING of this batch and say so
+      int nc = 0;
+      for (int k = rt.cfirst; k <= rt.clast; ++k) nc += cnt[k];
+      if (nc > rt.ccap) {
+        for (int k = 0; k < rt.nl; ++k) cnt[k] = 0;
+        dyn[2 * rt.nl] = 0;
+        atomicExch(status, 101);
+      }
+    }
     if (rt.merged >= 0 && rt.wfirst >= 0) {
       int nw = 0;
       for (int k = rt.wfirst; k <= rt.wlast; ++k) nw += cnt[k];
@@ -673,15 +684,16 @@ __global__ void __launch_bounds__(1024) route_kernel(const int32_t *__restrict__
 
 struct DynPlanImpl {
   uint64_t epoch = ~0ull;
-  int cap = 0, lmax = 0;
+  int cap = 0, ccap = 0, lmax = 0;
   Limits lim;
   std::vector<Launch> launches;
   RouteTable rt;
 };
 
-int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen, int cap) {
+int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen, int cap, int ccap) {
   p->lim = make_limits(c);
   p->cap = cap;
+  p->ccap = ccap;
   p->launches.clear();
   const Limits &lim = p->lim;
   int lmax = 0;
@@ -735,8 +747,9 @@ int build_dyn_plan(Context *c, DynPlanImpl *p, const int32_t *lengths, int nlen,
       int q0 = 0;
       while (q0 + 1 < kNumClusterClasses && kClusterClasses[q0] < cmaxlen) ++q0;
       const size_t per_seq = 2 * cluster_table_stride(kClusterClasses[q0]) * sizeof(int16_t);
-      if (per_seq * (size_t)cap > kClusterWorkspaceCap) return fail(RNAFOLD_EINVAL, "device-routed batch too large for the cluster workspace");
-      p->launches.push_back(Launch{0, cap, kClusterClasses[q0], kKindCluster, false});
+      if (per_seq * (size_t)ccap > kClusterWorkspaceCap) return fail(RNAFOLD_EINVAL, "device-routed batch too large for the cluster workspace");
+      p->launches.push_back(Launch{0, ccap, kClusterClasses[q0], kKindCluster, false});
+      rt.ccap = ccap;
       rt.upper[p->launches.size() - 1] = lim.cluster_limit;
       rt.cfirst = rt.clast = (int)p->launches.size() - 1;
       rt.cmax = cached_occ(c, 1, kClusterClasses[q0], 2, 0);
@@ -767,8 +780,10 @@ int fold_hamming_batch_enqueue(const uint8_t *seq, const int32_t *off, int32_t B
 
 // env.cu: the same for a batch whose size lives on the device (no host round trip at all).  `lengths` lists the
 // sequence lengths that can occur, `cap` bounds the count; off[0..count-1] are filled by the producer and
-// off[count] = *total_ptr is written here.  *plan caches the launch list between calls.
-int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int cap, const uint8_t *seq, int32_t *off,
+// off[count] = *total_ptr is written here.  *plan caches the launch list between calls.  cluster_cap (<= cap, 0 = cap) bounds
+// the sequences of cluster length among them (their global tables are what the workspace is sized by); a batch that breaks
+// the promise is not folded at all and sets status code 101.
+int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int cap, int cluster_cap, const uint8_t *seq, int32_t *off,
                              const int32_t *count_ptr, const int32_t *total_ptr, const uint8_t *target, uint8_t *db_out,
                              int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream) {
   std::lock_guard<std::mutex> lk(g_mu);
@@ -777,8 +792,9 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
   if (!plan || !lengths || nlen <= 0 || cap <= 0 || !seq || !off || !count_ptr) return fail(RNAFOLD_EINVAL, "bad arguments");
   DynPlanImpl *p = (DynPlanImpl *)*plan;
   if (!p) *plan = p = new DynPlanImpl();
-  if (p->epoch != c->params_epoch || p->cap != cap) {
-    int rc = build_dyn_plan(c, p, lengths, nlen, cap);
+  const int ccap = (cluster_cap > 0 && cluster_cap < cap) ? cluster_cap : cap;
+  if (p->epoch != c->params_epoch || p->cap != cap || p->ccap != ccap) {
+    int rc = build_dyn_plan(c, p, lengths, nlen, cap, ccap);
     if (rc) return rc;
   }
   cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
@@ -792,7 +808,7 @@ int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int 
   CUDA_TRY(c->d_ctl.reserve(sizeof(int32_t) * (size_t)(2 * nl + 2)));
   CUDA_TRY(c->d_redo.reserve(sizeof(int32_t) * (size_t)cap));
   route_kernel<<<1, 1024, 0, st>>>(count_ptr, total_ptr, off, cap, p->rt, (int32_t *)c->d_order.p, (int32_t *)c->d_dyn.p,
-                                   (int32_t *)c->d_ctl.p, 2 * nl + 2, (int32_t *)c->d_redo.p);
+                                   (int32_t *)c->d_ctl.p, 2 * nl + 2, (int32_t *)c->d_redo.p, c->d_status);
   CUDA_TRY(cudaGetLastError());
   c->last_launches++;
   // both kernel families present: the wavefront launches run on stream2 beside the cluster / global-table launches

@@ -37,6 +37,7 @@ using rnafold::set_error;
   } while (0)
 
 constexpr int kMaxDelay = 64;
+constexpr int kMaxFinishes = 8;   // an environment may finish this often within one window of deferred rewards
 constexpr int kRows = 10;  // 6 structure-motif rows (O C I H M E) + 4 nucleotide rows (A C G U)
 
 struct Env {
@@ -67,13 +68,14 @@ struct Env {
   int32_t *h_status = nullptr;  // pinned: the library's sticky status word, read with the end-of-step copies
   // deferred rewards (rnafold_env_config_delay): terminal sequences of up to `delay` consecutive steps are folded together
   int delay = 1;                // requested window (1 = every step folds its own terminals)
-  int min_episode = 1;          // shortest episode of the data set, in steps: no environment finishes twice within that many
+  int min_episode = 1;          // shortest episode of the data set, in steps: a window of w steps sees <= ceil(w / min_episode) finishes per environment
   int win = 0;                  // steps accumulated in the open window
   double win_exp = 0.0;         // their reward exponent
   double *win_r[kMaxDelay] = {};   // the callers' reward buffers of those steps (device pointers or null)
-  int32_t *d_pend = nullptr, *d_pend_t = nullptr;   // per environment: 1 + window step of its pending terminal / its target then
+  int32_t *d_pend = nullptr, *d_pend_t = nullptr;   // per batch slot of the open window: the window step it finished in / its target
   std::vector<int32_t> lens;    // distinct target lengths (what the device-routed fold must be prepared for)
   void *plan = nullptr;         // launch list of the device-routed fold (capi.cu)
+  void *plan_win = nullptr;     // ... of a window of deferred rewards (more entries)
   // statistics: episodes, solved, sum_hd, steps (int64) ; sum_reward, sum_mfe_kcal (double)
   unsigned long long *d_istat = nullptr;
   double *d_fstat = nullptr;
@@ -214,6 +216,10 @@ __global__ void env_finish_kernel(int n_envs, int n_targets, int lmax, int k, in
       last_seq[(size_t)e * lmax + q] = ch;
       my_u += ch == 'U';
     }
+    for (int q = len + threadIdx.x; q < lmax; q += blockDim.x) {   // nothing of an earlier, longer solution stays behind
+      last_db[(size_t)e * lmax + q] = '.';
+      last_seq[(size_t)e * lmax + q] = '-';
+    }
     if (gc_penalty && my_u) atomicAdd(&n_u, my_u);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -314,9 +320,9 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
       slot_of[e] = slot;
       keys[slot] = ((unsigned long long)(unsigned)e << 32) | (unsigned long long)(unsigned)ep[e];
       boff[slot] = o0;
-      if (full) {   // deferred rewards: which step of the window this terminal belongs to, and its target
-        pend[e] = jstep + 1;
-        pend_t[e] = t;
+      if (full) {   // deferred rewards: which step of the window this batch entry belongs to, and its target
+        pend[slot] = jstep;
+        pend_t[slot] = t;
       }
     }
     done[e] = (uint8_t)fin;
@@ -375,30 +381,37 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
 struct WindowRewards {
   double *r[kMaxDelay];
 };
-__global__ void env_rewards_kernel(int n_envs, int lmax, int gc_penalty, int32_t *pend, const int32_t *__restrict__ pend_t,
+__global__ void env_rewards_kernel(int cap, int lmax, int gc_penalty, const int32_t *__restrict__ list,
+                                   const int32_t *__restrict__ pend, const int32_t *__restrict__ pend_t,
                                    const int32_t *__restrict__ slot_of, const int32_t *__restrict__ off,
                                    const double *__restrict__ brw, const int32_t *__restrict__ bhd,
                                    const int32_t *__restrict__ bmfe, const uint8_t *__restrict__ bdb,
                                    const uint8_t *__restrict__ bseq, const int32_t *__restrict__ toff, WindowRewards out,
                                    uint8_t *last_db, uint8_t *last_seq, int32_t *last_hd, int32_t *last_mfe, int32_t *last_t,
-                                   unsigned long long *istat, double *fstat, unsigned long long *packed) {
+                                   unsigned long long *istat, double *fstat, const unsigned long long *packed) {
+  // one block per batch entry (slot) of the window; an environment may own several, the last one is its "last solution"
   __shared__ int n_u;
-  const int e = blockIdx.x;
-  if (e >= n_envs) return;
-  if (e == 0 && threadIdx.x == 0) *packed = 0ull;  // the next window starts empty
-  const int j1 = pend[e];
-  if (!j1) return;
-  const int s = slot_of[e], t0 = pend_t[e];
+  const int s = blockIdx.x;
+  if (s >= cap || s >= (int)(*packed >> 32)) return;
+  const int e = list[s], t0 = pend_t[s];
   const int o0 = off[s], len = toff[t0 + 1] - toff[t0];
+  const bool latest = slot_of[e] == s;
   if (threadIdx.x == 0) n_u = 0;
   __syncthreads();
   int my_u = 0;
   for (int q = threadIdx.x; q < len; q += blockDim.x) {
     const uint8_t ch = bseq[o0 + q];
-    last_db[(size_t)e * lmax + q] = bdb[o0 + q];
-    last_seq[(size_t)e * lmax + q] = ch;
+    if (latest) {
+      last_db[(size_t)e * lmax + q] = bdb[o0 + q];
+      last_seq[(size_t)e * lmax + q] = ch;
+    }
     my_u += ch == 'U';
   }
+  if (latest)
+    for (int q = len + threadIdx.x; q < lmax; q += blockDim.x) {   // nothing of an earlier, longer solution stays behind
+      last_db[(size_t)e * lmax + q] = '.';
+      last_seq[(size_t)e * lmax + q] = '-';
+    }
   if (gc_penalty && my_u) atomicAdd(&n_u, my_u);
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -409,17 +422,18 @@ __global__ void env_rewards_kernel(int n_envs, int lmax, int gc_penalty, int32_t
       for (int q = 0; q < n_u; ++q) u += inc;
       rw = rw * 0.85 + fmin(fmax(u, 0.0), 0.15);
     }
-    double *dst = out.r[j1 - 1];
+    double *dst = out.r[pend[s]];
     if (dst) dst[e] = rw;
-    last_hd[e] = bhd[s];
-    last_mfe[e] = bmfe[s];
-    last_t[e] = t0;
+    if (latest) {
+      last_hd[e] = bhd[s];
+      last_mfe[e] = bmfe[s];
+      last_t[e] = t0;
+    }
     atomicAdd(&istat[0], 1ull);
     if (bhd[s] == 0) atomicAdd(&istat[1], 1ull);
     atomicAdd(&istat[2], (unsigned long long)bhd[s]);
     atomicAdd(&fstat[0], rw);
     atomicAdd(&fstat[1], (double)bmfe[s] / 100.0);
-    pend[e] = 0;
   }
 }
 
@@ -460,6 +474,7 @@ static void env_free(Env *e) {
   if (e->h_off) cudaFreeHost(e->h_off);
   if (e->h_status) cudaFreeHost(e->h_status);
   if (e->plan) rnafold::fold_dyn_plan_free(e->plan);
+  if (e->plan_win) rnafold::fold_dyn_plan_free(e->plan_win);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
   delete e;
 }
@@ -470,21 +485,26 @@ static int env_window_end(Env *e) {
   if (e->win == 0) return RNAFOLD_OK;
   cudaStream_t st = e->stream;
   const int N = e->n_envs;
-  int rc = rnafold::fold_hamming_dyn_enqueue(&e->plan, e->lens.data(), (int)e->lens.size(), N, e->d_bseq, e->d_off + 2, e->d_off + 1,
-                                             e->d_off, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw, e->win_exp, (void *)st);
+  // entries a window of this many steps can hold at most; only wave-length targets can finish more than once in it
+  // (a cluster-length episode takes more steps than the longest window), so the cluster workspace stays sized for N
+  const int per_env = std::min(kMaxFinishes, (e->win + e->min_episode - 1) / e->min_episode);
+  const int cap = N * std::max(1, per_env);
+  int rc = rnafold::fold_hamming_dyn_enqueue(&e->plan_win, e->lens.data(), (int)e->lens.size(), cap, N, e->d_bseq, e->d_off + 2,
+                                             e->d_off + 1, e->d_off, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw, e->win_exp,
+                                             (void *)st);
   WindowRewards out{};
   for (int j = 0; j < e->win; ++j) out.r[j] = e->win_r[j];
   e->win = 0;
   if (rc) {
     cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st);
-    cudaMemsetAsync(e->d_pend, 0, sizeof(int32_t) * (size_t)N, st);
     return rc;
   }
-  env_rewards_kernel<<<N, 128, 0, st>>>(N, e->lmax, e->gc_penalty ? 1 : 0, e->d_pend, e->d_pend_t, e->d_slot, e->d_off + 2, e->d_brw,
-                                        e->d_hd, e->d_mfe, e->d_bdb, e->d_bseq, e->d_toff, out, e->d_last_db, e->d_last_seq,
-                                        e->d_last_hd, e->d_last_mfe, e->d_last_t, e->d_istat, e->d_fstat,
-                                        reinterpret_cast<unsigned long long *>(e->d_off));
+  env_rewards_kernel<<<cap, 128, 0, st>>>(cap, e->lmax, e->gc_penalty ? 1 : 0, e->d_list, e->d_pend, e->d_pend_t, e->d_slot,
+                                          e->d_off + 2, e->d_brw, e->d_hd, e->d_mfe, e->d_bdb, e->d_bseq, e->d_toff, out,
+                                          e->d_last_db, e->d_last_seq, e->d_last_hd, e->d_last_mfe, e->d_last_t, e->d_istat,
+                                          e->d_fstat, reinterpret_cast<const unsigned long long *>(e->d_off));
   ENV_TRY(cudaGetLastError());
+  ENV_TRY(cudaMemsetAsync(e->d_off, 0, sizeof(unsigned long long), st));   // the next window starts empty
   return RNAFOLD_OK;
 }
 
@@ -567,17 +587,17 @@ int rnafold_env_create(int32_t n_envs, int32_t kernel_size, int32_t *handle) {
   ENV_TRY(dalloc(&e->d_act, N));
   ENV_TRY(dalloc(&e->d_done, N));
   ENV_TRY(dalloc(&e->d_reward, N));
-  ENV_TRY(dalloc(&e->d_list, N));
+  const size_t NE = N * kMaxFinishes;   // batch entries of one window
+  ENV_TRY(dalloc(&e->d_list, NE));
   ENV_TRY(dalloc(&e->d_slot, N));
-  ENV_TRY(dalloc(&e->d_pend, N));
-  ENV_TRY(dalloc(&e->d_pend_t, N));
-  ENV_TRY(cudaMemset(e->d_pend, 0, N * sizeof(int32_t)));
-  ENV_TRY(dalloc(&e->d_keys, N));
-  ENV_TRY(dalloc(&e->d_off, N + 4));
+  ENV_TRY(dalloc(&e->d_pend, NE));
+  ENV_TRY(dalloc(&e->d_pend_t, NE));
+  ENV_TRY(dalloc(&e->d_keys, NE));
+  ENV_TRY(dalloc(&e->d_off, NE + 4));
   ENV_TRY(cudaMemset(e->d_off, 0, (N + 4) * sizeof(int32_t)));
-  ENV_TRY(dalloc(&e->d_hd, N));
-  ENV_TRY(dalloc(&e->d_mfe, N));
-  ENV_TRY(dalloc(&e->d_brw, N));
+  ENV_TRY(dalloc(&e->d_hd, NE));
+  ENV_TRY(dalloc(&e->d_mfe, NE));
+  ENV_TRY(dalloc(&e->d_brw, NE));
   ENV_TRY(dalloc(&e->d_last_hd, N));
   ENV_TRY(dalloc(&e->d_last_mfe, N));
   ENV_TRY(dalloc(&e->d_last_t, N));
@@ -714,9 +734,12 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
   ENV_TRY(dalloc(&e->d_toff, (size_t)n_targets + 1));
   ENV_TRY(dalloc(&e->d_seq, N * lmax));
   ENV_TRY(dalloc(&e->d_mask, N * lmax));
-  ENV_TRY(dalloc(&e->d_bseq, N * lmax + 16));
-  ENV_TRY(dalloc(&e->d_btgt, N * lmax + 16));
-  ENV_TRY(dalloc(&e->d_bdb, N * lmax + 16));
+  // bases of a window's batch: the first episode an environment finishes in it may be as long as lmax, every further one ran
+  // entirely inside the window, and an episode of L bases takes at least L / 2 steps
+  const size_t NB = N * ((size_t)lmax + 2 * kMaxDelay) + 16;
+  ENV_TRY(dalloc(&e->d_bseq, NB));
+  ENV_TRY(dalloc(&e->d_btgt, NB));
+  ENV_TRY(dalloc(&e->d_bdb, NB));
   ENV_TRY(dalloc(&e->d_last_db, N * lmax));
   ENV_TRY(dalloc(&e->d_last_seq, N * lmax));
   ENV_TRY(cudaMemcpy(e->d_tgt, bytes, total, cudaMemcpyHostToDevice));
@@ -736,7 +759,8 @@ int rnafold_env_set_targets(int32_t h, const uint8_t *bytes, const int32_t *off,
     if (std::find(e->lens.begin(), e->lens.end(), n) == e->lens.end()) e->lens.push_back(n);
   }
   if (e->plan) rnafold::fold_dyn_plan_free(e->plan);
-  e->plan = nullptr;
+  if (e->plan_win) rnafold::fold_dyn_plan_free(e->plan_win);
+  e->plan = e->plan_win = nullptr;
   env_reset_kernel<<<e->n_envs, 64, 0, e->stream>>>(e->n_envs, e->n_targets, e->lmax, e->randomize ? 1 : 0, e->seed, nullptr,
                                                      nullptr, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask);
   ENV_TRY(cudaGetLastError());
@@ -797,7 +821,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   }
   {
     // ---- deferred rewards: device outputs only, no local search
-    const int window = std::min(e->delay, e->min_episode);
+    const int window = std::min(e->delay, kMaxFinishes * e->min_episode);
     const bool dev_out = (!obs_out || env_is_device_ptr(obs_out)) && (!reward_out || env_is_device_ptr(reward_out)) &&
                          (!done_out || env_is_device_ptr(done_out));
     if (window > 1 && dev_out && !e->permute && e->auto_reset) {   // (without auto-reset a finished environment finishes again every step)
@@ -854,7 +878,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
       }
     }
   } else {
-    rc = rnafold::fold_hamming_dyn_enqueue(&e->plan, e->lens.data(), (int)e->lens.size(), N, e->d_bseq, e->d_off + 2,
+    rc = rnafold::fold_hamming_dyn_enqueue(&e->plan, e->lens.data(), (int)e->lens.size(), N, N, e->d_bseq, e->d_off + 2,
                                            e->d_off + 1, e->d_off, e->d_btgt, e->d_bdb, e->d_mfe, e->d_hd, e->d_brw,
                                            reward_exp, (void *)st);
     if (rc) {

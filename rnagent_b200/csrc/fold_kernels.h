@@ -70,7 +70,7 @@ int fold_hamming_batch_enqueue(const uint8_t *seq, const int32_t *off, int32_t B
 // capi.cu: the same for a batch whose SIZE lives on the device (count_ptr; cap bounds it; `lengths` = the sequence
 // lengths that can occur): a routing kernel bins the sequences by length class, every fold kernel reads its own
 // count from device memory -- nothing crosses to the host.  *plan caches the launch list (fold_dyn_plan_free).
-int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int cap, const uint8_t *seq, int32_t *off,
+int fold_hamming_dyn_enqueue(void **plan, const int32_t *lengths, int nlen, int cap, int cluster_cap, const uint8_t *seq, int32_t *off,
                              const int32_t *count_ptr, const int32_t *total_ptr, const uint8_t *target, uint8_t *db_out,
                              int32_t *mfe_out, int32_t *hd_out, double *reward_out, double reward_exp, void *stream);
 void fold_dyn_plan_free(void *plan);
