@@ -37,6 +37,10 @@ using rnafold::set_error;
   } while (0)
 
 constexpr int kMaxDelay = 64;
+#ifndef ENV_STEP_THREADS
+#define ENV_STEP_THREADS 128
+#endif
+constexpr int kStepThreads = ENV_STEP_THREADS;   // threads of the one-block-per-environment step kernel
 constexpr int kMaxFinishes = 8;   // an environment may finish this often within one window of deferred rewards
 constexpr int kRows = 10;  // 6 structure-motif rows (O C I H M E) + 4 nucleotide rows (A C G U)
 
@@ -831,7 +835,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
       }
       uint8_t *d_done = done_out ? done_out : e->d_done;
       double *d_rw = reward_out ? reward_out : e->d_reward;
-      env_step_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, 1, e->randomize ? 1 : 0, e->seed, d_act, e->d_toff, e->d_tgt,
+      env_step_kernel<<<N, kStepThreads, 0, st>>>(N, e->n_targets, e->lmax, e->k, 1, e->randomize ? 1 : 0, e->seed, d_act, e->d_toff, e->d_tgt,
                                             e->d_pair, e->d_mot, e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask, d_done, d_rw,
                                             e->d_istat, reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2,
                                             e->d_bseq, e->d_btgt, e->d_slot, e->d_keys, e->d_pend, e->d_pend_t, e->win,
@@ -847,7 +851,7 @@ int rnafold_env_step(int32_t h, const int32_t *actions, double reward_exp, uint8
   }
   // d_off: [0] total length, [1] count (one 64-bit word advanced atomically by the terminal environments), [2..] offsets
   // (the terminal counter is zero here: cleared by the last kernel of the previous step, by reset(), and on error returns)
-  env_step_kernel<<<N, 128, 0, st>>>(N, e->n_targets, e->lmax, e->k, 0, 0, e->seed, d_act, e->d_toff, e->d_tgt, e->d_pair, e->d_mot,
+  env_step_kernel<<<N, kStepThreads, 0, st>>>(N, e->n_targets, e->lmax, e->k, 0, 0, e->seed, d_act, e->d_toff, e->d_tgt, e->d_pair, e->d_mot,
                                         e->d_cur, e->d_idx, e->d_ep, e->d_seq, e->d_mask, e->d_done, e->d_reward, e->d_istat,
                                         reinterpret_cast<unsigned long long *>(e->d_off), e->d_list, e->d_off + 2, e->d_bseq,
                                         e->d_btgt, e->d_slot, e->d_keys, nullptr, nullptr, 0, nullptr, 0);
