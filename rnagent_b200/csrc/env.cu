@@ -291,7 +291,7 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
                                    unsigned long long *packed, int32_t *list, int32_t *boff, uint8_t *bseq, uint8_t *btgt,
                                    int32_t *slot_of, unsigned long long *keys, int32_t *pend, int32_t *pend_t, int jstep,
                                    uint8_t *obs, int full) {
-  __shared__ int sh[4];   // done, offset in the batch, target base, length
+  __shared__ int sh[7];   // done, offset in the batch, target base, length; then what the observation needs: base, length, cursor
   const int e = blockIdx.x;
   if (e >= n_envs) return;
   uint8_t *s = seq + (size_t)e * lmax, *m = mask + (size_t)e * lmax;
@@ -310,11 +310,12 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
       }
     }
     reward[e] = 0.0;
-    int fin = 0, o0 = 0;
+    int fin = 0, o0 = 0, inext = i;
     if (i < n - 1) {
       int q = i;
       while (q < n - 1 && s[q] != '-') ++q;  // stops at n-1 even if that slot is filled (reference quirk)
       idx[e] = q;
+      inext = q;
     } else {
       fin = 1;
       const unsigned long long old = atomicAdd(packed, (1ull << 32) | (unsigned long long)n);
@@ -335,6 +336,9 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
     sh[1] = o0;
     sh[2] = base;
     sh[3] = n;
+    sh[4] = base;   // (replaced below if the environment is reset)
+    sh[5] = n;
+    sh[6] = inext;
   }
   __syncthreads();
   if (sh[0]) {
@@ -353,6 +357,9 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
         cur[e] = t;
         idx[e] = 0;
         ep[e] = epn;
+        sh[4] = toff[t];
+        sh[5] = toff[t + 1] - sh[4];
+        sh[6] = 0;
       }
       for (int q = threadIdx.x; q < lmax; q += blockDim.x) {
         s[q] = '-';
@@ -362,7 +369,7 @@ __global__ void env_step_kernel(int n_envs, int n_targets, int lmax, int k, int 
     __syncthreads();
   }
   if (!full) return;   // step-synchronous rewards: env_finish_kernel resets and writes the observation after the fold
-  const int t = cur[e], base = toff[t], n = toff[t + 1] - base, i = idx[e];
+  const int base = sh[4], n = sh[5], i = sh[6];   // handed over in shared memory: no second chain of global loads
   const int w = 2 * k;
   auto cell = [&](int q) -> unsigned {
     const int row = q / w, col = q - row * w;
