@@ -568,6 +568,8 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
                   "per_gpu": stats.steps / secs / world, "us_per_vector_step": 1e6 * secs / steps,
                   "episodes_per_s": stats.episodes / secs, "envs_per_gpu": N, "steps_timed": steps,
                   "host_syncs_per_step": 0, "per_rank_us_per_vector_step": [round(v, 1) for v in rank_us],
+                  "rewards": "step-synchronous: every step's rewards are complete when the step is (one fold latency per step); "
+                             "rollout_deferred is the same loop as a rollout whose rewards may arrive up to 32 steps late",
                   "sum_of_rank_rates": sum(N * 1e6 / v for v in rank_us),
                   "rollout_deferred": {"value": dstats.steps / dsecs, "unit": "env steps/s", "per_gpu": dstats.steps / dsecs / world,
                                        "us_per_vector_step": 1e6 * dsecs / steps, "reward_delay_steps": 32,
