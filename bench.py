@@ -575,7 +575,7 @@ def secondary_metrics(torch, dist, _lib, vienna, dev, rank, world, barrier, max_
                                        "us_per_vector_step": 1e6 * dsecs / steps, "reward_delay_steps": 32,
                                        "episodes_per_s": dstats.episodes / dsecs,
                                        "note": "rnafold_env_config_delay(32): one reward row per step ([T, N] rollout buffer), the terminal folds of 32 steps "
-                                               "in one call; rewards complete at the end of the timed region (19.5 / 76 / 106 / 113 M steps/s at "
+                                               "in one call; rewards complete at the end of the timed region (20.4 / 82 / 119 / 127 M steps/s at "
                                                "delay 1 / 8 / 32 / 64, tools/env_speed.py)"},
                   "roofline": roof(stats.episodes / secs / world * synth.work_candidates(100),
                                    "terminal folds only (one per episode); the step is bound by ONE fold's latency, not by throughput"),
